@@ -1,0 +1,60 @@
+// C ABI: error handling, functional lookup, context life cycle (include/helfem_b200.h).
+#include <cstring>
+#include "../../include/helfem_b200.h"
+#include "context.h"
+#include "xc_functionals.cuh"
+
+namespace hfb {
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+}  // namespace hfb
+
+extern "C" {
+
+const char* hfb200_last_error(void) { return hfb::get_error(); }
+const char* hfb200_version(void) { return "helfem_b200 0.1 (sm_100a)"; }
+
+// Names as the reference's --method option spells them (general/dftfuncs.cpp:94-117).
+int hfb200_xc_id(const char* name) {
+  if (!name) return -1;
+  struct { const char* n; int id; } tab[] = {
+      {"none", HFB200_XC_NONE},          {"lda_x", HFB200_XC_LDA_X},
+      {"lda_c_pw", HFB200_XC_LDA_C_PW},  {"lda_c_pw_mod", HFB200_XC_LDA_C_PW_MOD},
+      {"gga_x_pbe", HFB200_XC_GGA_X_PBE}, {"gga_c_pbe", HFB200_XC_GGA_C_PBE},
+      {"mgga_x_r2scan", HFB200_XC_MGGA_X_R2SCAN}, {"mgga_c_r2scan", HFB200_XC_MGGA_C_R2SCAN}};
+  for (auto& t : tab)
+    if (strcasecmp(name, t.n) == 0) return t.id;
+  hfb::set_error("functional '%s' has no device implementation", name);
+  return -1;
+}
+
+int hfb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+void hfb200_destroy(hfb200_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  double* ptrs[] = {c->dBt, c->ddBt, c->dR, c->dW, c->dDisL, c->dDisM1L, c->dTei, c->dKtei, c->dCpl};
+  int* iptrs[] = {c->dFirst, c->dNpe, c->dElemOf};
+  for (int* p : iptrs)
+    if (p) cudaFree(p);
+  for (double* p : ptrs)
+    if (p) cudaFree(p);
+  hfb::DevBuf* bufs[] = {&c->dP, &c->dH, &c->dJ, &c->dPtot, &c->dTraces, &c->dPartial, &c->dScalars, &c->dK};
+  for (auto* b : bufs) b->release();
+  c->hIn.release();
+  c->hOut.release();
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+}  // extern "C"

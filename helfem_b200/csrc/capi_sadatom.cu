@@ -1,0 +1,316 @@
+// C ABI, spherically averaged atom: context creation, integral upload, and the three
+// operators (coulomb / exchange / eval_Fxc) in dense-host and batched-device form.
+#include <cstring>
+#include "../../include/helfem_b200.h"
+#include "context.h"
+#include "sadatom_kernels.cuh"
+
+using namespace hfb;
+
+namespace {
+
+int upload(double** dst, const std::vector<double>& src) {
+  HFB_CUDA_OK(cudaMalloc(dst, src.size() * sizeof(double)));
+  HFB_CUDA_OK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+bool valid_pair(int x_func, int c_func, int* fam) {
+  const int fx = xc::xc_family(x_func), fc = xc::xc_family(c_func);
+  if (x_func != 0 && (fx == 0 || !xc::xc_is_exchange(x_func))) return false;
+  if (c_func != 0 && (fc == 0 || xc::xc_is_exchange(c_func))) return false;
+  *fam = fx > fc ? fx : fc;
+  return *fam != 0;
+}
+
+template <int FAM, int NSPIN>
+int launch_grid_rpl(const SadGridParams& prm, int nb, size_t smem, cudaStream_t st) {
+  dim3 grid(prm.nel, nb);
+  if (prm.np_max <= 16) {
+    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sad_grid_kernel<FAM, NSPIN, 4><<<grid, 256, smem, st>>>(prm);
+  } else if (prm.np_max <= 32) {
+    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sad_grid_kernel<FAM, NSPIN, 8><<<grid, 256, smem, st>>>(prm);
+  } else {
+    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sad_grid_kernel<FAM, NSPIN, 16><<<grid, 256, smem, st>>>(prm);
+  }
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_grid(int fam, int nspin, const SadGridParams& prm, int nb, cudaStream_t st) {
+  const size_t smem = sad_grid_smem_bytes(fam, nspin, prm.np_max, prm.nq, prm.ldq);
+  if (smem > 227 * 1024) { set_error("element tables need %zu bytes of shared memory (>227 KB)", smem); return HFB200_EINVAL; }
+  if (prm.np_max > 64) { set_error("more than 64 functions per element are not supported"); return HFB200_EINVAL; }
+  if (nspin == 1) {
+    if (fam == xc::FAM_LDA) return launch_grid_rpl<xc::FAM_LDA, 1>(prm, nb, smem, st);
+    if (fam == xc::FAM_GGA) return launch_grid_rpl<xc::FAM_GGA, 1>(prm, nb, smem, st);
+    return launch_grid_rpl<xc::FAM_MGGA, 1>(prm, nb, smem, st);
+  }
+  if (fam == xc::FAM_LDA) return launch_grid_rpl<xc::FAM_LDA, 2>(prm, nb, smem, st);
+  if (fam == xc::FAM_GGA) return launch_grid_rpl<xc::FAM_GGA, 2>(prm, nb, smem, st);
+  return launch_grid_rpl<xc::FAM_MGGA, 2>(prm, nb, smem, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int hfb200_sadatom_create(hfb200_ctx** out, int device, int lmax, int nel, int nq, const int* first,
+                          const int* last, const double* r, const double* wrad, const double* bf,
+                          const double* df, const double* lf) {
+  (void)lf;  // no supported functional needs the Laplacian (reference: do_lapl arms)
+  if (!out || nel < 1 || nq < 1 || !first || !last || !r || !wrad || !bf || !df || lmax < 0) {
+    set_error("hfb200_sadatom_create: invalid argument");
+    return HFB200_EINVAL;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available: helfem_b200 has no CPU fallback");
+    return HFB200_ENODEVICE;
+  }
+  HFB_CUDA_OK(cudaSetDevice(device));
+  hfb200_ctx* c = new hfb200_ctx();
+  c->kind = CTX_SADATOM;
+  c->device = device;
+  c->lmax = lmax;
+  c->nel = nel;
+  c->nq = nq;
+  c->ldq = nq | 1;  // odd row stride: conflict-free 64-bit shared-memory columns
+  c->first.assign(first, first + nel);
+  c->last.assign(last, last + nel);
+  c->np_max = 0;
+  for (int e = 0; e < nel; e++) {
+    const int np = last[e] - first[e] + 1;
+    if (np < 1) { delete c; set_error("element %d has no functions", e); return HFB200_EINVAL; }
+    if (np > c->np_max) c->np_max = np;
+  }
+  c->nrad = last[nel - 1] + 1;
+  // tables: host (nq x np_e) column-major per element -> device [el][i][ldq]
+  const int np = c->np_max, ldq = c->ldq;
+  std::vector<double> B((size_t)nel * np * ldq, 0.0), dB((size_t)nel * np * ldq, 0.0);
+  size_t off = 0;
+  for (int e = 0; e < nel; e++) {
+    const int npe = last[e] - first[e] + 1;
+    for (int i = 0; i < npe; i++)
+      for (int p = 0; p < nq; p++) {
+        B[((size_t)e * np + i) * ldq + p] = bf[off + (size_t)i * nq + p];
+        dB[((size_t)e * np + i) * ldq + p] = df[off + (size_t)i * nq + p];
+      }
+    off += (size_t)npe * nq;
+  }
+  int rc;
+  if ((rc = upload(&c->dBt, B)) || (rc = upload(&c->ddBt, dB)) ||
+      (rc = upload(&c->dR, std::vector<double>(r, r + (size_t)nel * nq))) ||
+      (rc = upload(&c->dW, std::vector<double>(wrad, wrad + (size_t)nel * nq)))) {
+    hfb200_destroy(c);
+    return rc;
+  }
+  HFB_CUDA_OK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  *out = c;
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L,
+                           const double* const* disjoint_m1L, const double* const* prim_tei,
+                           const double* const* prim_ktei) {
+  if (!c || c->kind != CTX_SADATOM || nL < 1 || !disjoint_L || !disjoint_m1L || !prim_tei) {
+    set_error("hfb200_sadatom_set_tei: invalid argument");
+    return HFB200_EINVAL;
+  }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  const int nel = c->nel, np = c->np_max, np2 = np * np;
+  std::vector<double> dl((size_t)nL * nel * np2, 0.0), dm((size_t)nL * nel * np2, 0.0);
+  for (int L = 0; L < nL; L++)
+    for (int e = 0; e < nel; e++) {
+      const int npe = c->last[e] - c->first[e] + 1;
+      const double* a = disjoint_L[L * nel + e];
+      const double* bb = disjoint_m1L[L * nel + e];
+      for (int j = 0; j < npe; j++)
+        for (int i = 0; i < npe; i++) {
+          dl[((size_t)L * nel + e) * np2 + i + j * np] = a[i + j * npe];
+          dm[((size_t)L * nel + e) * np2 + i + j * np] = bb[i + j * npe];
+        }
+    }
+  for (double** p : {&c->dDisL, &c->dDisM1L, &c->dTei, &c->dKtei})
+    if (*p) { cudaFree(*p); *p = nullptr; }
+  int rc;
+  if ((rc = upload(&c->dDisL, dl)) || (rc = upload(&c->dDisM1L, dm))) return rc;
+  // in-element blocks, one (L, element) at a time through a padded staging buffer
+  const size_t blk = (size_t)np2 * np2;
+  HFB_CUDA_OK(cudaMalloc(&c->dTei, (size_t)nL * nel * blk * sizeof(double)));
+  if (prim_ktei) HFB_CUDA_OK(cudaMalloc(&c->dKtei, (size_t)nL * nel * blk * sizeof(double)));
+  std::vector<double> stage(blk);
+  for (int pass = 0; pass < (prim_ktei ? 2 : 1); pass++) {
+    const double* const* src = pass ? prim_ktei : prim_tei;
+    double* dst = pass ? c->dKtei : c->dTei;
+    for (int L = 0; L < nL; L++)
+      for (int e = 0; e < nel; e++) {
+        const int npe = c->last[e] - c->first[e] + 1;
+        const double* t = src[L * nel + e];
+        if (npe == np) {
+          HFB_CUDA_OK(cudaMemcpy(dst + ((size_t)L * nel + e) * blk, t, blk * sizeof(double), cudaMemcpyHostToDevice));
+        } else {
+          std::fill(stage.begin(), stage.end(), 0.0);
+          const size_t n2 = (size_t)npe * npe;
+          // both index pairs are (fast + slow*npe) -> (fast + slow*np)
+          for (int cs = 0; cs < npe; cs++)
+            for (int cf = 0; cf < npe; cf++)
+              for (int rs = 0; rs < npe; rs++)
+                for (int rf = 0; rf < npe; rf++)
+                  stage[(size_t)(rf + rs * np) + (size_t)(cf + cs * np) * np2] = t[(size_t)(rf + rs * npe) + (size_t)(cf + cs * npe) * n2];
+          HFB_CUDA_OK(cudaMemcpy(dst + ((size_t)L * nel + e) * blk, stage.data(), blk * sizeof(double), cudaMemcpyHostToDevice));
+        }
+      }
+  }
+  c->nL = nL;
+  c->have_ktei = prim_ktei != nullptr;
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_band_size(hfb200_ctx* c, int* nel, int* np_max) {
+  if (!c) { set_error("null context"); return HFB200_EINVAL; }
+  if (nel) *nel = c->nel;
+  if (np_max) *np_max = c->np_max;
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_pack_band(hfb200_ctx* c, const double* M, int ld, double* band) {
+  if (!c || !M || !band || ld < c->nrad) { set_error("pack_band: invalid argument"); return HFB200_EINVAL; }
+  const int np = c->np_max, np2 = np * np;
+  memset(band, 0, sizeof(double) * (size_t)c->nel * np2);
+  for (int e = 0; e < c->nel; e++) {
+    const int f = c->first[e], npe = c->last[e] - f + 1;
+    for (int j = 0; j < npe; j++)
+      memcpy(band + (size_t)e * np2 + (size_t)j * np, M + (size_t)f + (size_t)(f + j) * ld, sizeof(double) * npe);
+  }
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_unpack_band_add(hfb200_ctx* c, const double* band, double* M, int ld) {
+  if (!c || !M || !band || ld < c->nrad) { set_error("unpack_band: invalid argument"); return HFB200_EINVAL; }
+  const int np = c->np_max, np2 = np * np;
+  for (int e = 0; e < c->nel; e++) {
+    const int f = c->first[e], npe = c->last[e] - f + 1;
+    for (int j = 0; j < npe; j++)
+      for (int i = 0; i < npe; i++) M[(size_t)(f + i) + (size_t)(f + j) * ld] += band[(size_t)e * np2 + i + (size_t)j * np];
+  }
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                              double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
+                              double* dScalars, void* stream) {
+  if (!c || c->kind != CTX_SADATOM || nbatch < 1 || (nspin != 1 && nspin != 2) || nslices < 1 || !dP_band) {
+    set_error("hfb200_sadatom_fock_batch: invalid argument");
+    return HFB200_EINVAL;
+  }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int np2 = c->np_max * c->np_max;
+  int rc;
+  if (dH_band) {
+    int fam = 0;
+    if (!valid_pair(x_func, c_func, &fam)) {
+      set_error("functional pair (%d,%d) has no device implementation (no CPU fallback)", x_func, c_func);
+      return HFB200_EFUNC;
+    }
+    if ((rc = c->dPartial.reserve((size_t)nbatch * c->nel * 4))) return rc;
+    SadGridParams g;
+    g.Bt = c->dBt; g.dBt = c->ddBt; g.r = c->dR; g.wrad = c->dW;
+    g.nel = c->nel; g.nq = c->nq; g.ldq = c->ldq; g.np_max = c->np_max; g.nslices = nslices;
+    g.x_func = x_func; g.c_func = c_func; g.dens_thr = dens_thr;
+    g.P = dP_band; g.H = dH_band; g.partial = c->dPartial.p;
+    if ((rc = launch_grid(fam, nspin, g, nbatch, st))) return rc;
+    if (dScalars) {
+      sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(c->dPartial.p, c->nel, dScalars);
+      HFB_CUDA_OK(cudaGetLastError());
+    }
+  }
+  if (dJ_band) {
+    if (!c->dTei) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * np2))) return rc;
+    if ((rc = c->dTraces.reserve((size_t)nbatch * c->nel * 2))) return rc;
+    SadCoulombParams q;
+    q.dL = c->dDisL; q.dm1L = c->dDisM1L; q.tei = c->dTei;
+    q.nel = c->nel; q.np_max = c->np_max; q.nslices = nslices; q.nspin = nspin;
+    q.P = dP_band; q.Ptot = c->dPtot.p; q.traces = c->dTraces.p; q.J = dJ_band;
+    dim3 grid(c->nel, nbatch);
+    sad_trace_kernel<<<grid, 256, 0, st>>>(q);
+    HFB_CUDA_OK(cudaGetLastError());
+    sad_coulomb_kernel<<<grid, 256, np2 * sizeof(double), st>>>(q);
+    HFB_CUDA_OK(cudaGetLastError());
+  }
+  return HFB200_OK;
+}
+
+int hfb200_sadatom_coulomb(hfb200_ctx* c, const double* P, int ldp, double* J, int ldj) {
+  if (!c || c->kind != CTX_SADATOM || !P || !J || ldp < c->nrad || ldj < c->nrad) {
+    set_error("hfb200_sadatom_coulomb: density matrix does not match basis set");
+    return HFB200_EINVAL;
+  }
+  if (!c->dTei) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  const size_t nband = (size_t)c->nel * c->np_max * c->np_max;
+  int rc;
+  if ((rc = c->hIn.reserve(nband)) || (rc = c->hOut.reserve(nband)) || (rc = c->dP.reserve(nband)) || (rc = c->dJ.reserve(nband))) return rc;
+  hfb200_sadatom_pack_band(c, P, ldp, c->hIn.p);
+  HFB_CUDA_OK(cudaMemcpyAsync(c->dP.p, c->hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if ((rc = hfb200_sadatom_fock_batch(c, 1, 0, 0, 1, 1, 0.0, c->dP.p, c->dJ.p, nullptr, nullptr, c->stream))) return rc;
+  HFB_CUDA_OK(cudaMemcpyAsync(c->hOut.p, c->dJ.p, nband * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  for (int j = 0; j < c->nrad; j++) memset(J + (size_t)j * ldj, 0, sizeof(double) * c->nrad);
+  HFB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  return hfb200_sadatom_unpack_band_add(c, c->hOut.p, J, ldj);
+}
+
+int hfb200_sadatom_eval_fxc(hfb200_ctx* c, int x_func, int c_func, int nspin, const double* Pa,
+                            const double* Pb, int ldp, int nslices, double dens_thr, double* Ha,
+                            double* Hb, int ldh, int beta, double* Exc, double* Nel) {
+  if (!c || c->kind != CTX_SADATOM || !Pa || !Ha || (nspin != 1 && nspin != 2) || ldp < c->nrad || ldh < c->nrad ||
+      nslices < 1 || (nspin == 2 && (!Pb || (beta && !Hb)))) {
+    set_error("hfb200_sadatom_eval_fxc: invalid argument / empty density matrix");
+    return HFB200_EINVAL;
+  }
+  int fam = 0;
+  if (!valid_pair(x_func, c_func, &fam)) {
+    set_error("functional pair (%d,%d) has no device implementation (no CPU fallback)", x_func, c_func);
+    return HFB200_EFUNC;
+  }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  const size_t nblk = (size_t)c->nel * c->np_max * c->np_max;
+  const size_t nband = nblk * nslices * nspin;
+  int rc;
+  if ((rc = c->hIn.reserve(nband)) || (rc = c->hOut.reserve(nband + 4)) || (rc = c->dP.reserve(nband)) ||
+      (rc = c->dH.reserve(nband)) || (rc = c->dScalars.reserve(4)))
+    return rc;
+  for (int s = 0; s < nspin; s++)
+    for (int l = 0; l < nslices; l++)
+      hfb200_sadatom_pack_band(c, (s ? Pb : Pa) + (size_t)l * ldp * c->nrad, ldp, c->hIn.p + ((size_t)s * nslices + l) * nblk);
+  HFB_CUDA_OK(cudaMemcpyAsync(c->dP.p, c->hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if ((rc = hfb200_sadatom_fock_batch(c, 1, x_func, c_func, nspin, nslices, dens_thr, c->dP.p, nullptr, c->dH.p, c->dScalars.p, c->stream)))
+    return rc;
+  HFB_CUDA_OK(cudaMemcpyAsync(c->hOut.p, c->dH.p, nband * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  HFB_CUDA_OK(cudaMemcpyAsync(c->hOut.p + nband, c->dScalars.p, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  // zero the dense outputs while the device works (H.zeros() in the reference)
+  for (int s = 0; s < nspin; s++) {
+    double* H = s ? Hb : Ha;
+    if (!H) continue;
+    for (int l = 0; l < nslices; l++)
+      for (int j = 0; j < c->nrad; j++) memset(H + (size_t)l * ldh * c->nrad + (size_t)j * ldh, 0, sizeof(double) * c->nrad);
+  }
+  HFB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  for (int s = 0; s < nspin; s++) {
+    double* H = s ? Hb : Ha;
+    if (s == 1 && !beta) continue;
+    for (int l = 0; l < nslices; l++)
+      hfb200_sadatom_unpack_band_add(c, c->hOut.p + ((size_t)s * nslices + l) * nblk, H + (size_t)l * ldh * c->nrad, ldh);
+  }
+  if (Exc) *Exc = c->hOut.p[nband + 0];
+  if (Nel) *Nel = c->hOut.p[nband + 1];
+  return HFB200_OK;
+}
+
+}  // extern "C"

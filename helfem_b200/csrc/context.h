@@ -1,0 +1,79 @@
+// Device context shared by the C-ABI entry points.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+namespace hfb {
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define HFB_CUDA_OK(call)                                                                   \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      hfb::set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(e_), __FILE__, __LINE__, \
+                     cudaGetErrorString(e_));                                               \
+      return (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver) ? -4 : -5;      \
+    }                                                                                       \
+  } while (0)
+
+/// Growable device / pinned-host scratch buffer.
+struct DevBuf {
+  double* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, n * sizeof(double));
+    if (e != cudaSuccess) { set_error("cudaMalloc of %zu bytes failed: %s", n * sizeof(double), cudaGetErrorString(e)); return -5; }
+    cap = n;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct PinBuf {
+  double* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return 0;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMallocHost(&p, n * sizeof(double));
+    if (e != cudaSuccess) { set_error("cudaMallocHost of %zu bytes failed: %s", n * sizeof(double), cudaGetErrorString(e)); return -5; }
+    cap = n;
+    return 0;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+enum CtxKind { CTX_SADATOM = 1, CTX_ATOMIC = 2, CTX_DIATOMIC = 3 };
+
+}  // namespace hfb
+
+// The opaque handle of include/helfem_b200.h
+struct hfb200_ctx {
+  int kind = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  // ---- radial tables ----
+  int lmax = 0, nel = 0, nq = 0, ldq = 0, np_max = 0, nrad = 0;
+  std::vector<int> first, last;
+  double *dBt = nullptr, *ddBt = nullptr, *dR = nullptr, *dW = nullptr;
+  int *dFirst = nullptr, *dNpe = nullptr, *dElemOf = nullptr;  // [nel], [nel], [nrad][2]
+  double* dCpl = nullptr;  // sadatom exchange coupling [lout][lin][L]
+  // ---- stored integrals (padded to np_max) ----
+  int nL = 0;
+  bool have_ktei = false;
+  double *dDisL = nullptr, *dDisM1L = nullptr;  // [nL][nel][np2]
+  double *dTei = nullptr, *dKtei = nullptr;     // [nL][nel][np2*np2]
+  // ---- scratch ----
+  hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;
+  hfb::PinBuf hIn, hOut;
+};

@@ -1,0 +1,197 @@
+// Flat C entry points over the host-side mirror classes, so the Python test / bench harness
+// (ctypes) can drive exactly the objects a C++ driver would use.  Every function returns 0 on
+// success; C++ exceptions are translated to a non-zero code (1 = std::logic_error,
+// 2 = std::runtime_error, 3 = other) and the message kept for hfh_last_error().
+#include <cstring>
+#include <string>
+#include "../../include/helfem_b200.h"
+#include "angular.h"
+#include "sadatom.h"
+
+using namespace hfb;
+
+static thread_local std::string g_msg;
+
+#define HFH_TRY try {
+#define HFH_CATCH                                           \
+  }                                                         \
+  catch (const std::logic_error& e) { g_msg = e.what(); return 1; }   \
+  catch (const std::runtime_error& e) { g_msg = e.what(); return 2; } \
+  catch (const std::exception& e) { g_msg = e.what(); return 3; }     \
+  return 0;
+
+extern "C" {
+
+const char* hfh_last_error(void) { return g_msg.c_str(); }
+
+// ---- FEM primitives (exposed for the known-answer tests) ----
+int hfh_chebyshev(int n, double* x, double* w) {
+  HFH_TRY
+  Vec xv, wv;
+  fem::chebyshev(n, xv, wv);
+  memcpy(x, xv.data(), n * sizeof(double));
+  memcpy(w, wv.data(), n * sizeof(double));
+  HFH_CATCH
+}
+int hfh_lobatto_nodes(int n, double* x) {
+  HFH_TRY
+  Vec xv = fem::lobatto_nodes(n);
+  memcpy(x, xv.data(), n * sizeof(double));
+  HFH_CATCH
+}
+int hfh_get_grid(double rmax, int nel, int igrid, double zexp, double* bval) {
+  HFH_TRY
+  Vec b = fem::get_grid(rmax, nel, igrid, zexp);
+  memcpy(bval, b.data(), b.size() * sizeof(double));
+  HFH_CATCH
+}
+/// values of the n-th derivative of the primitive basis at x: out is (nx x nbf) column-major
+int hfh_poly_eval(int primbas, int nnodes, int nx, const double* x, int n, double element_length, double* out, int* nbf) {
+  HFH_TRY
+  fem::PolyBasis p(primbas, nnodes);
+  Mat m = p.eval_dnf(Vec(x, x + nx), n, element_length);
+  if (nbf) *nbf = (int)m.nc;
+  if (out) memcpy(out, m.ptr(), m.size() * sizeof(double));
+  HFH_CATCH
+}
+/// quadrature::twoe_integral on [rmin,rmax] for the full primitive basis (inttest.cpp known-answer test)
+int hfh_twoe_integral(int primbas, int nnodes, int nquad, double rmin, double rmax, int L, double* out) {
+  HFH_TRY
+  fem::PolyBasis p(primbas, nnodes);
+  Vec xq, wq;
+  fem::chebyshev(nquad, xq, wq);
+  Mat m = fem::twoe_integral(rmin, rmax, xq, wq, p, L);
+  memcpy(out, m.ptr(), m.size() * sizeof(double));
+  HFH_CATCH
+}
+double hfh_gaunt(int L, int M, int l, int m, int lp, int mp) { return angular::gaunt_coefficient(L, M, l, m, lp, mp); }
+double hfh_modified_gaunt(int lj, int mj, int L, int M, int li, int mi) { return angular::modified_gaunt_coefficient(lj, mj, L, M, li, mi); }
+void hfh_ylm(int l, int m, double cth, double phi, double* re, double* im) {
+  std::complex<double> y = angular::spherical_harmonics(l, m, cth, phi);
+  *re = y.real();
+  *im = y.imag();
+}
+
+// ---- sadatom ----
+int hfh_sadatom_new(void** out, int Z, int primbas, int nnodes, int nquad, int nelem, double rmax, int igrid, double zexp,
+                    int taylor_order, int lmax, int zeroder, int device) {
+  HFH_TRY
+  fem::PolyBasis poly(primbas, nnodes);
+  if (nquad <= 0) nquad = 5 * poly.get_nbf();  // sadatom/main.cpp:211-213
+  if (taylor_order < 0) taylor_order = poly.get_nprim() - 1;  // sadatom/main.cpp:219-220
+  Vec bval = fem::get_grid(rmax, nelem, igrid, zexp);
+  *out = new sadatom::TwoDBasis(Z, poly, zeroder != 0, nquad, bval, taylor_order, lmax, device);
+  HFH_CATCH
+}
+void hfh_sadatom_free(void* h) { delete (sadatom::TwoDBasis*)h; }
+
+int hfh_sadatom_dims(void* h, int* nbf, int* nel, int* nq, int* np_max, double* taylor_cutoff, double* taylor_diff) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  if (nbf) *nbf = (int)b->Nbf();
+  if (nel) *nel = (int)b->get_rad_Nel();
+  if (nq) *nq = b->get_radial().get_nquad();
+  if (np_max) {
+    *np_max = 0;
+    for (size_t e = 0; e < b->get_rad_Nel(); e++) *np_max = std::max(*np_max, (int)b->get_radial().Nprim(e));
+  }
+  if (taylor_cutoff) *taylor_cutoff = b->get_radial().get_small_r_taylor_cutoff();
+  if (taylor_diff) *taylor_diff = b->get_radial().get_taylor_diff();
+  HFH_CATCH
+}
+int hfh_sadatom_idx(void* h, int* first, int* last) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  for (size_t e = 0; e < b->get_rad_Nel(); e++) {
+    size_t f, l;
+    b->get_radial().get_idx(e, f, l);
+    first[e] = (int)f;
+    last[e] = (int)l;
+  }
+  HFH_CATCH
+}
+/// which: 0 overlap, 1 kinetic, 2 kinetic_l, 3 nuclear
+int hfh_sadatom_matrix(void* h, int which, double* out) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  Mat m = which == 0 ? b->overlap() : which == 1 ? b->kinetic() : which == 2 ? b->kinetic_l() : b->nuclear();
+  memcpy(out, m.ptr(), m.size() * sizeof(double));
+  HFH_CATCH
+}
+/// tables of element iel: r, wrad (nq), bf/df/lf (nq x np_iel column-major); NULLs are skipped
+int hfh_sadatom_tables(void* h, int iel, double* r, double* wrad, double* bf, double* df, double* lf) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  if (r) { Vec v = b->get_r(iel); memcpy(r, v.data(), v.size() * sizeof(double)); }
+  if (wrad) { Vec v = b->get_wrad(iel); memcpy(wrad, v.data(), v.size() * sizeof(double)); }
+  if (bf) { Mat m = b->eval_bf(iel); memcpy(bf, m.ptr(), m.size() * sizeof(double)); }
+  if (df) { Mat m = b->eval_df(iel); memcpy(df, m.ptr(), m.size() * sizeof(double)); }
+  if (lf) { Mat m = b->eval_lf(iel); memcpy(lf, m.ptr(), m.size() * sizeof(double)); }
+  HFH_CATCH
+}
+int hfh_sadatom_compute_tei(void* h, int nL, int exchange) {
+  HFH_TRY
+  ((sadatom::TwoDBasis*)h)->compute_tei(nL, exchange != 0);
+  HFH_CATCH
+}
+int hfh_sadatom_get_tei(void* h, int L, int iel, double* disL, double* dism1L, double* tei, double* ktei) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  const size_t idx = (size_t)L * b->get_rad_Nel() + iel;
+  if (L >= b->get_nL()) throw std::logic_error("Primitive teis have not been computed!\n");
+  if (disL) memcpy(disL, b->get_disjoint_L()[idx].ptr(), b->get_disjoint_L()[idx].size() * sizeof(double));
+  if (dism1L) memcpy(dism1L, b->get_disjoint_m1L()[idx].ptr(), b->get_disjoint_m1L()[idx].size() * sizeof(double));
+  if (tei) memcpy(tei, b->get_prim_tei()[idx].ptr(), b->get_prim_tei()[idx].size() * sizeof(double));
+  if (ktei) {
+    if (b->get_prim_ktei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+    memcpy(ktei, b->get_prim_ktei()[idx].ptr(), b->get_prim_ktei()[idx].size() * sizeof(double));
+  }
+  HFH_CATCH
+}
+int hfh_sadatom_context(void* h, hfb200_ctx** ctx) {
+  HFH_TRY
+  *ctx = ((sadatom::TwoDBasis*)h)->context();
+  HFH_CATCH
+}
+int hfh_sadatom_coulomb(void* h, const double* P, double* J) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Mat Pm(n, n);
+  memcpy(Pm.ptr(), P, n * n * sizeof(double));
+  Mat Jm = b->coulomb(Pm);
+  memcpy(J, Jm.ptr(), n * n * sizeof(double));
+  HFH_CATCH
+}
+int hfh_sadatom_exchange(void* h, const double* P, int nslices, double* K) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Cube Pc(n, n, nslices);
+  memcpy(Pc.ptr(), P, n * n * nslices * sizeof(double));
+  Cube Kc = b->exchange(Pc);
+  memcpy(K, Kc.ptr(), n * n * nslices * sizeof(double));
+  HFH_CATCH
+}
+int hfh_sadatom_eval_fxc(void* h, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, int nslices,
+                         double thr, double* Ha, double* Hb, int beta, double* Exc, double* Nel) {
+  HFH_TRY
+  auto* b = (sadatom::TwoDBasis*)h;
+  const size_t n = b->Nbf(), tot = n * n * nslices;
+  sadatom::DFTGrid grid(b);
+  Cube P1(n, n, nslices), H1, H2;
+  memcpy(P1.ptr(), Pa, tot * sizeof(double));
+  if (nspin == 1) {
+    grid.eval_Fxc(x_func, Vec(), c_func, Vec(), P1, H1, *Exc, *Nel, thr);
+    memcpy(Ha, H1.ptr(), tot * sizeof(double));
+  } else {
+    Cube P2(n, n, nslices);
+    memcpy(P2.ptr(), Pb, tot * sizeof(double));
+    grid.eval_Fxc(x_func, Vec(), c_func, Vec(), P1, P2, H1, H2, *Exc, *Nel, beta != 0, thr);
+    memcpy(Ha, H1.ptr(), tot * sizeof(double));
+    if (Hb) memcpy(Hb, H2.ptr(), tot * sizeof(double));
+  }
+  HFH_CATCH
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+/* helfem_b200 -- C ABI of the B200 Fock-build library (libhelfem_b200.so).
+ *
+ * The reference (kluonj/HelFEM) has no FFI: its hot path sits behind C++ member functions
+ * that take and return Armadillo objects.  This header is the thin C layer those member
+ * functions bind to in the drop-in build (see INTEGRATION.md for the 10-line shims):
+ *
+ *   helfem::sadatom::basis::TwoDBasis::coulomb(P)      sadatom/basis.cpp:296   -> hfb200_sadatom_coulomb
+ *   helfem::sadatom::basis::TwoDBasis::exchange(P)     sadatom/basis.cpp:360   -> hfb200_sadatom_exchange
+ *   helfem::sadatom::dftgrid::DFTGrid::eval_Fxc(...)   sadatom/dftgrid.cpp:874,941 -> hfb200_sadatom_eval_fxc
+ *   helfem::atomic::basis::TwoDBasis::coulomb/exchange atomic/TwoDBasis.cpp:817,957 -> hfb200_atomic_coulomb/_exchange
+ *   helfem::atomic::dftgrid::DFTGrid::eval_Fxc(...)    atomic/dftgrid.cpp:810,872  -> hfb200_atomic_eval_fxc
+ *   helfem::diatomic::basis::TwoDBasis::coulomb/exchange diatomic/basis.cpp:1359,1532 -> hfb200_diatomic_*
+ *
+ * Conventions: all matrices are FP64 column-major with an explicit leading dimension (what
+ * arma::mat::memptr() gives); every function returns 0 on success and a negative HFB200_E*
+ * code otherwise and never throws; hfb200_last_error() returns the message the C++ shim
+ * re-throws as the exception type the reference uses (std::logic_error for missing
+ * integrals / size mismatch, std::runtime_error for an unsupported functional).
+ * One opaque context per basis object holds every constant of the path on the device
+ * (basis tables on the quadrature grid, weights, stored radial integrals); per call only the
+ * density goes down and the Fock contribution comes back.  There is NO CPU fallback: without
+ * a CUDA device every compute entry point fails with HFB200_ENODEVICE.
+ */
+#ifndef HELFEM_B200_H
+#define HELFEM_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HFB200_OK 0
+#define HFB200_EINVAL (-1)    /* size / argument mismatch      (reference: std::logic_error)   */
+#define HFB200_ENOTEI (-2)    /* integrals not uploaded        (reference: "Primitive teis have not been computed!") */
+#define HFB200_EFUNC (-3)     /* unsupported functional        (reference: std::runtime_error)  */
+#define HFB200_ENODEVICE (-4) /* no CUDA device / CUDA failure; the library never falls back to the CPU */
+#define HFB200_ECUDA (-5)
+
+/* XC functionals implemented on the device (named as on the reference's command line,
+ * general/dftfuncs.cpp:94-117).  Anything else yields HFB200_EFUNC. */
+#define HFB200_XC_NONE 0
+#define HFB200_XC_LDA_X 1
+#define HFB200_XC_LDA_C_PW 12
+#define HFB200_XC_LDA_C_PW_MOD 13
+#define HFB200_XC_GGA_X_PBE 101
+#define HFB200_XC_GGA_C_PBE 130
+#define HFB200_XC_MGGA_X_R2SCAN 497
+#define HFB200_XC_MGGA_C_R2SCAN 498
+
+typedef struct hfb200_ctx hfb200_ctx;
+
+const char* hfb200_last_error(void);
+const char* hfb200_version(void);
+/* "lda_x" -> HFB200_XC_LDA_X ...; -1 if the functional has no device implementation. */
+int hfb200_xc_id(const char* libxc_name);
+/* Number of visible CUDA devices (0 if none; never an error). */
+int hfb200_device_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Radial context: the spherically averaged atom (sadatom) and the radial part of `atomic`.
+ *
+ * nel elements, nq quadrature points per element, element iel owns the radial functions
+ * first[iel]..last[iel] (FiniteElementBasis::get_idx).  r, wrad: nel*nq values
+ * (RadialBasis::get_r / get_wrad).  bf, df, lf: for each element the (nq x np_iel) column-major
+ * matrix RadialBasis::get_bf/get_df/get_lf(iel) returns, concatenated over elements (lf may be
+ * NULL: no supported functional needs the Laplacian).  lmax: largest l of the density cube.
+ * ------------------------------------------------------------------------------------------ */
+int hfb200_sadatom_create(hfb200_ctx** ctx, int device, int lmax, int nel, int nq, const int* first,
+                          const int* last, const double* r, const double* wrad, const double* bf,
+                          const double* df, const double* lf);
+/* Stored integrals built by TwoDBasis::compute_tei (sadatom/basis.cpp:181-218).  Arrays of
+ * nL*nel pointers, entry [L*nel+iel]: disjoint_L / disjoint_m1L (np x np), prim_tei / prim_ktei
+ * (np^2 x np^2).  prim_ktei may be NULL if exchange() is never called. */
+int hfb200_sadatom_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoint_L,
+                           const double* const* disjoint_m1L, const double* const* prim_tei,
+                           const double* const* prim_ktei);
+void hfb200_destroy(hfb200_ctx* ctx);
+
+/* J = coulomb(P): P, J are nrad x nrad (host). */
+int hfb200_sadatom_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
+/* K = exchange(P): P, K are nrad x nrad x nslices cubes (slice stride ld*nrad); returns -K
+ * like the reference. */
+int hfb200_sadatom_exchange(hfb200_ctx* ctx, const double* P, int ldp, int nslices, double* K, int ldk);
+/* eval_Fxc: nspin=1 restricted (Pb, Hb ignored), nspin=2 unrestricted (beta!=0 also fills Hb).
+ * P*, H* are nrad x nrad x nslices cubes; H is fully overwritten (zero outside the element
+ * blocks, like H.zeros() in the reference). */
+int hfb200_sadatom_eval_fxc(hfb200_ctx* ctx, int x_func, int c_func, int nspin, const double* Pa,
+                            const double* Pb, int ldp, int nslices, double dens_thr, double* Ha,
+                            double* Hb, int ldh, int beta, double* Exc, double* Nel);
+
+/* ---- batched, device-resident form of the same three operators ---------------------------
+ * Many independent Fock builds on the same basis (trial configurations of one atom, atoms of
+ * a sweep on a common grid, spin channels) in one pass.  Densities and results stay on the
+ * device in "element-band" layout: for build b, spin s, slice l, element e the np_max x np_max
+ * block (column-major, zero padded) at offset (((b*nspin+s)*nslices+l)*nel+e)*np_max^2 holds
+ * M(first[e]+i, first[e]+j).  J bands are [b][e][np_max^2]; scalars are [b][4] = Exc, Nel, Ekin-like
+ * tau integral, reserved.  Pointers are DEVICE pointers; stream is a cudaStream_t (0 = default). */
+int hfb200_sadatom_band_size(hfb200_ctx* ctx, int* nel, int* np_max);
+int hfb200_sadatom_pack_band(hfb200_ctx* ctx, const double* M /*host nrad x nrad*/, int ld, double* band /*host*/);
+int hfb200_sadatom_unpack_band_add(hfb200_ctx* ctx, const double* band /*host*/, double* M, int ld);
+int hfb200_sadatom_fock_batch(hfb200_ctx* ctx, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                              double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
+                              double* dScalars, void* stream);
+
+/* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
+ * outputs are overwritten with exchange + correlation). */
+int hfb200_xc_eval(int device, int x_func, int c_func, int nspin, int n, double dens_thr, const double* rho,
+                   const double* sigma, const double* tau, double* exc, double* vrho, double* vsigma,
+                   double* vtau);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,152 @@
+"""ORACLE package (test infrastructure).  CPU restatement of the reference's algorithm for the
+Fock-build path.  May be imported ONLY by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs -- never by helfem_b200 (the product).
+
+  fem_oracle.py        numpy restatement of the finite-element setup (tables + stored integrals)
+  xc_oracle.hpp        XC functionals, complex-step derivatives
+  hotpath_oracle.cpp   coulomb / exchange / eval_Fxc loops (liboracle.so, built by `make -C oracle`)
+
+Parity pins: see DESIGN.md section "Oracle".  XC values are "parity unpinned" upstream (libxc is an
+un-vendored, unversioned dependency of the reference and none of its tests holds an XC value).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_lib = None
+c_double_p = ctypes.POINTER(ctypes.c_double)
+c_int_p = ctypes.POINTER(ctypes.c_int)
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        _lib = ctypes.CDLL(LIB_PATH)
+        _lib.oracle_gaunt.restype = ctypes.c_double
+        _lib.oracle_gaunt.argtypes = [ctypes.c_int] * 6
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(c_double_p)
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_int_p)
+
+
+def _ptr_array(mats):
+    arr = (c_double_p * len(mats))()
+    for i, m in enumerate(mats):
+        arr[i] = _p(m)
+    return arr
+
+
+def gaunt(L, M, l, m, lp, mp):
+    return lib().oracle_gaunt(L, M, l, m, lp, mp)
+
+
+def xc(func, rho, sigma=None, tau=None, thr=1e-12, polarized=False):
+    """libxc-style arrays (spin fastest).  Returns exc, vrho, vsigma, vtau for ONE functional id."""
+    rho = np.ascontiguousarray(rho, dtype=np.float64)
+    n = rho.size // (2 if polarized else 1)
+    exc = np.zeros(n)
+    vrho = np.zeros_like(rho)
+    vs = np.zeros(n * (3 if polarized else 1))
+    vt = np.zeros_like(rho)
+    sg = None if sigma is None else np.ascontiguousarray(sigma, dtype=np.float64)
+    ta = None if tau is None else np.ascontiguousarray(tau, dtype=np.float64)
+    fn = lib().oracle_xc_pol if polarized else lib().oracle_xc_unpol
+    fn(int(func), int(n), ctypes.c_double(thr), _p(rho), _p(sg) if sg is not None else None,
+       _p(ta) if ta is not None else None, _p(exc), _p(vrho), _p(vs), _p(vt))
+    return exc, vrho, vs, vt
+
+
+class SadatomOracle:
+    """Holds the tables of one basis (from fem_oracle.RadialSetup or from the product's host library)
+    and evaluates the three operators with the reference's algorithm on the CPU."""
+
+    def __init__(self, first, last, r, wrad, bf, df, lmax):
+        self.first = np.ascontiguousarray(first, dtype=np.int32)
+        self.last = np.ascontiguousarray(last, dtype=np.int32)
+        self.nel = len(self.first)
+        self.nrad = int(self.last[-1]) + 1
+        self.r = np.ascontiguousarray(np.concatenate(r))
+        self.wrad = np.ascontiguousarray(np.concatenate(wrad))
+        self.nq = len(r[0])
+        self.bf = np.concatenate([np.asfortranarray(b).reshape(-1, order="F") for b in bf])
+        self.df = np.concatenate([np.asfortranarray(b).reshape(-1, order="F") for b in df])
+        self.lmax = lmax
+        self.dL = self.dm1L = self.tei = self.ktei = None
+
+    def set_tei(self, dL, dm1L, tei, ktei=None):
+        """lists indexed [L*nel+iel] of Fortran-ordered arrays"""
+        self.dL = [np.asfortranarray(a) for a in dL]
+        self.dm1L = [np.asfortranarray(a) for a in dm1L]
+        self.tei = [np.asfortranarray(a) for a in tei]
+        self.ktei = None if ktei is None else [np.asfortranarray(a) for a in ktei]
+
+    def coulomb(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        J = np.zeros_like(P, order="F")
+        n = self.nel
+        lib().oracle_sadatom_coulomb(n, _ip(self.first), _ip(self.last), _ptr_array(self.dL[:n]), _ptr_array(self.dm1L[:n]),
+                                     _ptr_array(self.tei[:n]), _p(P), self.nrad, _p(J))
+        return J
+
+    def exchange(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        K = np.zeros_like(P, order="F")
+        lib().oracle_sadatom_exchange(self.lmax, self.nel, _ip(self.first), _ip(self.last), _ptr_array(self.dL),
+                                      _ptr_array(self.dm1L), _ptr_array(self.ktei), _p(P), self.nrad, _p(K))
+        return K
+
+    def eval_fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True):
+        P = np.asfortranarray(P, dtype=np.float64)
+        H = np.zeros_like(P, order="F")
+        exc, nel = ctypes.c_double(), ctypes.c_double()
+        nspin = 1 if Pb is None else 2
+        Hb = None
+        if Pb is not None:
+            Pb = np.asfortranarray(Pb, dtype=np.float64)
+            Hb = np.zeros_like(P, order="F")
+        rc = lib().oracle_sadatom_eval_fxc(self.nel, self.nq, _ip(self.first), _ip(self.last), _p(self.r), _p(self.wrad),
+                                           _p(self.bf), _p(self.df), int(x_func), int(c_func), nspin, _p(P),
+                                           _p(Pb) if Pb is not None else None, self.nrad, int(P.shape[2]),
+                                           ctypes.c_double(thr), _p(H), _p(Hb) if Hb is not None else None,
+                                           int(bool(beta)), ctypes.byref(exc), ctypes.byref(nel))
+        if rc != 0:
+            raise RuntimeError("oracle: functional not restated")
+        if Pb is None:
+            return H, exc.value, nel.value
+        return H, Hb, exc.value, nel.value
+
+
+def sadatom_from_setup(rs, lmax, nL=1, exchange=False):
+    """Build a SadatomOracle (tables + stored integrals) from fem_oracle.RadialSetup."""
+    from . import fem_oracle
+    o = SadatomOracle(rs.first, rs.last, [rs.r(e) for e in range(rs.nel)], [rs.wrad(e) for e in range(rs.nel)],
+                      [rs.get_bf(e) for e in range(rs.nel)], [rs.get_df(e) for e in range(rs.nel)], lmax)
+    dL, dm1L, tei, ktei = [], [], [], []
+    for L in range(nL):
+        for e in range(rs.nel):
+            dL.append(rs.radial_integral(L, e))
+            dm1L.append(rs.radial_integral(-L - 1, e))
+            t = rs.twoe_integral(L, e)
+            tei.append(t)
+            if exchange:
+                n = rs.basis(e).nbf
+                ktei.append(fem_oracle.exchange_tei(t, n, n, n, n))
+    o.set_tei(dL, dm1L, tei, ktei if exchange else None)
+    return o
