@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py -- SCF Fock builds per second (J + K + Vxc, FP64) on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (the CPU arm: oracle port on the host cores)
+
+A *step* is one pass of the hot path over one batch of synthetic densities on one basis:
+`batch` independent Fock builds (coulomb + eval_Fxc; exchange is not called for a pure functional,
+sadatom/solver.cpp:822) of BASELINE.json configs[1] (Kr, PBE, 20 LIP-15 elements, lmax 3), the
+situation of the sadatom configuration search / Z sweep where many trial densities share one basis.
+`value` = builds/s with the densities already resident in HBM (element-band layout);
+`e2e`   = the same through the reference-facing dense C-ABI calls with HOST matrices in and out
+          (pack + H2D + kernels + D2H + scatter inside the timed region).
+Ranks (N>1) each process their own batch: the path shards by atom / trial configuration with no
+data-path collective ("weak" scaling); only the timing is reduced (max over ranks).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: dict(Z, primbas, nnodes, nelem, taylor, lmax, method, nspin)
+    "kr_pbe_cfg2": dict(Z=36, primbas=4, nnodes=15, nelem=20, taylor=-1, lmax=3, x=101, c=130, nspin=1,
+                        desc="gensap --Z Kr --nelem 20 --nnodes 15 --primbas 4 --method gga_x_pbe-gga_c_pbe (configs[1])"),
+    "rn_r2scan_cfg3": dict(Z=86, primbas=5, nnodes=15, nelem=40, taylor=20, lmax=3, x=497, c=498, nspin=2,
+                           desc="gensap --Z Rn --nelem 40 --nnodes 15 --primbas 5 --method mgga_x_r2scan-mgga_c_r2scan (configs[2])"),
+    "ne_pbe_small": dict(Z=10, primbas=4, nnodes=15, nelem=5, taylor=-1, lmax=2, x=101, c=130, nspin=1,
+                         desc="small smoke case"),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.samples, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_basis(w, device=0):
+    import helfem_b200 as hb
+    b = hb.SadatomBasis(Z=w["Z"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"], taylor_order=w["taylor"],
+                        lmax=w["lmax"], device=device)
+    b.compute_tei(1, False)  # a pure functional only ever reads L = 0 (sadatom/basis.cpp:306)
+    return b
+
+
+def make_densities(b, w):
+    """Aufbau density cube(s) of core-Hamiltonian orbitals, divided by 4 pi as FockBuild passes them
+    (sadatom/solver.cpp:784,804)."""
+    from util import sadatom_density
+    S, T, Tl, V = b.overlap(), b.kinetic(), b.kinetic_l(), b.nuclear()
+    if w["nspin"] == 1:
+        return [sadatom_density(S, T, Tl, V, w["Z"], w["lmax"]) / (4 * np.pi)]
+    return [sadatom_density(S, T, Tl, V, w["Z"], w["lmax"], spin=s) / (4 * np.pi) for s in ("a", "b")]
+
+
+def algorithmic(b, w):
+    """Algorithmic bytes / flops of ONE Fock build (restated in DESIGN.md)."""
+    nsl, nspin = w["lmax"] + 1, w["nspin"]
+    fam = {1: 1, 101: 2, 497: 3}[w["x"]]
+    c = {1: 4, 2: 6, 3: 14}[fam]
+    npe = (b.last - b.first + 1).astype(np.int64)
+    np2 = b.np_max ** 2
+    grid_flops = int(c * np.sum(npe ** 2) * b.nq * nspin)
+    n_tab = 1 if fam == 1 else 2
+    # batched: per build the P band comes in and the H band goes out; tables are shared (L2-resident)
+    grid_bytes_batched = int(2 * nspin * nsl * b.nel * np2 * 8)
+    grid_bytes_single = grid_bytes_batched + int(n_tab * np.sum(npe) * b.nq * 8)
+    j_flops = int(2 * np.sum(npe ** 4))
+    j_bytes_single = int(np.sum(npe ** 4) * 8 + (nspin * nsl + 1) * b.nel * np2 * 8)
+    j_bytes_batched = int((nspin * nsl + 1) * b.nel * np2 * 8)
+    return dict(grid_flops=grid_flops, grid_bytes_batched=grid_bytes_batched, grid_bytes_single=grid_bytes_single,
+                j_flops=j_flops, j_bytes_single=j_bytes_single, j_bytes_batched=j_bytes_batched)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (oracle/hotpath_oracle.cpp, OpenMP) fed with the same tables
+# ------------------------------------------------------------------------------------------------
+def oracle_from_basis(b):
+    import oracle
+    tabs = [b.tables(e) for e in range(b.nel)]
+    o = oracle.SadatomOracle(b.first, b.last, [t[0] for t in tabs], [t[1] for t in tabs], [t[2] for t in tabs],
+                             [t[3] for t in tabs], b.lmax)
+    tei = [b.tei(0, e) for e in range(b.nel)]
+    o.set_tei([t[0] for t in tei], [t[1] for t in tei], [t[2] for t in tei])
+    return o
+
+
+def cpu_builds(o, w, dens, nbuilds):
+    """nbuilds Fock builds on the host cores; returns seconds."""
+    t0 = time.perf_counter()
+    for i in range(nbuilds):
+        s = 1.0 + 0.01 * i
+        if w["nspin"] == 1:
+            P = dens[0] * s
+            o.coulomb(np.asfortranarray(P.sum(axis=2)))
+            o.eval_fxc(w["x"], w["c"], P)
+        else:
+            Pa, Pb = dens[0] * s, dens[1] * s
+            o.coulomb(np.asfortranarray((Pa + Pb).sum(axis=2)))
+            o.eval_fxc(w["x"], w["c"], Pa, Pb)
+    return time.perf_counter() - t0
+
+
+def run_reference(args, w, rank):
+    if rank != 0:
+        return
+    import oracle
+    b = make_basis_host_only(w)
+    o = oracle_from_basis(b)
+    dens = make_densities(b, w)
+    nthreads = oracle.lib().oracle_num_threads()
+    one = cpu_builds(o, w, dens, 1)
+    per_step = max(1, min(args.batch, int(2.0 / max(one, 1e-6))))  # ~2 s of CPU work per step
+    for _ in range(args.warmup):
+        cpu_builds(o, w, dens, max(1, per_step // 4))
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_builds(o, w, dens, per_step)
+    value = per_step * args.steps / t
+    line = {"impl": "reference", "metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "builds_per_step": per_step,
+                       "note": "CPU restatement of the reference loops (oracle/hotpath_oracle.cpp, -O3 -fopenmp); the "
+                               "reference itself cannot be compiled here (no Armadillo/GSL/libxc/HDF5/gfortran)"},
+            "cpu_baseline": {"value": value, "unit": "builds/s", "cores": nthreads, "kind": "port",
+                             "sample": "%d builds per step x %d steps" % (per_step, args.steps)},
+            "e2e": {"value": value, "unit": "builds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def make_basis_host_only(w):
+    """Tables + stored integrals from the host library only (no device context is created)."""
+    return make_basis(w)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_gpu(args, w, rank, world, local_rank):
+    import torch
+    import helfem_b200 as hb
+    if not torch.cuda.is_available() or hb.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: helfem_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    b = make_basis(w, device=local_rank)
+    dens = make_densities(b, w)
+    nsl, nspin, nb = w["lmax"] + 1, w["nspin"], args.batch
+    blk = b.nel * b.np_max ** 2
+    base = np.zeros((nspin, nsl, blk))
+    for s in range(nspin):
+        for l in range(nsl):
+            base[s, l] = b.pack_band(dens[s][:, :, l])
+    # batch of distinct trial densities: rank- and build-dependent rescaling (XC is nonlinear in P)
+    rng = np.random.RandomState(20261104 + rank)
+    scales = 1.0 + 0.05 * rng.uniform(-1, 1, nb)
+    dbase = torch.from_numpy(base).cuda()
+    dP = (torch.from_numpy(scales).cuda().view(nb, 1, 1, 1) * dbase.unsqueeze(0)).contiguous()
+    dJ = torch.zeros((nb, blk), dtype=torch.float64, device="cuda")
+    dH = torch.zeros((nb, nspin, nsl, blk), dtype=torch.float64, device="cuda")
+    dS = torch.zeros((nb, 4), dtype=torch.float64, device="cuda")
+    stream = torch.cuda.current_stream()
+    sh = stream.cuda_stream
+    x, c, thr = w["x"], w["c"], 1e-12
+
+    def step(J=True, H=True):
+        b.fock_batch(nb, x, c, nspin, nsl, thr, dP.data_ptr(), dJ.data_ptr() if J else 0, dH.data_ptr() if H else 0,
+                     dS.data_ptr() if H else 0, sh)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for e0, e1 in ev:
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+        torch.cuda.synchronize()
+        return sum(e0.elapsed_time(e1) for e0, e1 in ev)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ms = timed(step, args.steps)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = nb * world * args.steps / (ms * 1e-3)
+
+    # ---- per-kernel timing (rank 0 reports): the grid/XC kernel and the Coulomb kernels on their own ----
+    ms_grid = timed(lambda: step(J=False), args.steps) / args.steps
+    ms_j = timed(lambda: step(H=False), args.steps) / args.steps
+
+    # ---- end to end through the dense host-matrix C ABI (the call the reference's drivers make) ----
+    ne2e = min(nb, args.e2e_builds)
+    Ptot = [np.asfortranarray(sum(d.sum(axis=2) for d in dens) * s) for s in scales[:ne2e]]
+    Pcubes = [[np.asfortranarray(d * s) for d in dens] for s in scales[:ne2e]]
+
+    def e2e_pass():
+        for i in range(ne2e):
+            b.coulomb(Ptot[i])
+            if nspin == 1:
+                b.eval_fxc(x, c, Pcubes[i][0])
+            else:
+                b.eval_fxc(x, c, Pcubes[i][0], Pcubes[i][1])
+
+    e2e_pass()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_pass()
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    e2e_value = ne2e * world * args.steps / t_e2e
+    h2d = ne2e * (nspin * nsl + 1) * blk * 8
+    d2h = ne2e * ((nspin * nsl + 1) * blk * 8 + 32)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    alg = algorithmic(b, w)
+    hbm_peak, peak_src = peaks()
+    # dominant kernel of the batched step
+    if ms_grid >= ms_j:
+        kname, kms, kbytes = "sad_grid_kernel", ms_grid, alg["grid_bytes_batched"] * nb
+        kflops = alg["grid_flops"] * nb
+    else:
+        kname, kms, kbytes = "sad_coulomb_kernel", ms_j, alg["j_bytes_batched"] * nb
+        kflops = alg["j_flops"] * nb
+    achieved = kbytes / (kms * 1e-3) / 1e9
+    roofline = {"kernel": kname, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": kbytes, "ms_per_launch": kms,
+                "fp64_tflops_algorithmic": kflops / (kms * 1e-3) / 1e12,
+                "ms_grid_kernel": ms_grid, "ms_coulomb_kernels": ms_j}
+    # CPU baseline: the oracle port on this box's host cores, bounded sample
+    import oracle
+    o = oracle_from_basis(b)
+    one = cpu_builds(o, w, dens, 1)
+    nsample = max(2, min(200, int(10.0 / max(one, 1e-6))))
+    tc = cpu_builds(o, w, dens, nsample)
+    cpu = {"value": nsample / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
+           "sample": "%d Fock builds (coulomb + eval_Fxc) of the same workload" % nsample}
+    line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "builds_per_step_per_gpu": nb,
+                       "operators": "coulomb + eval_Fxc(%s) %s" % ("PBE" if x == 101 else "r2SCAN" if x == 497 else "LDA",
+                                                                   "restricted" if nspin == 1 else "unrestricted"),
+                       "l2": "inputs larger than L2: P+H+J bands = %.0f MB per step" % ((dP.numel() + dH.numel() + dJ.numel()) * 8 / 1e6),
+                       "partition": "independent builds per rank, no data-path collective"},
+            "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": "builds/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "builds_per_step": ne2e, "api": "hfb200_sadatom_coulomb + hfb200_sadatom_eval_fxc, dense host matrices"},
+            "gpu_launches": int(args.steps * 4), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="kr_pbe_cfg2", choices=list(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
+    ap.add_argument("--e2e-builds", type=int, default=64)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w, rank)
+    else:
+        run_gpu(args, w, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
