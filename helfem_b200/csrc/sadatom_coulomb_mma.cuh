@@ -1,0 +1,170 @@
+// sm_100a kernels for TwoDBasis::coulomb of the spherically averaged atom (sadatom/basis.cpp:296-358,
+// L = 0 only, :306) on the FP64 tensor pipe.
+//
+// Algebra.  For element e the reference forms  Jsub = Lfac * prim_tei_e * vec(Psub)  with
+// prim_tei(j*N+i, l*N+k) = (ij|kl), plus the disjoint terms  dL_e * sum_{j>e} jbig_j  and
+// dm1L_e * sum_{j<e} jsmall_j  where  jsmall/jbig = Lfac tr(dL/dm1L * Psub)  (:314-352).  (ij|kl) is
+// symmetric in i<->j and in k<->l, so the product only sees the symmetric part of Psub and only the
+// i<=j rows are distinct: the integrals are stored TRIANGLE-PACKED, Tc[(i<=j),(k<=l)] (ntri = N(N+1)/2
+// per side, 3.5x fewer bytes than the reference's N^2 x N^2 block) against the folded density
+// pc[(k<=l)] = P_kl + P_lk (k<l), P_kk.  This is exact for ANY input matrix, symmetric or not.
+//
+//   sad_jpack_kernel   (element, build): pc and the two traces
+//   sad_jmma_kernel    (element, 32-row tile, build chunk): J_c = Tc_e pc as DMMA.8x8x4 with the A
+//                      operand pre-swizzled on the host into fragment order (one coalesced 256 B load
+//                      per warp per fragment, straight from L2/HBM into registers), then the prefix /
+//                      suffix trace sums, the disjoint terms and the scatter to the element band.
+//                      SPLITK=false: warps split the builds (batched GEMM, FP64-pipe bound);
+//                      SPLITK=true : warps split K and reduce through shared memory (one or a few
+//                      builds: a GEMV that streams every stored integral once, HBM bound).
+#pragma once
+#include <cuda_runtime.h>
+#include "sadatom_grid_mma.cuh"
+
+namespace hfb {
+
+struct SadJParams {
+  const double* teiF;   // [nel][MT][KS][32]  fragment-ordered Tc: lane -> Tc[8 mt + lane/4][4 ks + lane%4]
+  const double* dLc;    // [nel][MP]  triangle-packed disjoint_L   (L = 0)
+  const double* dm1Lc;  // [nel][MP]
+  const int2* tri;      // [ntri] (i, j), i <= j, m = i + j(j+1)/2
+  int nel, np_max, ntri, MT, KS, nslices, nspin, nb;
+  const double* P;      // [nb][nspin][nslices][nel][np2]
+  double* pc;           // [nb][nel][4 KS]   scratch
+  double* traces;       // [nb][nel][2]      scratch: jsmall, jbig
+  double* J;            // [nb][nel][np2]
+};
+
+// grid (nel, nb), 128 threads
+__global__ void __launch_bounds__(128) sad_jpack_kernel(SadJParams prm) {
+  __shared__ double red[8];
+  const int el = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+  const int np = prm.np_max, np2 = np * np, KP = 4 * prm.KS, MP = 8 * prm.MT;
+  const size_t sstride = (size_t)prm.nel * np2;
+  const double* gP = prm.P + ((size_t)b * prm.nspin * prm.nslices * prm.nel + el) * np2;
+  double ts = 0.0, tb = 0.0;
+  for (int m = tid; m < KP; m += blockDim.x) {
+    double v = 0.0;
+    if (m < prm.ntri) {
+      const int2 ij = prm.tri[m];
+      const int a = ij.x + ij.y * np, c = ij.y + ij.x * np;
+      for (int sl = 0; sl < prm.nspin * prm.nslices; sl++) {
+        v += gP[(size_t)sl * sstride + a];
+        if (ij.x != ij.y) v += gP[(size_t)sl * sstride + c];
+      }
+      ts = fma(prm.dLc[(size_t)el * MP + m], v, ts);
+      tb = fma(prm.dm1Lc[(size_t)el * MP + m], v, tb);
+    }
+    prm.pc[((size_t)b * prm.nel + el) * KP + m] = v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ts += __shfl_xor_sync(0xffffffffu, ts, o);
+    tb += __shfl_xor_sync(0xffffffffu, tb, o);
+  }
+  if ((tid & 31) == 0) { red[tid >> 5] = ts; red[4 + (tid >> 5)] = tb; }
+  __syncthreads();
+  if (tid == 0) {
+    const double Lfac = 4.0 * HFB_PI;
+    prm.traces[((size_t)b * prm.nel + el) * 2 + 0] = Lfac * ((red[0] + red[1]) + (red[2] + red[3]));
+    prm.traces[((size_t)b * prm.nel + el) * 2 + 1] = Lfac * ((red[4] + red[5]) + (red[6] + red[7]));
+  }
+}
+
+// grid (nel * ceil(MT/4), nchunks), 256 threads.  NTW: 8-build tiles per warp pass.
+template <bool SPLITK, int NTW>
+__global__ void __launch_bounds__(256) sad_jmma_kernel(SadJParams prm) {
+  __shared__ double sred[SPLITK ? 8 * 4 * NTW * 64 : 1];
+  const int rts = (prm.MT + 3) >> 2;
+  const int el = blockIdx.x / rts, rt = blockIdx.x % rts;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gid = lane >> 2, t4 = lane & 3;
+  const int KS = prm.KS, KP = 4 * KS, MP = 8 * prm.MT, np = prm.np_max, np2 = np * np;
+  const int mt0 = 4 * rt, nmt = min(4, prm.MT - mt0);
+  // builds of this CTA / warp
+  const int chunk = SPLITK ? 8 * NTW : 8 * 8 * NTW;
+  const int bw0 = blockIdx.y * chunk + (SPLITK ? 0 : warp * 8 * NTW);
+  if (!SPLITK && bw0 >= prm.nb) return;
+
+  double acc[4][NTW][2];
+#pragma unroll
+  for (int m = 0; m < 4; m++)
+#pragma unroll
+    for (int n = 0; n < NTW; n++) { acc[m][n][0] = 0.0; acc[m][n][1] = 0.0; }
+
+  const double* A = prm.teiF + (((size_t)el * prm.MT + mt0) * KS) * 32 + lane;
+  // B operand: Bop[k][n] = pc[b = bw0 + 8 n + gid][el][4 ks + t4]
+  const double* Bp[NTW];
+  bool bok[NTW];
+#pragma unroll
+  for (int n = 0; n < NTW; n++) {
+    const int bb = bw0 + 8 * n + gid;
+    bok[n] = bb < prm.nb;
+    Bp[n] = prm.pc + ((size_t)(bok[n] ? bb : 0) * prm.nel + el) * KP + t4;
+  }
+  const int ks0 = SPLITK ? warp : 0, kstep = SPLITK ? 8 : 1;
+#pragma unroll 2
+  for (int ks = ks0; ks < KS; ks += kstep) {
+    double a[4], bf[NTW];
+#pragma unroll
+    for (int m = 0; m < 4; m++) a[m] = (m < nmt) ? __ldg(A + ((size_t)m * KS + ks) * 32) : 0.0;
+#pragma unroll
+    for (int n = 0; n < NTW; n++) bf[n] = bok[n] ? Bp[n][4 * ks] : 0.0;
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) dmma(acc[m][n][0], acc[m][n][1], a[m], bf[n]);
+  }
+  if (SPLITK) {
+    // cross-warp reduction in a fixed order (deterministic)
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) {
+        sred[((warp * 4 + m) * NTW + n) * 64 + lane] = acc[m][n][0];
+        sred[((warp * 4 + m) * NTW + n) * 64 + 32 + lane] = acc[m][n][1];
+      }
+    __syncthreads();
+    if (warp != 0) return;
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) {
+        double s0 = 0.0, s1 = 0.0;
+        for (int w = 0; w < 8; w++) {
+          s0 += sred[((w * 4 + m) * NTW + n) * 64 + lane];
+          s1 += sred[((w * 4 + m) * NTW + n) * 64 + 32 + lane];
+        }
+        acc[m][n][0] = s0;
+        acc[m][n][1] = s1;
+      }
+  }
+  // epilogue: thread holds Jc[m = 8 (mt0+mm) + gid][b = bw0 + 8 n + 2 t4 + c]
+  const double Lfac = 4.0 * HFB_PI;
+#pragma unroll
+  for (int n = 0; n < NTW; n++)
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      const int bb = bw0 + 8 * n + 2 * t4 + c;
+      if (bb >= prm.nb) continue;
+      const double* tr = prm.traces + (size_t)bb * prm.nel * 2;
+      double below = 0.0, above = 0.0;  // sum of jsmall over j < el, of jbig over j > el (reference order)
+      for (int j = 0; j < el; j++) below += tr[2 * j];
+      for (int j = el + 1; j < prm.nel; j++) above += tr[2 * j + 1];
+      double* gJ = prm.J + ((size_t)bb * prm.nel + el) * np2;
+#pragma unroll
+      for (int mm = 0; mm < 4; mm++) {
+        const int m = 8 * (mt0 + mm) + gid;
+        if (mm < nmt && m < prm.ntri) {
+          double v = Lfac * acc[mm][n][c];
+          v = fma(above, prm.dLc[(size_t)el * MP + m], v);
+          v = fma(below, prm.dm1Lc[(size_t)el * MP + m], v);
+          const int2 ij = prm.tri[m];
+          gJ[ij.x + ij.y * np] = v;
+          gJ[ij.y + ij.x * np] = v;
+        }
+      }
+    }
+}
+
+}  // namespace hfb
