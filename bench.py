@@ -124,8 +124,10 @@ def algorithmic(b, w):
     # batched: per build the P band comes in and the H band goes out; tables are shared (L2-resident)
     grid_bytes_batched = int(2 * nspin * nsl * b.nel * np2 * 8)
     grid_bytes_single = grid_bytes_batched + int(n_tab * np.sum(npe) * b.nq * 8)
-    j_flops = int(2 * np.sum(npe ** 4))
-    j_bytes_single = int(np.sum(npe ** 4) * 8 + (nspin * nsl + 1) * b.nel * np2 * 8)
+    # Coulomb on triangle-packed integrals: (ij|kl) = (ji|kl) = (ij|lk), so ntri = np(np+1)/2 per side
+    ntri = npe * (npe + 1) // 2
+    j_flops = int(2 * np.sum(ntri ** 2))
+    j_bytes_single = int(np.sum(ntri ** 2) * 8 + (nspin * nsl + 1) * b.nel * np2 * 8)
     j_bytes_batched = int((nspin * nsl + 1) * b.nel * np2 * 8)
     return dict(grid_flops=grid_flops, grid_bytes_batched=grid_bytes_batched, grid_bytes_single=grid_bytes_single,
                 j_flops=j_flops, j_bytes_single=j_bytes_single, j_bytes_batched=j_bytes_batched)
@@ -266,33 +268,63 @@ def run_gpu(args, w, rank, world, local_rank):
     ms_grid = timed(lambda: step(J=False), args.steps) / args.steps
     ms_j = timed(lambda: step(H=False), args.steps) / args.steps
 
-    # ---- end to end through the dense host-matrix C ABI (the call the reference's drivers make) ----
-    ne2e = min(nb, args.e2e_builds)
-    Ptot = [np.asfortranarray(sum(d.sum(axis=2) for d in dens) * s) for s in scales[:ne2e]]
-    Pcubes = [[np.asfortranarray(d * s) for d in dens] for s in scales[:ne2e]]
+    # ---- end to end: the same batch through the C ABI with HOST buffers (pinned element bands in and out,
+    # H2D + kernels + D2H inside the timed region) ----
+    hP = torch.empty(dP.shape, dtype=torch.float64).pin_memory()
+    hP.copy_(dP.cpu())
+    hJ = torch.empty(dJ.shape, dtype=torch.float64).pin_memory()
+    hH = torch.empty(dH.shape, dtype=torch.float64).pin_memory()
+    hS = torch.empty(dS.shape, dtype=torch.float64).pin_memory()
+    hPn, hJn, hHn, hSn = hP.numpy(), hJ.numpy(), hH.numpy(), hS.numpy()
 
     def e2e_pass():
-        for i in range(ne2e):
-            b.coulomb(Ptot[i])
-            if nspin == 1:
-                b.eval_fxc(x, c, Pcubes[i][0])
-            else:
-                b.eval_fxc(x, c, Pcubes[i][0], Pcubes[i][1])
+        b.fock_host(nb, x, c, nspin, nsl, thr, hPn, hJn, hHn, hSn)
 
     e2e_pass()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_pass()
-    torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
     if dist is not None:
         t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_e2e = float(t.item())
-    e2e_value = ne2e * world * args.steps / t_e2e
-    h2d = ne2e * (nspin * nsl + 1) * blk * 8
-    d2h = ne2e * ((nspin * nsl + 1) * blk * 8 + 32)
+    e2e_value = nb * world * args.steps / t_e2e
+    h2d = hP.numel() * 8
+    d2h = (hJ.numel() + hH.numel() + hS.numel()) * 8
+    # cross-check: host path reproduces the device-resident results bit for bit
+    if not (torch.equal(hJ, dJ.cpu()) and torch.equal(hH, dH.cpu())):
+        raise RuntimeError("host-buffer path and device-resident path disagree")
+
+    # ---- latency of ONE build through the dense reference-facing calls (coulomb + eval_Fxc, dense host matrices) ----
+    import helfem_b200 as hb_
+    L = hb_.lib()
+    ctx = b.context()
+    nrad = b.nbf
+    Pd = [np.asfortranarray(d) for d in dens]
+    Ptot = np.asfortranarray(sum(d.sum(axis=2) for d in dens))
+    Jd = np.zeros((nrad, nrad), order="F")
+    Hd = [np.zeros((nrad, nrad, nsl), order="F") for _ in range(nspin)]
+    exc_, nel_ = ctypes.c_double(), ctypes.c_double()
+    dpp = ctypes.POINTER(ctypes.c_double)
+    ptr = lambda a: a.ctypes.data_as(dpp)
+
+    def dense_build():
+        rc = L.hfb200_sadatom_coulomb(ctx, ptr(Ptot), nrad, ptr(Jd), nrad)
+        rc |= L.hfb200_sadatom_eval_fxc(ctx, x, c, nspin, ptr(Pd[0]), ptr(Pd[1]) if nspin == 2 else None, nrad, nsl,
+                                        ctypes.c_double(thr), ptr(Hd[0]), ptr(Hd[1]) if nspin == 2 else None, nrad, 1,
+                                        ctypes.byref(exc_), ctypes.byref(nel_))
+        if rc:
+            raise RuntimeError("dense C-ABI call failed")
+
+    for _ in range(3):
+        dense_build()
+    t0 = time.perf_counter()
+    ndense = 50
+    for _ in range(ndense):
+        dense_build()
+    dense_us = (time.perf_counter() - t0) / ndense * 1e6
 
     if rank != 0:
         if dist is not None:
@@ -331,7 +363,9 @@ def run_gpu(args, w, rank, world, local_rank):
                        "partition": "independent builds per rank, no data-path collective"},
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "builds/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "builds_per_step": ne2e, "api": "hfb200_sadatom_coulomb + hfb200_sadatom_eval_fxc, dense host matrices"},
+                    "builds_per_step": nb, "api": "hfb200_sadatom_fock_host: pinned host element bands in, J/H bands + scalars out",
+                    "dense_single_build_us": dense_us,
+                    "dense_api": "hfb200_sadatom_coulomb + hfb200_sadatom_eval_fxc on dense host matrices, one build per call"},
             "gpu_launches": int(args.steps * 4), "clocks": clocks}
     print(json.dumps(line), flush=True)
     if dist is not None:
@@ -346,7 +380,6 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="kr_pbe_cfg2", choices=list(WORKLOADS))
     ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
-    ap.add_argument("--e2e-builds", type=int, default=64)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

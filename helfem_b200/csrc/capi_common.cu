@@ -43,7 +43,8 @@ int hfb200_device_count(void) {
 void hfb200_destroy(hfb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  double* ptrs[] = {c->dBt, c->ddBt, c->dR, c->dW, c->dDisL, c->dDisM1L, c->dTei, c->dKtei, c->dCpl};
+  double* ptrs[] = {c->dBt, c->ddBt, c->dR, c->dW, c->dDisL, c->dDisM1L, c->dTeiF, c->dLc, c->dm1Lc, c->dKtei, c->dCpl};
+  if (c->dTri) cudaFree(c->dTri);
   int* iptrs[] = {c->dFirst, c->dNpe, c->dElemOf};
   for (int* p : iptrs)
     if (p) cudaFree(p);

@@ -1,17 +1,20 @@
-// C ABI, spherically averaged atom: context creation, integral upload, and the three
-// operators (coulomb / exchange / eval_Fxc) in dense-host and batched-device form.
+// C ABI, spherically averaged atom: context creation, integral upload, and the operators
+// coulomb / eval_Fxc in dense-host, band-host and batched-device form (exchange lives in
+// capi_sadatom_exchange.cu).
 #include <cstring>
 #include "../../include/helfem_b200.h"
 #include "context.h"
-#include "sadatom_kernels.cuh"
+#include "sadatom_coulomb_mma.cuh"
+#include "sadatom_grid_mma.cuh"
 
 using namespace hfb;
 
 namespace {
 
-int upload(double** dst, const std::vector<double>& src) {
-  HFB_CUDA_OK(cudaMalloc(dst, src.size() * sizeof(double)));
-  HFB_CUDA_OK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(double), cudaMemcpyHostToDevice));
+template <class T>
+int upload(T** dst, const std::vector<T>& src) {
+  HFB_CUDA_OK(cudaMalloc(dst, src.size() * sizeof(T)));
+  HFB_CUDA_OK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
   return 0;
 }
 
@@ -23,35 +26,60 @@ bool valid_pair(int x_func, int c_func, int* fam) {
   return *fam != 0;
 }
 
-template <int FAM, int NSPIN>
-int launch_grid_rpl(const SadGridParams& prm, int nb, size_t smem, cudaStream_t st) {
-  dim3 grid(prm.nel, nb);
-  if (prm.np_max <= 16) {
-    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sad_grid_kernel<FAM, NSPIN, 4><<<grid, 256, smem, st>>>(prm);
-  } else if (prm.np_max <= 32) {
-    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sad_grid_kernel<FAM, NSPIN, 8><<<grid, 256, smem, st>>>(prm);
-  } else {
-    HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_kernel<FAM, NSPIN, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sad_grid_kernel<FAM, NSPIN, 16><<<grid, 256, smem, st>>>(prm);
-  }
+template <int FAM, int NSPIN, int NT>
+int launch_grid_nt(const SadGridParams& prm, int nwarps, size_t smem, cudaStream_t st) {
+  dim3 grid(prm.nel, (prm.nb + nwarps - 1) / nwarps);
+  HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_mma_kernel<FAM, NSPIN, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sad_grid_mma_kernel<FAM, NSPIN, NT><<<grid, 32 * nwarps, smem, st>>>(prm);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
-int launch_grid(int fam, int nspin, const SadGridParams& prm, int nb, cudaStream_t st) {
-  const size_t smem = sad_grid_smem_bytes(fam, nspin, prm.np_max, prm.nq, prm.ldq);
-  if (smem > 227 * 1024) { set_error("element tables need %zu bytes of shared memory (>227 KB)", smem); return HFB200_EINVAL; }
-  if (prm.np_max > 64) { set_error("more than 64 functions per element are not supported"); return HFB200_EINVAL; }
-  if (nspin == 1) {
-    if (fam == xc::FAM_LDA) return launch_grid_rpl<xc::FAM_LDA, 1>(prm, nb, smem, st);
-    if (fam == xc::FAM_GGA) return launch_grid_rpl<xc::FAM_GGA, 1>(prm, nb, smem, st);
-    return launch_grid_rpl<xc::FAM_MGGA, 1>(prm, nb, smem, st);
+template <int FAM, int NSPIN>
+int launch_grid_fs(const SadGridParams& prm, int nwarps, size_t smem, cudaStream_t st) {
+  switch (prm.np_pad / 8) {
+    case 1: return launch_grid_nt<FAM, NSPIN, 1>(prm, nwarps, smem, st);
+    case 2: return launch_grid_nt<FAM, NSPIN, 2>(prm, nwarps, smem, st);
+    case 3: return launch_grid_nt<FAM, NSPIN, 3>(prm, nwarps, smem, st);
+    case 4: return launch_grid_nt<FAM, NSPIN, 4>(prm, nwarps, smem, st);
+    default:
+      set_error("more than 32 functions per element are not supported by the grid kernel");
+      return HFB200_EINVAL;
   }
-  if (fam == xc::FAM_LDA) return launch_grid_rpl<xc::FAM_LDA, 2>(prm, nb, smem, st);
-  if (fam == xc::FAM_GGA) return launch_grid_rpl<xc::FAM_GGA, 2>(prm, nb, smem, st);
-  return launch_grid_rpl<xc::FAM_MGGA, 2>(prm, nb, smem, st);
+}
+
+int launch_grid(int fam, int nspin, const SadGridParams& prm, cudaStream_t st) {
+  // one warp per build; up to 8 builds share a CTA's staged tables
+  int nwarps = prm.nb < 8 ? prm.nb : 8;
+  size_t smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps);
+  while (smem > 227 * 1024 && nwarps > 1) {
+    nwarps >>= 1;
+    smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps);
+  }
+  if (smem > 227 * 1024) { set_error("element tables need %zu bytes of shared memory (>227 KB)", smem); return HFB200_EINVAL; }
+  if (nspin == 1) {
+    if (fam == xc::FAM_LDA) return launch_grid_fs<xc::FAM_LDA, 1>(prm, nwarps, smem, st);
+    if (fam == xc::FAM_GGA) return launch_grid_fs<xc::FAM_GGA, 1>(prm, nwarps, smem, st);
+    return launch_grid_fs<xc::FAM_MGGA, 1>(prm, nwarps, smem, st);
+  }
+  if (fam == xc::FAM_LDA) return launch_grid_fs<xc::FAM_LDA, 2>(prm, nwarps, smem, st);
+  if (fam == xc::FAM_GGA) return launch_grid_fs<xc::FAM_GGA, 2>(prm, nwarps, smem, st);
+  return launch_grid_fs<xc::FAM_MGGA, 2>(prm, nwarps, smem, st);
+}
+
+int launch_coulomb(const SadJParams& q, cudaStream_t st) {
+  sad_jpack_kernel<<<dim3(q.nel, q.nb), 128, 0, st>>>(q);
+  HFB_CUDA_OK(cudaGetLastError());
+  const int rts = (q.MT + 3) / 4;
+  if (q.nb <= 8) {
+    sad_jmma_kernel<true, 1><<<dim3(q.nel * rts, 1), 256, 0, st>>>(q);
+  } else if (q.nb <= 16) {
+    sad_jmma_kernel<true, 2><<<dim3(q.nel * rts, 1), 256, 0, st>>>(q);
+  } else {
+    sad_jmma_kernel<false, 2><<<dim3(q.nel * rts, (q.nb + 127) / 128), 256, 0, st>>>(q);
+  }
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
 }
 
 }  // namespace
@@ -79,7 +107,8 @@ int hfb200_sadatom_create(hfb200_ctx** out, int device, int lmax, int nel, int n
   c->lmax = lmax;
   c->nel = nel;
   c->nq = nq;
-  c->ldq = nq | 1;  // odd row stride: conflict-free 64-bit shared-memory columns
+  c->nq8 = (nq + 7) & ~7;
+  c->ldq = sad_grid_ldq(nq);  // = 4 (mod 16): conflict-free DMMA fragment loads (sadatom_grid_mma.cuh)
   c->first.assign(first, first + nel);
   c->last.assign(last, last + nel);
   c->np_max = 0;
@@ -89,8 +118,9 @@ int hfb200_sadatom_create(hfb200_ctx** out, int device, int lmax, int nel, int n
     if (np > c->np_max) c->np_max = np;
   }
   c->nrad = last[nel - 1] + 1;
-  // tables: host (nq x np_e) column-major per element -> device [el][i][ldq]
-  const int np = c->np_max, ldq = c->ldq;
+  c->np_pad = (c->np_max + 7) & ~7;
+  // tables: host (nq x np_e) column-major per element -> device [el][i][ldq], zero padded
+  const int np = c->np_pad, ldq = c->ldq;
   std::vector<double> B((size_t)nel * np * ldq, 0.0), dB((size_t)nel * np * ldq, 0.0);
   size_t off = 0;
   for (int e = 0; e < nel; e++) {
@@ -123,36 +153,72 @@ int hfb200_sadatom_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_
   }
   HFB_CUDA_OK(cudaSetDevice(c->device));
   const int nel = c->nel, np = c->np_max, np2 = np * np;
-  std::vector<double> dl((size_t)nL * nel * np2, 0.0), dm((size_t)nL * nel * np2, 0.0);
-  for (int L = 0; L < nL; L++)
-    for (int e = 0; e < nel; e++) {
-      const int npe = c->last[e] - c->first[e] + 1;
-      const double* a = disjoint_L[L * nel + e];
-      const double* bb = disjoint_m1L[L * nel + e];
-      for (int j = 0; j < npe; j++)
-        for (int i = 0; i < npe; i++) {
-          dl[((size_t)L * nel + e) * np2 + i + j * np] = a[i + j * npe];
-          dm[((size_t)L * nel + e) * np2 + i + j * np] = bb[i + j * npe];
-        }
-    }
-  for (double** p : {&c->dDisL, &c->dDisM1L, &c->dTei, &c->dKtei})
+  for (double** p : {&c->dDisL, &c->dDisM1L, &c->dTeiF, &c->dKtei, &c->dLc, &c->dm1Lc})
     if (*p) { cudaFree(*p); *p = nullptr; }
+  if (c->dTri) { cudaFree(c->dTri); c->dTri = nullptr; }
   int rc;
-  if ((rc = upload(&c->dDisL, dl)) || (rc = upload(&c->dDisM1L, dm))) return rc;
-  // in-element blocks, one (L, element) at a time through a padded staging buffer
-  const size_t blk = (size_t)np2 * np2;
-  HFB_CUDA_OK(cudaMalloc(&c->dTei, (size_t)nL * nel * blk * sizeof(double)));
-  if (prim_ktei) HFB_CUDA_OK(cudaMalloc(&c->dKtei, (size_t)nL * nel * blk * sizeof(double)));
-  std::vector<double> stage(blk);
-  for (int pass = 0; pass < (prim_ktei ? 2 : 1); pass++) {
-    const double* const* src = pass ? prim_ktei : prim_tei;
-    double* dst = pass ? c->dKtei : c->dTei;
+  // ---- disjoint factors, all L, zero padded to np_max (exchange path) ----
+  {
+    std::vector<double> dl((size_t)nL * nel * np2, 0.0), dm((size_t)nL * nel * np2, 0.0);
     for (int L = 0; L < nL; L++)
       for (int e = 0; e < nel; e++) {
         const int npe = c->last[e] - c->first[e] + 1;
-        const double* t = src[L * nel + e];
+        const double* a = disjoint_L[L * nel + e];
+        const double* bb = disjoint_m1L[L * nel + e];
+        for (int j = 0; j < npe; j++)
+          for (int i = 0; i < npe; i++) {
+            dl[((size_t)L * nel + e) * np2 + i + j * np] = a[i + j * npe];
+            dm[((size_t)L * nel + e) * np2 + i + j * np] = bb[i + j * npe];
+          }
+      }
+    if ((rc = upload(&c->dDisL, dl)) || (rc = upload(&c->dDisM1L, dm))) return rc;
+  }
+  // ---- Coulomb path (L = 0 only, sadatom/basis.cpp:306): triangle-packed, fragment-ordered ----
+  {
+    const int ntri = np * (np + 1) / 2;
+    const int MP = (ntri + 7) & ~7, KP = (ntri + 3) & ~3, MT = MP / 8, KS = KP / 4;
+    c->ntri = ntri; c->jMT = MT; c->jKS = KS;
+    std::vector<int2> tri(ntri);
+    for (int j = 0; j < np; j++)
+      for (int i = 0; i <= j; i++) tri[i + j * (j + 1) / 2] = make_int2(i, j);
+    std::vector<double> dlc((size_t)nel * MP, 0.0), dmc((size_t)nel * MP, 0.0);
+    std::vector<double> F((size_t)nel * MT * KS * 32, 0.0);
+    for (int e = 0; e < nel; e++) {
+      const int npe = c->last[e] - c->first[e] + 1;
+      const size_t n2 = (size_t)npe * npe;
+      const double* t = prim_tei[e];          // L = 0
+      const double* a = disjoint_L[e];
+      const double* bb = disjoint_m1L[e];
+      for (int m = 0; m < ntri; m++) {
+        const int i = tri[m].x, j = tri[m].y;
+        if (j >= npe) continue;
+        dlc[(size_t)e * MP + m] = a[i + j * npe];
+        dmc[(size_t)e * MP + m] = bb[i + j * npe];
+        for (int kk = 0; kk < ntri; kk++) {
+          const int k = tri[kk].x, l = tri[kk].y;
+          if (l >= npe) continue;
+          const double v = t[(size_t)(i + j * npe) + (size_t)(k + l * npe) * n2];
+          const int mt = m >> 3, ks = kk >> 2, lane = (m & 7) * 4 + (kk & 3);
+          F[(((size_t)e * MT + mt) * KS + ks) * 32 + lane] = v;
+        }
+      }
+    }
+    if ((rc = upload(&c->dTeiF, F)) || (rc = upload(&c->dLc, dlc)) || (rc = upload(&c->dm1Lc, dmc)) ||
+        (rc = upload(&c->dTri, tri)))
+      return rc;
+  }
+  // ---- K-ordered in-element blocks, all L, zero padded (exchange path) ----
+  if (prim_ktei) {
+    const size_t blk = (size_t)np2 * np2;
+    HFB_CUDA_OK(cudaMalloc(&c->dKtei, (size_t)nL * nel * blk * sizeof(double)));
+    std::vector<double> stage(blk);
+    for (int L = 0; L < nL; L++)
+      for (int e = 0; e < nel; e++) {
+        const int npe = c->last[e] - c->first[e] + 1;
+        const double* t = prim_ktei[L * nel + e];
+        double* dst = c->dKtei + ((size_t)L * nel + e) * blk;
         if (npe == np) {
-          HFB_CUDA_OK(cudaMemcpy(dst + ((size_t)L * nel + e) * blk, t, blk * sizeof(double), cudaMemcpyHostToDevice));
+          HFB_CUDA_OK(cudaMemcpy(dst, t, blk * sizeof(double), cudaMemcpyHostToDevice));
         } else {
           std::fill(stage.begin(), stage.end(), 0.0);
           const size_t n2 = (size_t)npe * npe;
@@ -162,7 +228,7 @@ int hfb200_sadatom_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_
               for (int rs = 0; rs < npe; rs++)
                 for (int rf = 0; rf < npe; rf++)
                   stage[(size_t)(rf + rs * np) + (size_t)(cf + cs * np) * np2] = t[(size_t)(rf + rs * npe) + (size_t)(cf + cs * npe) * n2];
-          HFB_CUDA_OK(cudaMemcpy(dst + ((size_t)L * nel + e) * blk, stage.data(), blk * sizeof(double), cudaMemcpyHostToDevice));
+          HFB_CUDA_OK(cudaMemcpy(dst, stage.data(), blk * sizeof(double), cudaMemcpyHostToDevice));
         }
       }
   }
@@ -181,11 +247,12 @@ int hfb200_sadatom_band_size(hfb200_ctx* c, int* nel, int* np_max) {
 int hfb200_sadatom_pack_band(hfb200_ctx* c, const double* M, int ld, double* band) {
   if (!c || !M || !band || ld < c->nrad) { set_error("pack_band: invalid argument"); return HFB200_EINVAL; }
   const int np = c->np_max, np2 = np * np;
-  memset(band, 0, sizeof(double) * (size_t)c->nel * np2);
   for (int e = 0; e < c->nel; e++) {
     const int f = c->first[e], npe = c->last[e] - f + 1;
+    double* blk = band + (size_t)e * np2;
+    if (npe < np) memset(blk, 0, sizeof(double) * np2);
     for (int j = 0; j < npe; j++)
-      memcpy(band + (size_t)e * np2 + (size_t)j * np, M + (size_t)f + (size_t)(f + j) * ld, sizeof(double) * npe);
+      memcpy(blk + (size_t)j * np, M + (size_t)f + (size_t)(f + j) * ld, sizeof(double) * npe);
   }
   return HFB200_OK;
 }
@@ -210,7 +277,6 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
   }
   HFB_CUDA_OK(cudaSetDevice(c->device));
   cudaStream_t st = (cudaStream_t)stream;
-  const int np2 = c->np_max * c->np_max;
   int rc;
   if (dH_band) {
     int fam = 0;
@@ -221,28 +287,26 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
     if ((rc = c->dPartial.reserve((size_t)nbatch * c->nel * 4))) return rc;
     SadGridParams g;
     g.Bt = c->dBt; g.dBt = c->ddBt; g.r = c->dR; g.wrad = c->dW;
-    g.nel = c->nel; g.nq = c->nq; g.ldq = c->ldq; g.np_max = c->np_max; g.nslices = nslices;
+    g.nel = c->nel; g.nq = c->nq; g.nq8 = c->nq8; g.ldq = c->ldq; g.np_max = c->np_max; g.np_pad = c->np_pad;
+    g.nslices = nslices; g.nb = nbatch;
     g.x_func = x_func; g.c_func = c_func; g.dens_thr = dens_thr;
     g.P = dP_band; g.H = dH_band; g.partial = c->dPartial.p;
-    if ((rc = launch_grid(fam, nspin, g, nbatch, st))) return rc;
+    if ((rc = launch_grid(fam, nspin, g, st))) return rc;
     if (dScalars) {
       sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(c->dPartial.p, c->nel, dScalars);
       HFB_CUDA_OK(cudaGetLastError());
     }
   }
   if (dJ_band) {
-    if (!c->dTei) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * np2))) return rc;
+    if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * 4 * c->jKS))) return rc;
     if ((rc = c->dTraces.reserve((size_t)nbatch * c->nel * 2))) return rc;
-    SadCoulombParams q;
-    q.dL = c->dDisL; q.dm1L = c->dDisM1L; q.tei = c->dTei;
-    q.nel = c->nel; q.np_max = c->np_max; q.nslices = nslices; q.nspin = nspin;
-    q.P = dP_band; q.Ptot = c->dPtot.p; q.traces = c->dTraces.p; q.J = dJ_band;
-    dim3 grid(c->nel, nbatch);
-    sad_trace_kernel<<<grid, 256, 0, st>>>(q);
-    HFB_CUDA_OK(cudaGetLastError());
-    sad_coulomb_kernel<<<grid, 256, np2 * sizeof(double), st>>>(q);
-    HFB_CUDA_OK(cudaGetLastError());
+    SadJParams q;
+    q.teiF = c->dTeiF; q.dLc = c->dLc; q.dm1Lc = c->dm1Lc; q.tri = c->dTri;
+    q.nel = c->nel; q.np_max = c->np_max; q.ntri = c->ntri; q.MT = c->jMT; q.KS = c->jKS;
+    q.nslices = nslices; q.nspin = nspin; q.nb = nbatch;
+    q.P = dP_band; q.pc = c->dPtot.p; q.traces = c->dTraces.p; q.J = dJ_band;
+    if ((rc = launch_coulomb(q, st))) return rc;
   }
   return HFB200_OK;
 }
@@ -252,7 +316,7 @@ int hfb200_sadatom_coulomb(hfb200_ctx* c, const double* P, int ldp, double* J, i
     set_error("hfb200_sadatom_coulomb: density matrix does not match basis set");
     return HFB200_EINVAL;
   }
-  if (!c->dTei) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
   HFB_CUDA_OK(cudaSetDevice(c->device));
   const size_t nband = (size_t)c->nel * c->np_max * c->np_max;
   int rc;
@@ -310,6 +374,34 @@ int hfb200_sadatom_eval_fxc(hfb200_ctx* c, int x_func, int c_func, int nspin, co
   }
   if (Exc) *Exc = c->hOut.p[nband + 0];
   if (Nel) *Nel = c->hOut.p[nband + 1];
+  return HFB200_OK;
+}
+
+/* Batched Fock builds with HOST element-band buffers (pinned or pageable): densities down, J / H bands and
+ * scalars back, all on the context's stream; returns after the results are on the host. */
+int hfb200_sadatom_fock_host(hfb200_ctx* c, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                             double dens_thr, const double* hP_band, double* hJ_band, double* hH_band,
+                             double* hScalars) {
+  if (!c || c->kind != CTX_SADATOM || nbatch < 1 || !hP_band || (nspin != 1 && nspin != 2) || nslices < 1) {
+    set_error("hfb200_sadatom_fock_host: invalid argument");
+    return HFB200_EINVAL;
+  }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  const size_t nblk = (size_t)c->nel * c->np_max * c->np_max;
+  const size_t nP = nblk * nslices * nspin * nbatch, nJ = nblk * nbatch;
+  int rc;
+  if ((rc = c->dP.reserve(nP)) || (hH_band && (rc = c->dH.reserve(nP))) || (hJ_band && (rc = c->dJ.reserve(nJ))) ||
+      (rc = c->dScalars.reserve((size_t)4 * nbatch)))
+    return rc;
+  HFB_CUDA_OK(cudaMemcpyAsync(c->dP.p, hP_band, nP * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if ((rc = hfb200_sadatom_fock_batch(c, nbatch, x_func, c_func, nspin, nslices, dens_thr, c->dP.p, hJ_band ? c->dJ.p : nullptr,
+                                      hH_band ? c->dH.p : nullptr, (hH_band && hScalars) ? c->dScalars.p : nullptr, c->stream)))
+    return rc;
+  if (hJ_band) HFB_CUDA_OK(cudaMemcpyAsync(hJ_band, c->dJ.p, nJ * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (hH_band) HFB_CUDA_OK(cudaMemcpyAsync(hH_band, c->dH.p, nP * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (hH_band && hScalars)
+    HFB_CUDA_OK(cudaMemcpyAsync(hScalars, c->dScalars.p, (size_t)4 * nbatch * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  HFB_CUDA_OK(cudaStreamSynchronize(c->stream));
   return HFB200_OK;
 }
 

@@ -63,7 +63,7 @@ struct hfb200_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   // ---- radial tables ----
-  int lmax = 0, nel = 0, nq = 0, ldq = 0, np_max = 0, nrad = 0;
+  int lmax = 0, nel = 0, nq = 0, nq8 = 0, ldq = 0, np_max = 0, np_pad = 0, nrad = 0;
   std::vector<int> first, last;
   double *dBt = nullptr, *ddBt = nullptr, *dR = nullptr, *dW = nullptr;
   int *dFirst = nullptr, *dNpe = nullptr, *dElemOf = nullptr;  // [nel], [nel], [nrad][2]
@@ -71,8 +71,12 @@ struct hfb200_ctx {
   // ---- stored integrals (padded to np_max) ----
   int nL = 0;
   bool have_ktei = false;
-  double *dDisL = nullptr, *dDisM1L = nullptr;  // [nL][nel][np2]
-  double *dTei = nullptr, *dKtei = nullptr;     // [nL][nel][np2*np2]
+  double *dDisL = nullptr, *dDisM1L = nullptr;  // [nL][nel][np2]            (exchange path)
+  double* dKtei = nullptr;                      // [nL][nel][np2*np2]        (exchange path)
+  // Coulomb path (L = 0): triangle-packed integrals in DMMA fragment order (sadatom_coulomb_mma.cuh)
+  int ntri = 0, jMT = 0, jKS = 0;
+  double *dTeiF = nullptr, *dLc = nullptr, *dm1Lc = nullptr;
+  int2* dTri = nullptr;
   // ---- scratch ----
   hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;
   hfb::PinBuf hIn, hOut;

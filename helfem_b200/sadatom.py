@@ -136,3 +136,9 @@ class SadatomBasis:
         check(lib().hfb200_sadatom_fock_batch(self.context(), int(nbatch), int(x_func), int(c_func), int(nspin), int(nslices),
                                               ctypes.c_double(thr), ctypes.c_void_p(dP), ctypes.c_void_p(dJ), ctypes.c_void_p(dH),
                                               ctypes.c_void_p(dS), ctypes.c_void_p(stream)))
+
+    def fock_host(self, nbatch, x_func, c_func, nspin, nslices, thr, hP, hJ=None, hH=None, hS=None):
+        """Host element-band arrays (numpy, C-contiguous float64) in and out; see include/helfem_b200.h."""
+        check(lib().hfb200_sadatom_fock_host(self.context(), int(nbatch), int(x_func), int(c_func), int(nspin), int(nslices),
+                                             ctypes.c_double(thr), _p(hP), _p(hJ) if hJ is not None else None,
+                                             _p(hH) if hH is not None else None, _p(hS) if hS is not None else None))

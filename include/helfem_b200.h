@@ -101,6 +101,13 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* ctx, int nbatch, int x_func, int c_fun
                               double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
                               double* dScalars, void* stream);
 
+/* The same batch with HOST element-band buffers (layout as above): one H2D copy of the densities, the
+ * kernels, D2H copies of J / H bands and scalars; returns when the results are on the host.  hJ_band,
+ * hH_band, hScalars may each be NULL to skip that operator. */
+int hfb200_sadatom_fock_host(hfb200_ctx* ctx, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                             double dens_thr, const double* hP_band, double* hJ_band, double* hH_band,
+                             double* hScalars);
+
 /* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
  * outputs are overwritten with exchange + correlation). */
 int hfb200_xc_eval(int device, int x_func, int c_func, int nspin, int n, double dens_thr, const double* rho,
