@@ -264,6 +264,11 @@ def run_gpu(args, w, rank, world, local_rank):
         ms = float(t.item())
     value = nb * world * args.steps / (ms * 1e-3)
 
+    if args.kernels_only:  # for ncu: just the timed steps, nothing else
+        if rank == 0:
+            print(json.dumps({"kernels_only": True, "ms_per_step": ms / args.steps, "value": value}), flush=True)
+        return
+
     # ---- per-kernel timing (rank 0 reports): the grid/XC kernel and the Coulomb kernels on their own ----
     ms_grid = timed(lambda: step(J=False), args.steps) / args.steps
     ms_j = timed(lambda: step(H=False), args.steps) / args.steps
@@ -380,6 +385,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="kr_pbe_cfg2", choices=list(WORKLOADS))
     ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
+    ap.add_argument("--kernels-only", action="store_true", help="run only the timed device steps (ncu captures)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -103,17 +103,27 @@ __global__ void __launch_bounds__(256) sad_jmma_kernel(SadJParams prm) {
     Bp[n] = prm.pc + ((size_t)(bok[n] ? bb : 0) * prm.nel + el) * KP + t4;
   }
   const int ks0 = SPLITK ? warp : 0, kstep = SPLITK ? 8 : 1;
-#pragma unroll 2
+  // software pipeline: fragments of step ks+kstep are in flight while step ks is multiplied
+  double a[4], bf[NTW];
+  auto load = [&](int ks, double* aa, double* bb) {
+#pragma unroll
+    for (int m = 0; m < 4; m++) aa[m] = (m < nmt && ks < KS) ? __ldg(A + ((size_t)m * KS + ks) * 32) : 0.0;
+#pragma unroll
+    for (int n = 0; n < NTW; n++) bb[n] = (bok[n] && ks < KS) ? __ldg(Bp[n] + 4 * ks) : 0.0;
+  };
+  load(ks0, a, bf);
+#pragma unroll 4
   for (int ks = ks0; ks < KS; ks += kstep) {
-    double a[4], bf[NTW];
-#pragma unroll
-    for (int m = 0; m < 4; m++) a[m] = (m < nmt) ? __ldg(A + ((size_t)m * KS + ks) * 32) : 0.0;
-#pragma unroll
-    for (int n = 0; n < NTW; n++) bf[n] = bok[n] ? Bp[n][4 * ks] : 0.0;
+    double an[4], bn[NTW];
+    load(ks + kstep, an, bn);
 #pragma unroll
     for (int m = 0; m < 4; m++)
 #pragma unroll
       for (int n = 0; n < NTW; n++) dmma(acc[m][n][0], acc[m][n][1], a[m], bf[n]);
+#pragma unroll
+    for (int m = 0; m < 4; m++) a[m] = an[m];
+#pragma unroll
+    for (int n = 0; n < NTW; n++) bf[n] = bn[n];
   }
   if (SPLITK) {
     // cross-warp reduction in a fixed order (deterministic)
