@@ -1,0 +1,83 @@
+"""ctypes view of hfb::atomic::TwoDBasis (helfem_b200/host/atomic.h), the host-side mirror of
+helfem::atomic::basis::TwoDBasis (/root/reference/src/atomic/TwoDBasis.h:38-226).  Harness only."""
+import ctypes
+
+import numpy as np
+
+from . import lib, check_host, _p, _ip
+
+
+class AtomicBasis:
+    """Arguments follow the reference's `atomic` flags (/root/reference/src/atomic/main.cpp:63-119)."""
+
+    def __init__(self, Z, nelem, nnodes=15, primbas=4, nquad=0, rmax=40.0, igrid=4, zexp=2.0, taylor_order=-1,
+                 lmax=0, mmax=0, zeroder=False, device=0):
+        L = lib()
+        L.hfh_atomic_free.argtypes = [ctypes.c_void_p]
+        L.hfh_atomic_free.restype = None
+        self._h = ctypes.c_void_p()
+        check_host(L.hfh_atomic_new(ctypes.byref(self._h), int(Z), int(primbas), int(nnodes), int(nquad), int(nelem),
+                                    ctypes.c_double(rmax), int(igrid), ctypes.c_double(zexp), int(taylor_order),
+                                    int(lmax), int(mmax), int(bool(zeroder)), int(device)))
+        nbf, nrad, nang, nel, nL = (ctypes.c_int() for _ in range(5))
+        check_host(L.hfh_atomic_dims(self._h, ctypes.byref(nbf), ctypes.byref(nrad), ctypes.byref(nang), ctypes.byref(nel),
+                                     ctypes.byref(nL)))
+        self.Z = Z
+        self.nbf, self.nrad, self.nang, self.nel = nbf.value, nrad.value, nang.value, nel.value
+        self.lval = np.zeros(self.nang, dtype=np.int32)
+        self.mval = np.zeros(self.nang, dtype=np.int32)
+        check_host(L.hfh_atomic_lm(self._h, _ip(self.lval), _ip(self.mval)))
+        self.first = np.zeros(self.nel, dtype=np.int32)
+        self.last = np.zeros(self.nel, dtype=np.int32)
+        check_host(L.hfh_atomic_idx(self._h, _ip(self.first), _ip(self.last)))
+        self.nL = 0
+        self.have_ktei = False
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib().hfh_atomic_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _matrix(self, which):
+        out = np.zeros((self.nbf, self.nbf), order="F")
+        check_host(lib().hfh_atomic_matrix(self._h, which, _p(out)))
+        return out
+
+    def overlap(self):
+        return self._matrix(0)
+
+    def kinetic(self):
+        return self._matrix(1)
+
+    def nuclear(self):
+        return self._matrix(3)
+
+    def compute_tei(self, exchange=True):
+        check_host(lib().hfh_atomic_compute_tei(self._h, int(bool(exchange))))
+        self.nL = 2 * int(self.lval.max()) + 1
+        self.have_ktei = bool(exchange)
+
+    def tei(self, L, iel):
+        npe = int(self.last[iel] - self.first[iel] + 1)
+        a = np.zeros((npe, npe), order="F")
+        b = np.zeros((npe, npe), order="F")
+        t = np.zeros((npe * npe, npe * npe), order="F")
+        k = np.zeros((npe * npe, npe * npe), order="F") if self.have_ktei else None
+        check_host(lib().hfh_atomic_get_tei(self._h, int(L), int(iel), _p(a), _p(b), _p(t), _p(k) if k is not None else None))
+        return a, b, t, k
+
+    def coulomb(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        J = np.zeros_like(P, order="F")
+        check_host(lib().hfh_atomic_coulomb(self._h, _p(P), _p(J)))
+        return J
+
+    def exchange(self, P):
+        """returns -K like the reference"""
+        P = np.asfortranarray(P, dtype=np.float64)
+        K = np.zeros_like(P, order="F")
+        check_host(lib().hfh_atomic_exchange(self._h, _p(P), _p(K)))
+        return K

@@ -1,6 +1,7 @@
 // C ABI: error handling, functional lookup, context life cycle (include/helfem_b200.h).
 #include <cstring>
 #include "../../include/helfem_b200.h"
+#include "chan_engine.h"
 #include "context.h"
 #include "xc_functionals.cuh"
 
@@ -54,6 +55,7 @@ void hfb200_destroy(hfb200_ctx* c) {
   for (auto* b : bufs) b->release();
   c->hIn.release();
   c->hOut.release();
+  if (c->chan) { c->chan->release(); delete c->chan; }
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }

@@ -1,0 +1,55 @@
+// Host-side driver of the channel-coupled Coulomb / exchange kernels (chan_kernels.cuh,
+// chan_exchange.cuh) shared by the `atomic` and `diatomic` C-ABI entry points.
+#pragma once
+#include <functional>
+#include <vector>
+#include "chan_exchange.cuh"
+#include "chan_kernels.cuh"
+#include "context.h"
+
+namespace hfb {
+
+/// One coupling of an ordered angular pair (k,l) to a channel: Paux_c += coef[h] * P_{kl} (h = stack half).
+struct ChanCoupling {
+  int chan;
+  double coef[2];
+};
+
+/// Host description of a coupled-channel problem (everything constant across SCF iterations).
+struct ChanSpec {
+  int nel = 0, nang = 0, stack = 1, nr = 0;
+  std::vector<int> first, last;            // element index ranges (FiniteElementBasis::get_idx)
+  std::vector<double> fac;                 // [nr]  4 pi/(2L+1)  resp.  LMfac
+  std::vector<int> chan_r;                 // [nchan] family of each channel, sorted by family
+  std::vector<std::vector<ChanCoupling>> pair_coupl;  // [nang*nang], index k*nang + l
+  // in-element integrals of family r, element e, block (hout, hin) of the stacked matrix:
+  // returns the (np_e^2 x np_e^2) column-major block and its sign, nullptr if the block is absent
+  std::function<const double*(int r, int e, int hout, int hin, double* sign)> tei;
+  // K-ordered in-element integrals (exchange), same indexing; may be empty
+  std::function<const double*(int r, int e, int hout, int hin, double* sign)> ktei;
+  // disjoint factors (np_e x np_e): "small" (r_<-type: dL, P0/P2) and "big" (r_>-type: dm1L, Q0/Q2)
+  std::function<const double*(int r, int e, int h, double* sign)> small_f, big_f;
+};
+
+struct ChanEngine {
+  ChanParams prm{};                 // device pointers + sizes
+  int nrad = 0, nchan = 0, npair = 0;
+  std::vector<int> first, last;
+  std::vector<void*> owned;         // device allocations to free
+  DevBuf dP, dPc, dTr, dJc, dJ;
+  PinBuf hIn, hOut;
+  std::vector<int> fam_c0_host, out_pairs_host;
+  // exchange tables
+  bool have_k = false;
+  ChanXParams xprm{};
+  int nout = 0;
+  DevBuf dPdense, dKdense, dKblocks;
+
+  int build_exchange(const ChanSpec& spec);
+  int build(const ChanSpec& spec, bool with_exchange);
+  int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st);
+  int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st);
+  void release();
+};
+
+}  // namespace hfb

@@ -1,0 +1,222 @@
+// sm_100a kernels for the Gaunt-coupled Coulomb operator of the `atomic` and `diatomic` programs.
+//
+// Both references have the same three-step structure
+//   atomic    /root/reference/src/atomic/TwoDBasis.cpp:817-955
+//   diatomic  /root/reference/src/diatomic/basis.cpp:1359-1530
+//   (i)   ket contraction: per coupling channel c = (L,M) a radial density  Paux_c = sum_{(k,l)} G P_{kl}
+//   (ii)  radial Coulomb operator of the channel's integral family r (atomic: r = L; diatomic: r = (L,|M|)):
+//         in-element block  fac * T_r * vec(Psub)  + disjoint terms driven by two traces per element
+//   (iii) bra contraction:  J_{ij} += G * Jaux_c
+// which is re-derived here as three kernels over device-resident constants:
+//   chan_pre_kernel    (element, channel, build): CSR gather of the angular-pair band into a
+//                      triangle-packed, symmetry-folded density vector + the two traces
+//   chan_jmma_kernel   (element x 32-row tile, column chunk, family): DMMA.8x8x4 product with the
+//                      fragment-ordered packed integrals; columns = the channels of the family x builds
+//   chan_post_kernel   (element, angular pair, build): CSR gather of the channel results into the
+//                      angular-pair band of J
+// "Stacking" (diatomic): the two coupled densities (Paux0, Paux2) and results (Jaux0, Jaux2) of a
+// channel are stacked into one vector of length 2 ntri, the four integral families into one matrix
+// fac [[T00, -T02], [-T20, T22]], and the four disjoint factors into s = fac [P0; -P2], b = [Q0; -Q2];
+// then the diatomic update rules (:1432-1489) are literally the atomic ones (:879-923) on stacked data.
+#pragma once
+#include <cuda_runtime.h>
+#include "sadatom_grid_mma.cuh"  // dmma()
+
+namespace hfb {
+
+struct ChanParams {
+  // ---- constants ----
+  int nel, np, np2, ntri, stack, MT, KS, nr, nchan, npair;
+  const int2* tri;        // [ntri] (i<=j)
+  const double* teiF;     // [nr][nel][MT][KS][32]   fac folded in
+  const double* svec;     // [nr][nel][8 MT]         "small" disjoint factor, fac folded in
+  const double* bvec;     // [nr][nel][8 MT]         "big" disjoint factor
+  const int* chan_r;      // [nchan] family of a channel (channels sorted by family)
+  const int* fam_c0;      // [nr+1]  channel range of a family
+  const int* pre_ptr;     // [nchan+1] CSR: channel -> (pair, coef[stack])
+  const int* pre_pair;
+  const double* pre_coef; // [nnz][2]
+  const int* post_ptr;    // [npair+1] CSR: pair -> (channel, coef[stack])
+  const int* post_chan;
+  const double* post_coef;
+  // ---- per call ----
+  int nb;
+  const double* P;        // [nb][npair][nel][np2]
+  double* pc;             // [nchan][nb][nel][4 KS]
+  double* traces;         // [nchan][nb][nel][2]
+  double* jc;             // [nchan][nb][nel][8 MT]
+  double* J;              // [nb][npair][nel][np2]
+};
+
+// grid (nel, nchan, nb), 128 threads
+static __global__ void __launch_bounds__(128) chan_pre_kernel(ChanParams prm) {
+  __shared__ double red[8];
+  const int el = blockIdx.x, c = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
+  const int np = prm.np, np2 = prm.np2, KP = 4 * prm.KS, MP = 8 * prm.MT, r = prm.chan_r[c];
+  const int e0 = prm.pre_ptr[c], e1 = prm.pre_ptr[c + 1];
+  const double* gP = prm.P + ((size_t)b * prm.npair * prm.nel + el) * np2;
+  const size_t pstride = (size_t)prm.nel * np2;
+  const double* sv = prm.svec + ((size_t)r * prm.nel + el) * MP;
+  const double* bv = prm.bvec + ((size_t)r * prm.nel + el) * MP;
+  double* out = prm.pc + (((size_t)c * prm.nb + b) * prm.nel + el) * KP;
+  double ts = 0.0, tb = 0.0;
+  for (int m = tid; m < KP; m += blockDim.x) {
+    double v = 0.0;
+    if (m < prm.stack * prm.ntri) {
+      const int h = m >= prm.ntri ? 1 : 0;
+      const int2 ij = prm.tri[m - h * prm.ntri];
+      const int a = ij.x + ij.y * np, at = ij.y + ij.x * np;
+      for (int e = e0; e < e1; e++) {
+        const double cf = prm.pre_coef[2 * e + h];
+        if (cf == 0.0) continue;
+        const double* src = gP + (size_t)prm.pre_pair[e] * pstride;
+        double p = src[a];
+        if (ij.x != ij.y) p += src[at];
+        v = fma(cf, p, v);
+      }
+      ts = fma(sv[m], v, ts);
+      tb = fma(bv[m], v, tb);
+    }
+    out[m] = v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ts += __shfl_xor_sync(0xffffffffu, ts, o);
+    tb += __shfl_xor_sync(0xffffffffu, tb, o);
+  }
+  if ((tid & 31) == 0) { red[tid >> 5] = ts; red[4 + (tid >> 5)] = tb; }
+  __syncthreads();
+  if (tid == 0) {
+    double* tr = prm.traces + (((size_t)c * prm.nb + b) * prm.nel + el) * 2;
+    tr[0] = (red[0] + red[1]) + (red[2] + red[3]);
+    tr[1] = (red[4] + red[5]) + (red[6] + red[7]);
+  }
+}
+
+// grid (nel * ceil(MT/4), column chunks, nr), 256 threads.  Columns n of family r: (channel - c0) * nb + build.
+template <bool SPLITK, int NTW>
+__global__ void __launch_bounds__(256) chan_jmma_kernel(ChanParams prm) {
+  __shared__ double sred[SPLITK ? 8 * 4 * NTW * 64 : 1];
+  const int rts = (prm.MT + 3) >> 2;
+  const int el = blockIdx.x / rts, rt = blockIdx.x % rts, r = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gid = lane >> 2, t4 = lane & 3;
+  const int KS = prm.KS, KP = 4 * KS, MP = 8 * prm.MT;
+  const int mt0 = 4 * rt, nmt = min(4, prm.MT - mt0);
+  const int c0 = prm.fam_c0[r];
+  const int ncol = (prm.fam_c0[r + 1] - c0) * prm.nb;
+  const int chunk = SPLITK ? 8 * NTW : 8 * 8 * NTW;
+  if (blockIdx.y * chunk >= ncol) return;  // block-uniform
+  const int bw0 = blockIdx.y * chunk + (SPLITK ? 0 : warp * 8 * NTW);
+  if (!SPLITK && bw0 >= ncol) return;
+
+  double acc[4][NTW][2];
+#pragma unroll
+  for (int m = 0; m < 4; m++)
+#pragma unroll
+    for (int n = 0; n < NTW; n++) { acc[m][n][0] = 0.0; acc[m][n][1] = 0.0; }
+
+  const double* A = prm.teiF + ((((size_t)r * prm.nel + el) * prm.MT + mt0) * KS) * 32 + lane;
+  const double* colbase = prm.pc + (size_t)c0 * prm.nb * prm.nel * KP;  // column n at n * nel * KP
+  const double* Bp[NTW];
+  bool bok[NTW];
+#pragma unroll
+  for (int n = 0; n < NTW; n++) {
+    const int col = bw0 + 8 * n + gid;
+    bok[n] = col < ncol;
+    Bp[n] = colbase + ((size_t)(bok[n] ? col : 0) * prm.nel + el) * KP + t4;
+  }
+  const int ks0 = SPLITK ? warp : 0, kstep = SPLITK ? 8 : 1;
+  double a[4], bf[NTW];
+  auto load = [&](int ks, double* aa, double* bb) {
+#pragma unroll
+    for (int m = 0; m < 4; m++) aa[m] = (m < nmt && ks < KS) ? __ldg(A + ((size_t)m * KS + ks) * 32) : 0.0;
+#pragma unroll
+    for (int n = 0; n < NTW; n++) bb[n] = (bok[n] && ks < KS) ? __ldg(Bp[n] + 4 * ks) : 0.0;
+  };
+  load(ks0, a, bf);
+#pragma unroll 4
+  for (int ks = ks0; ks < KS; ks += kstep) {
+    double an[4], bn[NTW];
+    load(ks + kstep, an, bn);
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) dmma(acc[m][n][0], acc[m][n][1], a[m], bf[n]);
+#pragma unroll
+    for (int m = 0; m < 4; m++) a[m] = an[m];
+#pragma unroll
+    for (int n = 0; n < NTW; n++) bf[n] = bn[n];
+  }
+  if (SPLITK) {
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) {
+        sred[((warp * 4 + m) * NTW + n) * 64 + lane] = acc[m][n][0];
+        sred[((warp * 4 + m) * NTW + n) * 64 + 32 + lane] = acc[m][n][1];
+      }
+    __syncthreads();
+    if (warp != 0) return;
+#pragma unroll
+    for (int m = 0; m < 4; m++)
+#pragma unroll
+      for (int n = 0; n < NTW; n++) {
+        double s0 = 0.0, s1 = 0.0;
+        for (int w = 0; w < 8; w++) {
+          s0 += sred[((w * 4 + m) * NTW + n) * 64 + lane];
+          s1 += sred[((w * 4 + m) * NTW + n) * 64 + 32 + lane];
+        }
+        acc[m][n][0] = s0;
+        acc[m][n][1] = s1;
+      }
+  }
+  // epilogue: thread holds Jc[m = 8 (mt0+mm) + gid][column bw0 + 8 n + 2 t4 + cc]
+  const double* sv = prm.svec + ((size_t)r * prm.nel + el) * MP;
+  const double* bv = prm.bvec + ((size_t)r * prm.nel + el) * MP;
+#pragma unroll
+  for (int n = 0; n < NTW; n++)
+#pragma unroll
+    for (int cc = 0; cc < 2; cc++) {
+      const int col = bw0 + 8 * n + 2 * t4 + cc;
+      if (col >= ncol) continue;
+      const double* tr = prm.traces + ((size_t)c0 * prm.nb + col) * prm.nel * 2;
+      double below = 0.0, above = 0.0;  // sum_{j<el} jsmall_j ; sum_{j>el} jbig_j
+      for (int j = 0; j < el; j++) below += tr[2 * j];
+      for (int j = el + 1; j < prm.nel; j++) above += tr[2 * j + 1];
+      double* out = prm.jc + (((size_t)c0 * prm.nb + col) * prm.nel + el) * MP;
+#pragma unroll
+      for (int mm = 0; mm < 4; mm++) {
+        const int m = 8 * (mt0 + mm) + gid;
+        if (mm < nmt) {
+          // J_el += jbig_j * s_el (j > el) + jsmall_j * b_el (j < el); fac is folded into s and T
+          double v = acc[mm][n][cc];
+          v = fma(above, sv[m], v);
+          v = fma(below, bv[m], v);
+          out[m] = v;
+        }
+      }
+    }
+}
+
+// grid (nel, npair, nb), 128 threads
+static __global__ void __launch_bounds__(128) chan_post_kernel(ChanParams prm) {
+  const int el = blockIdx.x, pr = blockIdx.y, b = blockIdx.z;
+  const int np = prm.np, np2 = prm.np2, MP = 8 * prm.MT;
+  const int e0 = prm.post_ptr[pr], e1 = prm.post_ptr[pr + 1];
+  double* out = prm.J + (((size_t)b * prm.npair + pr) * prm.nel + el) * np2;
+  for (int k = threadIdx.x; k < np2; k += blockDim.x) {
+    const int i = k % np, j = k / np;
+    const int lo = min(i, j), hi = max(i, j);
+    const int m = lo + hi * (hi + 1) / 2;
+    double v = 0.0;
+    for (int e = e0; e < e1; e++) {
+      const double* src = prm.jc + (((size_t)prm.post_chan[e] * prm.nb + b) * prm.nel + el) * MP;
+      v = fma(prm.post_coef[2 * e], src[m], v);
+      if (prm.stack == 2) v = fma(prm.post_coef[2 * e + 1], src[prm.ntri + m], v);
+    }
+    out[k] = v;
+  }
+}
+
+}  // namespace hfb

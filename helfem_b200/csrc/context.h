@@ -54,6 +54,7 @@ struct PinBuf {
 };
 
 enum CtxKind { CTX_SADATOM = 1, CTX_ATOMIC = 2, CTX_DIATOMIC = 3 };
+struct ChanEngine;
 
 }  // namespace hfb
 
@@ -77,6 +78,9 @@ struct hfb200_ctx {
   int ntri = 0, jMT = 0, jKS = 0;
   double *dTeiF = nullptr, *dLc = nullptr, *dm1Lc = nullptr;
   int2* dTri = nullptr;
+  // ---- atomic / diatomic: angular basis + channel engine (chan_engine.h) ----
+  std::vector<int> lval, mval;
+  hfb::ChanEngine* chan = nullptr;
   // ---- scratch ----
   hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;
   hfb::PinBuf hIn, hOut;

@@ -36,7 +36,7 @@ struct SadJParams {
 };
 
 // grid (nel, nb), 128 threads
-__global__ void __launch_bounds__(128) sad_jpack_kernel(SadJParams prm) {
+static __global__ void __launch_bounds__(128) sad_jpack_kernel(SadJParams prm) {
   __shared__ double red[8];
   const int el = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
   const int np = prm.np_max, np2 = np * np, KP = 4 * prm.KS, MP = 8 * prm.MT;

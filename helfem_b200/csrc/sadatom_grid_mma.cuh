@@ -303,7 +303,7 @@ inline size_t sad_grid_mma_smem_bytes(int fam, int nspin, int np_pad, int nq8, i
 }
 
 // [nb][nel][4] partial scalars -> [nb][4], fixed order
-__global__ void sad_reduce_scalars_kernel(const double* partial, int nel, double* out) {
+static __global__ void sad_reduce_scalars_kernel(const double* partial, int nel, double* out) {
   const int b = blockIdx.x;
   if (threadIdx.x < 4) {
     double s = 0.0;

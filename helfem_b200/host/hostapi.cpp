@@ -6,6 +6,7 @@
 #include <string>
 #include "../../include/helfem_b200.h"
 #include "angular.h"
+#include "atomic.h"
 #include "sadatom.h"
 
 using namespace hfb;
@@ -191,6 +192,95 @@ int hfh_sadatom_eval_fxc(void* h, int x_func, int c_func, int nspin, const doubl
     memcpy(Ha, H1.ptr(), tot * sizeof(double));
     if (Hb) memcpy(Hb, H2.ptr(), tot * sizeof(double));
   }
+  HFH_CATCH
+}
+
+// ---- atomic ----
+int hfh_atomic_new(void** out, int Z, int primbas, int nnodes, int nquad, int nelem, double rmax, int igrid, double zexp,
+                   int taylor_order, int lmax, int mmax, int zeroder, int device) {
+  HFH_TRY
+  fem::PolyBasis poly(primbas, nnodes);
+  if (nquad <= 0) nquad = 5 * poly.get_nbf();  // atomic/main.cpp:245-249
+  if (taylor_order < 0) taylor_order = poly.get_nprim() - 1;
+  Vec bval = fem::get_grid(rmax, nelem, igrid, zexp);
+  std::vector<int> lval, mval;
+  angular::angular_basis(lmax, mmax, lval, mval);  // atomic/main.cpp:268
+  *out = new atomic::TwoDBasis(Z, poly, zeroder != 0, nquad, bval, taylor_order, lval, mval, device);
+  HFH_CATCH
+}
+void hfh_atomic_free(void* h) { delete (atomic::TwoDBasis*)h; }
+int hfh_atomic_dims(void* h, int* nbf, int* nrad, int* nang, int* nel, int* nL) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  if (nbf) *nbf = (int)b->Nbf();
+  if (nrad) *nrad = (int)b->Nrad();
+  if (nang) *nang = (int)b->Nang();
+  if (nel) *nel = (int)b->get_radial().Nel();
+  if (nL) *nL = b->get_nL();
+  HFH_CATCH
+}
+int hfh_atomic_lm(void* h, int* lval, int* mval) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  for (size_t a = 0; a < b->Nang(); a++) { lval[a] = b->get_lval()[a]; mval[a] = b->get_mval()[a]; }
+  HFH_CATCH
+}
+int hfh_atomic_idx(void* h, int* first, int* last) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  for (size_t e = 0; e < b->get_radial().Nel(); e++) {
+    size_t f, l;
+    b->get_radial().get_idx(e, f, l);
+    first[e] = (int)f;
+    last[e] = (int)l;
+  }
+  HFH_CATCH
+}
+/// which: 0 overlap, 1 kinetic, 3 nuclear
+int hfh_atomic_matrix(void* h, int which, double* out) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  Mat m = which == 0 ? b->overlap() : which == 1 ? b->kinetic() : b->nuclear();
+  memcpy(out, m.ptr(), m.size() * sizeof(double));
+  HFH_CATCH
+}
+int hfh_atomic_compute_tei(void* h, int exchange) {
+  HFH_TRY
+  ((atomic::TwoDBasis*)h)->compute_tei(exchange != 0);
+  HFH_CATCH
+}
+int hfh_atomic_get_tei(void* h, int L, int iel, double* disL, double* dism1L, double* tei, double* ktei) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  const size_t idx = (size_t)L * b->get_radial().Nel() + iel;
+  if (L >= b->get_nL()) throw std::logic_error("Primitive teis have not been computed!\n");
+  if (disL) memcpy(disL, b->get_disjoint_L()[idx].ptr(), b->get_disjoint_L()[idx].size() * sizeof(double));
+  if (dism1L) memcpy(dism1L, b->get_disjoint_m1L()[idx].ptr(), b->get_disjoint_m1L()[idx].size() * sizeof(double));
+  if (tei) memcpy(tei, b->get_prim_tei()[idx].ptr(), b->get_prim_tei()[idx].size() * sizeof(double));
+  if (ktei) {
+    if (b->get_prim_ktei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+    memcpy(ktei, b->get_prim_ktei()[idx].ptr(), b->get_prim_ktei()[idx].size() * sizeof(double));
+  }
+  HFH_CATCH
+}
+int hfh_atomic_coulomb(void* h, const double* P, double* J) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Mat Pm(n, n);
+  memcpy(Pm.ptr(), P, n * n * sizeof(double));
+  Mat Jm = b->coulomb(Pm);
+  memcpy(J, Jm.ptr(), n * n * sizeof(double));
+  HFH_CATCH
+}
+int hfh_atomic_exchange(void* h, const double* P, double* K) {
+  HFH_TRY
+  auto* b = (atomic::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Mat Pm(n, n);
+  memcpy(Pm.ptr(), P, n * n * sizeof(double));
+  Mat Km = b->exchange(Pm);
+  memcpy(K, Km.ptr(), n * n * sizeof(double));
   HFH_CATCH
 }
 

@@ -108,6 +108,21 @@ int hfb200_sadatom_fock_host(hfb200_ctx* ctx, int nbatch, int x_func, int c_func
                              double dens_thr, const double* hP_band, double* hJ_band, double* hH_band,
                              double* hScalars);
 
+/* ------------------------------------------------------------------------------------------
+ * `atomic` program: product basis (l,m) x radial, global index iang*nrad + irad
+ * (atomic/TwoDBasis.cpp:290-300).  lval/mval: the angular list of atomic::basis::angular_basis
+ * (atomic/basis.cpp:174-198).  Stored integrals as built by TwoDBasis::compute_tei
+ * (atomic/TwoDBasis.cpp:666-739) for L = 0..2 max(lval): arrays of nL*nel pointers, entry [L*nel+iel]
+ * (the reference's in-element index Nel*Nel*L + iel*Nel + iel).  prim_ktei may be NULL.
+ * P, J, K: dense (nang*nrad)^2 host matrices; exchange returns -K like the reference.
+ * ------------------------------------------------------------------------------------------ */
+int hfb200_atomic_create(hfb200_ctx** ctx, int device, int nang, const int* lval, const int* mval, int nel,
+                         const int* first, const int* last);
+int hfb200_atomic_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoint_L, const double* const* disjoint_m1L,
+                          const double* const* prim_tei, const double* const* prim_ktei);
+int hfb200_atomic_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
+int hfb200_atomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* K, int ldk);
+
 /* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
  * outputs are overwritten with exchange + correlation). */
 int hfb200_xc_eval(int device, int x_func, int c_func, int nspin, int n, double dens_thr, const double* rho,

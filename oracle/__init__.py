@@ -150,3 +150,33 @@ def sadatom_from_setup(rs, lmax, nL=1, exchange=False):
                 ktei.append(fem_oracle.exchange_tei(t, n, n, n, n))
     o.set_tei(dL, dm1L, tei, ktei if exchange else None)
     return o
+
+
+class AtomicOracle:
+    """Reference algorithm of atomic::basis::TwoDBasis::coulomb / exchange on the CPU (oracle/chan_oracle.cpp).
+    dL, dm1L, tei, ktei: lists indexed [L*nel + iel] of Fortran-ordered arrays."""
+
+    def __init__(self, lval, mval, first, last, dL, dm1L, tei, ktei=None):
+        self.lval = np.ascontiguousarray(lval, dtype=np.int32)
+        self.mval = np.ascontiguousarray(mval, dtype=np.int32)
+        self.first = np.ascontiguousarray(first, dtype=np.int32)
+        self.last = np.ascontiguousarray(last, dtype=np.int32)
+        self.nel, self.nang = len(self.first), len(self.lval)
+        self.dL = [np.asfortranarray(a) for a in dL]
+        self.dm1L = [np.asfortranarray(a) for a in dm1L]
+        self.tei = [np.asfortranarray(a) for a in tei]
+        self.ktei = None if ktei is None else [np.asfortranarray(a) for a in ktei]
+
+    def coulomb(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        J = np.zeros_like(P, order="F")
+        lib().oracle_atomic_coulomb(self.nang, _ip(self.lval), _ip(self.mval), self.nel, _ip(self.first), _ip(self.last),
+                                    _ptr_array(self.dL), _ptr_array(self.dm1L), _ptr_array(self.tei), _p(P), _p(J))
+        return J
+
+    def exchange(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        K = np.zeros_like(P, order="F")
+        lib().oracle_atomic_exchange(self.nang, _ip(self.lval), _ip(self.mval), self.nel, _ip(self.first), _ip(self.last),
+                                     _ptr_array(self.dL), _ptr_array(self.dm1L), _ptr_array(self.ktei), _p(P), _p(K))
+        return K

@@ -1,0 +1,186 @@
+// ORACLE (test infrastructure, not product code): CPU restatement of the reference's Gaunt-coupled
+// Coulomb / exchange operators of the `atomic` program, following the reference's own loop structure
+// with dense Nrad x Nrad helper matrices.
+//   oracle_atomic_coulomb    /root/reference/src/atomic/TwoDBasis.cpp:817-955
+//   oracle_atomic_exchange   /root/reference/src/atomic/TwoDBasis.cpp:957-1140
+// Stored integrals are INPUTS (arrays of pointers, entry [L*nel + iel]); Gaunt coefficients come from
+// the oracle's own Racah-formula implementation (hotpath_oracle.cpp), not from the product.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+extern "C" double oracle_gaunt(int L, int M, int l, int m, int lp, int mp);
+
+namespace {
+typedef std::vector<double> vec;
+inline double gcoeff(int L, int M, int l, int m, int lp, int mp) {
+  if (std::abs(M) > L || std::abs(m) > l || std::abs(mp) > lp) return 0.0;  // Gaunt::coeff guards, gaunt.cpp:113-115
+  return oracle_gaunt(L, M, l, m, lp, mp);
+}
+}  // namespace
+
+extern "C" {
+
+int oracle_atomic_coulomb(int nang, const int* lval, const int* mval, int nel, const int* first, const int* last,
+                          const double* const* dL, const double* const* dm1L, const double* const* tei, const double* P,
+                          double* J) {
+  const int nrad = last[nel - 1] + 1, ntot = nang * nrad;
+  const size_t n2 = (size_t)nrad * nrad;
+  int lmax = 0, mmin = 0, mmx = 0;
+  for (int a = 0; a < nang; a++) { lmax = std::max(lmax, lval[a]); mmin = std::min(mmin, mval[a]); mmx = std::max(mmx, mval[a]); }
+  const int Mmax = mmx - mmin, nL = 2 * lmax + 1, nM = 2 * Mmax + 1;
+  std::vector<vec> Paux((size_t)nL * nM), Jaux((size_t)nL * nM);
+  for (int L = 0; L < nL; L++)
+    for (int M = -std::min(L, Mmax); M <= std::min(L, Mmax); M++) {
+      Paux[L * nM + M + Mmax].assign(n2, 0.0);
+      Jaux[L * nM + M + Mmax].assign(n2, 0.0);
+    }
+  // contract ket (:845-864)
+  for (int k = 0; k < nang; k++)
+    for (int l = 0; l < nang; l++) {
+      const int lk = lval[k], mk = mval[k], ll = lval[l], ml = mval[l], M = mk - ml;
+      for (int L = std::max(std::abs(lk - ll), std::abs(M)); L <= lk + ll; L++) {
+        const double cpl = gcoeff(lk, mk, L, M, ll, ml);
+        if (cpl == 0.0) continue;
+        vec& Pa = Paux[L * nM + M + Mmax];
+        for (int b = 0; b < nrad; b++)
+          for (int a = 0; a < nrad; a++) Pa[a + (size_t)b * nrad] += cpl * P[(size_t)(k * nrad + a) + (size_t)(l * nrad + b) * ntot];
+      }
+    }
+  // radial contraction (:872-927)
+  for (int L = 0; L < nL; L++) {
+    const double Lfac = 4.0 * M_PI / (2 * L + 1);
+    for (int M = -std::min(L, Mmax); M <= std::min(L, Mmax); M++) {
+      const vec& Pa = Paux[L * nM + M + Mmax];
+      vec& Ja = Jaux[L * nM + M + Mmax];
+      for (int jel = 0; jel < nel; jel++) {
+        const int jf = first[jel], Nj = last[jel] - jf + 1;
+        vec Psub((size_t)Nj * Nj);
+        for (int b = 0; b < Nj; b++)
+          for (int a = 0; a < Nj; a++) Psub[a + b * Nj] = Pa[(jf + a) + (size_t)(jf + b) * nrad];
+        double ts = 0.0, tb = 0.0;
+        for (int a = 0; a < Nj; a++)
+          for (int b = 0; b < Nj; b++) {
+            ts += dL[L * nel + jel][a + b * Nj] * Psub[b + a * Nj];
+            tb += dm1L[L * nel + jel][a + b * Nj] * Psub[b + a * Nj];
+          }
+        const double jsmall = Lfac * ts, jbig = Lfac * tb;
+        for (int iel = 0; iel < jel; iel++) {
+          const int f = first[iel], Ni = last[iel] - f + 1;
+          for (int b = 0; b < Ni; b++)
+            for (int a = 0; a < Ni; a++) Ja[(f + a) + (size_t)(f + b) * nrad] += jbig * dL[L * nel + iel][a + b * Ni];
+        }
+        for (int iel = jel + 1; iel < nel; iel++) {
+          const int f = first[iel], Ni = last[iel] - f + 1;
+          for (int b = 0; b < Ni; b++)
+            for (int a = 0; a < Ni; a++) Ja[(f + a) + (size_t)(f + b) * nrad] += jsmall * dm1L[L * nel + iel][a + b * Ni];
+        }
+        const size_t m2 = (size_t)Nj * Nj;
+        vec Jsub(m2, 0.0);
+        const double* T = tei[L * nel + jel];
+        for (size_t c = 0; c < m2; c++)
+          for (size_t r = 0; r < m2; r++) Jsub[r] += T[r + c * m2] * Psub[c];
+        for (int b = 0; b < Nj; b++)
+          for (int a = 0; a < Nj; a++) Ja[(jf + a) + (size_t)(jf + b) * nrad] += Lfac * Jsub[a + b * Nj];
+      }
+    }
+  }
+  // bra (:932-952)
+  std::fill(J, J + (size_t)ntot * ntot, 0.0);
+  for (int i = 0; i < nang; i++)
+    for (int j = 0; j < nang; j++) {
+      const int li = lval[i], mi = mval[i], lj = lval[j], mj = mval[j], M = mj - mi;
+      for (int L = std::max(std::abs(lj - li), std::abs(M)); L <= lj + li; L++) {
+        const double cpl = gcoeff(lj, mj, L, M, li, mi);
+        if (cpl == 0.0) continue;
+        const vec& Ja = Jaux[L * nM + M + Mmax];
+        for (int b = 0; b < nrad; b++)
+          for (int a = 0; a < nrad; a++) J[(size_t)(i * nrad + a) + (size_t)(j * nrad + b) * ntot] += cpl * Ja[a + (size_t)b * nrad];
+      }
+    }
+  return 0;
+}
+
+int oracle_atomic_exchange(int nang, const int* lval, const int* mval, int nel, const int* first, const int* last,
+                           const double* const* dL, const double* const* dm1L, const double* const* ktei, const double* P,
+                           double* K) {
+  const int nrad = last[nel - 1] + 1, ntot = nang * nrad;
+  const size_t n2 = (size_t)nrad * nrad;
+  int lmax = 0;
+  for (int a = 0; a < nang; a++) lmax = std::max(lmax, lval[a]);
+  const int nL = 2 * lmax + 1;
+  std::fill(K, K + (size_t)ntot * ntot, 0.0);
+#ifdef _OPENMP
+#pragma omp parallel for collapse(2) schedule(dynamic)
+#endif
+  for (int jang = 0; jang < nang; jang++)
+    for (int kang = 0; kang < nang; kang++) {
+      const int lj = lval[jang], mj = mval[jang], lk = lval[kang], mk = mval[kang];
+      std::vector<vec> Rmat(nL, vec(n2, 0.0));
+      std::vector<bool> couple(nL, false);
+      for (int iang = 0; iang < nang; iang++)
+        for (int lang = 0; lang < nang; lang++) {
+          const int li = lval[iang], mi = mval[iang], ll = lval[lang], ml = mval[lang];
+          const int M = mj - mi, Mp = mk - ml;
+          if (M != Mp) continue;
+          double nrm = 0.0;
+          for (int b = 0; b < nrad; b++)
+            for (int a = 0; a < nrad; a++) {
+              const double v = P[(size_t)(iang * nrad + a) + (size_t)(lang * nrad + b) * ntot];
+              nrm += v * v;
+            }
+          if (std::sqrt(nrm) < 10 * 2.220446049250313e-16) continue;
+          const int Lmin = std::max(std::max(std::abs(li - lj), std::abs(lk - ll)), std::abs(M));
+          const int Lmax = std::min(li + lj, lk + ll);
+          for (int L = Lmin; L <= Lmax; L++) {
+            const double cpl = gcoeff(lj, mj, L, M, li, mi) * gcoeff(lk, mk, L, M, ll, ml);
+            if (cpl == 0.0) continue;
+            const double Lfac = 4.0 * M_PI / (2 * L + 1);
+            for (int b = 0; b < nrad; b++)
+              for (int a = 0; a < nrad; a++)
+                Rmat[L][a + (size_t)b * nrad] += (Lfac * cpl) * P[(size_t)(iang * nrad + a) + (size_t)(lang * nrad + b) * ntot];
+            couple[L] = true;
+          }
+        }
+      for (int iel = 0; iel < nel; iel++)
+        for (int jel = 0; jel < nel; jel++) {
+          const int fi = first[iel], fj = first[jel], Ni = last[iel] - fi + 1, Nj = last[jel] - fj + 1;
+          vec Ksub((size_t)Ni * Nj, 0.0);
+          for (int L = 0; L < nL; L++) {
+            if (!couple[L]) continue;
+            const vec& R = Rmat[L];
+            if (iel == jel) {
+              const size_t m2 = (size_t)Ni * Nj;
+              const double* T = ktei[L * nel + iel];
+              for (int b = 0; b < Nj; b++)
+                for (int a = 0; a < Ni; a++) {
+                  const double pv = R[(fi + a) + (size_t)(fj + b) * nrad];
+                  const size_t c = a + (size_t)b * Ni;
+                  for (size_t r = 0; r < m2; r++) Ksub[r] += T[r + c * m2] * pv;
+                }
+            } else {
+              const double* iint = (iel > jel) ? dm1L[L * nel + iel] : dL[L * nel + iel];
+              const double* jint = (iel > jel) ? dL[L * nel + jel] : dm1L[L * nel + jel];
+              vec T((size_t)Ni * Nj, 0.0);
+              for (int k = 0; k < Nj; k++)
+                for (int b = 0; b < Nj; b++) {
+                  const double jv = jint[k + b * Nj];
+                  for (int a = 0; a < Ni; a++) T[a + k * Ni] += R[(fi + a) + (size_t)(fj + b) * nrad] * jv;
+                }
+              for (int k = 0; k < Nj; k++)
+                for (int c = 0; c < Ni; c++) {
+                  const double tv = T[c + k * Ni];
+                  for (int a = 0; a < Ni; a++) Ksub[a + k * Ni] += iint[a + c * Ni] * tv;
+                }
+            }
+          }
+          for (int b = 0; b < Nj; b++)
+            for (int a = 0; a < Ni; a++)
+              K[(size_t)(jang * nrad + fi + a) + (size_t)(kang * nrad + fj + b) * ntot] -= Ksub[a + b * Ni];
+        }
+    }
+  return 0;
+}
+
+}  // extern "C"
