@@ -113,3 +113,4 @@ def device_count():
 
 from .sadatom import SadatomBasis  # noqa: E402,F401
 from .atomic import AtomicBasis  # noqa: E402,F401
+from .diatomic import DiatomicBasis  # noqa: E402,F401

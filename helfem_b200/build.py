@@ -20,8 +20,8 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-fopenmp,-O2"]
 
 CU_SOURCES = ["csrc/capi_common.cu", "csrc/capi_sadatom.cu", "csrc/capi_sadatom_exchange.cu", "csrc/capi_xc.cu",
-              "csrc/chan_engine.cu", "csrc/capi_atomic.cu"]
-CPP_SOURCES = ["host/fem.cpp", "host/angular.cpp", "host/sadatom.cpp", "host/atomic.cpp", "host/hostapi.cpp"]
+              "csrc/chan_engine.cu", "csrc/capi_atomic.cu", "csrc/capi_diatomic.cu"]
+CPP_SOURCES = ["host/fem.cpp", "host/angular.cpp", "host/sadatom.cpp", "host/atomic.cpp", "host/legendre.cpp", "host/diatomic.cpp", "host/hostapi.cpp"]
 
 
 def _headers():

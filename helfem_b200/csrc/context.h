@@ -80,6 +80,7 @@ struct hfb200_ctx {
   int2* dTri = nullptr;
   // ---- atomic / diatomic: angular basis + channel engine (chan_engine.h) ----
   std::vector<int> lval, mval;
+  double Rhalf = 0.0;
   hfb::ChanEngine* chan = nullptr;
   // ---- scratch ----
   hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;

@@ -1,0 +1,75 @@
+"""ctypes view of hfb::diatomic::TwoDBasis (helfem_b200/host/diatomic.h), the host-side mirror of
+helfem::diatomic::basis::TwoDBasis (/root/reference/src/diatomic/basis.h).  Harness only."""
+import ctypes
+
+import numpy as np
+
+from . import lib, check_host, _p, _ip
+
+
+class DiatomicBasis:
+    """Arguments follow the reference's `diatomic` flags (/root/reference/src/diatomic/main.cpp:89-133):
+    lmax is an int (same for every |m| <= mmax) or a list of per-|m| maxima."""
+
+    def __init__(self, Z1, Z2, Rbond, nelem, nnodes=15, primbas=4, nquad=0, rmax=40.0, igrid=4, zexp=2.0, lmax=2, mmax=0,
+                 device=0):
+        L = lib()
+        L.hfh_diatomic_free.argtypes = [ctypes.c_void_p]
+        L.hfh_diatomic_free.restype = None
+        lm = np.ascontiguousarray([lmax] * (mmax + 1) if np.isscalar(lmax) else lmax, dtype=np.int32)
+        self._h = ctypes.c_void_p()
+        check_host(L.hfh_diatomic_new(ctypes.byref(self._h), int(Z1), int(Z2), ctypes.c_double(Rbond), int(primbas), int(nnodes),
+                                      int(nquad), int(nelem), ctypes.c_double(rmax), int(igrid), ctypes.c_double(zexp),
+                                      int(len(lm)), _ip(lm), int(device)))
+        v = [ctypes.c_int() for _ in range(6)]
+        check_host(L.hfh_diatomic_dims(self._h, *[ctypes.byref(x) for x in v]))
+        self.nbf, self.ndummy, self.nrad, self.nang, self.nel, self.nlm = [x.value for x in v]
+        self.Rhalf = 0.5 * Rbond
+        self.lval = np.zeros(self.nang, dtype=np.int32)
+        self.mval = np.zeros(self.nang, dtype=np.int32)
+        self.first = np.zeros(self.nel, dtype=np.int32)
+        self.last = np.zeros(self.nel, dtype=np.int32)
+        self.Lmap = np.zeros(self.nlm, dtype=np.int32)
+        self.Mmap = np.zeros(self.nlm, dtype=np.int32)
+        check_host(L.hfh_diatomic_tables(self._h, _ip(self.lval), _ip(self.mval), _ip(self.first), _ip(self.last),
+                                         _ip(self.Lmap), _ip(self.Mmap)))
+        self.have_ktei = False
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib().hfh_diatomic_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def pure_indices(self):
+        idx = []
+        for i, m in enumerate(self.mval):
+            idx.extend(range(i * self.nrad + (1 if m != 0 else 0), (i + 1) * self.nrad))
+        return np.asarray(idx)
+
+    def compute_tei(self, exchange=True):
+        check_host(lib().hfh_diatomic_compute_tei(self._h, int(bool(exchange))))
+        self.have_ktei = bool(exchange)
+
+    def tei(self, which, ilm, iel):
+        """which: 0 P0, 1 P2, 2 Q0, 3 Q2; 4..7 prim_tei 00,02,20,22; 8..11 prim_ktei."""
+        npe = int(self.last[iel] - self.first[iel] + 1)
+        n = npe if which < 4 else npe * npe
+        out = np.zeros((n, n), order="F")
+        check_host(lib().hfh_diatomic_get_tei(self._h, int(which), int(ilm), int(iel), _p(out)))
+        return out
+
+    def coulomb(self, P):
+        P = np.asfortranarray(P, dtype=np.float64)
+        J = np.zeros_like(P, order="F")
+        check_host(lib().hfh_diatomic_coulomb(self._h, _p(P), _p(J)))
+        return J
+
+    def exchange(self, P):
+        """returns -K like the reference"""
+        P = np.asfortranarray(P, dtype=np.float64)
+        K = np.zeros_like(P, order="F")
+        check_host(lib().hfh_diatomic_exchange(self._h, _p(P), _p(K)))
+        return K

@@ -2,11 +2,14 @@
 // (ctypes) can drive exactly the objects a C++ driver would use.  Every function returns 0 on
 // success; C++ exceptions are translated to a non-zero code (1 = std::logic_error,
 // 2 = std::runtime_error, 3 = other) and the message kept for hfh_last_error().
+#include <cmath>
 #include <cstring>
 #include <string>
 #include "../../include/helfem_b200.h"
 #include "angular.h"
 #include "atomic.h"
+#include "diatomic.h"
+#include "legendre.h"
 #include "sadatom.h"
 
 using namespace hfb;
@@ -72,6 +75,10 @@ void hfh_ylm(int l, int m, double cth, double phi, double* re, double* im) {
   *re = y.real();
   *im = y.imag();
 }
+
+/// out: (Mmax+1) x (Lmax+1), out[M*(Lmax+1)+L]
+void hfh_plm_array(int Lmax, int Mmax, double mu, double* out) { legendre::plm_array(Lmax, Mmax, mu, out); }
+void hfh_qlm_array(int Lmax, int Mmax, double mu, double* out) { legendre::qlm_array(Lmax, Mmax, mu, out); }
 
 // ---- sadatom ----
 int hfh_sadatom_new(void** out, int Z, int primbas, int nnodes, int nquad, int nelem, double rmax, int igrid, double zexp,
@@ -276,6 +283,93 @@ int hfh_atomic_coulomb(void* h, const double* P, double* J) {
 int hfh_atomic_exchange(void* h, const double* P, double* K) {
   HFH_TRY
   auto* b = (atomic::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Mat Pm(n, n);
+  memcpy(Pm.ptr(), P, n * n * sizeof(double));
+  Mat Km = b->exchange(Pm);
+  memcpy(K, Km.ptr(), n * n * sizeof(double));
+  HFH_CATCH
+}
+
+// ---- diatomic ----
+/// lmax_per_m: lmax for each |m| = 0..nm-1 (diatomic/main.cpp:255-273, lm_to_l_m basis.cpp:287-302)
+int hfh_diatomic_new(void** out, int Z1, int Z2, double Rbond, int primbas, int nnodes, int nquad, int nelem, double rmax,
+                     int igrid, double zexp, int nm, const int* lmax_per_m, int device) {
+  HFH_TRY
+  fem::PolyBasis poly(primbas, nnodes);
+  if (nquad <= 0) nquad = 5 * poly.get_nbf();
+  std::vector<int> lval, mval;
+  for (int mabs = 0; mabs < nm; mabs++)
+    for (int l = mabs; l <= lmax_per_m[mabs]; l++) {
+      lval.push_back(l);
+      mval.push_back(mabs);
+      if (mabs > 0) { lval.push_back(l); mval.push_back(-mabs); }
+    }
+  const double Rhalf = 0.5 * Rbond;
+  const double mumax = acosh(rmax / Rhalf);  // diatomic/main.cpp:275
+  Vec bval = fem::get_grid(mumax, nelem, igrid, zexp);
+  *out = new diatomic::TwoDBasis(Z1, Z2, Rhalf, poly, nquad, bval, lval, mval, device);
+  HFH_CATCH
+}
+void hfh_diatomic_free(void* h) { delete (diatomic::TwoDBasis*)h; }
+int hfh_diatomic_dims(void* h, int* nbf, int* ndummy, int* nrad, int* nang, int* nel, int* nlm) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
+  if (nbf) *nbf = (int)b->Nbf();
+  if (ndummy) *ndummy = (int)b->Ndummy();
+  if (nrad) *nrad = (int)b->Nrad();
+  if (nang) *nang = (int)b->Nang();
+  if (nel) *nel = (int)b->get_radial().Nel();
+  if (nlm) *nlm = (int)b->get_lm_map().size();
+  HFH_CATCH
+}
+int hfh_diatomic_tables(void* h, int* lval, int* mval, int* first, int* last, int* Lmap, int* Mmap) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
+  for (size_t a = 0; a < b->Nang(); a++) { lval[a] = b->get_lval()[a]; mval[a] = b->get_mval()[a]; }
+  for (size_t e = 0; e < b->get_radial().Nel(); e++) {
+    size_t f, l;
+    b->get_radial().get_idx(e, f, l);
+    first[e] = (int)f;
+    last[e] = (int)l;
+  }
+  for (size_t r = 0; r < b->get_lm_map().size(); r++) { Lmap[r] = b->get_lm_map()[r].first; Mmap[r] = b->get_lm_map()[r].second; }
+  HFH_CATCH
+}
+int hfh_diatomic_compute_tei(void* h, int exchange) {
+  HFH_TRY
+  ((diatomic::TwoDBasis*)h)->compute_tei(exchange != 0);
+  HFH_CATCH
+}
+/// which: 0 P0, 1 P2, 2 Q0, 3 Q2 (np x np); 4+ab prim_tei block ab, 8+ab prim_ktei block ab (np^2 x np^2)
+int hfh_diatomic_get_tei(void* h, int which, int ilm, int iel, double* out) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
+  const size_t idx = (size_t)ilm * b->get_radial().Nel() + iel;
+  const Mat* m = nullptr;
+  if (b->get_prim_tei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+  if (which < 4) m = &b->get_disjoint(which)[idx];
+  else if (which < 8) m = &b->get_prim_tei()[4 * idx + which - 4];
+  else {
+    if (b->get_prim_ktei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+    m = &b->get_prim_ktei()[4 * idx + which - 8];
+  }
+  memcpy(out, m->ptr(), m->size() * sizeof(double));
+  HFH_CATCH
+}
+int hfh_diatomic_coulomb(void* h, const double* P, double* J) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
+  const size_t n = b->Nbf();
+  Mat Pm(n, n);
+  memcpy(Pm.ptr(), P, n * n * sizeof(double));
+  Mat Jm = b->coulomb(Pm);
+  memcpy(J, Jm.ptr(), n * n * sizeof(double));
+  HFH_CATCH
+}
+int hfh_diatomic_exchange(void* h, const double* P, double* K) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
   const size_t n = b->Nbf();
   Mat Pm(n, n);
   memcpy(Pm.ptr(), P, n * n * sizeof(double));

@@ -123,6 +123,24 @@ int hfb200_atomic_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoint
 int hfb200_atomic_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
 int hfb200_atomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* K, int ldk);
 
+/* ------------------------------------------------------------------------------------------
+ * `diatomic` program (prolate spheroidal coordinates).  lval/mval: diatomic::basis::lm_to_l_m
+ * (diatomic/basis.cpp:287-302); radial = FEM in mu.  Lmap/Mmap: the sorted (L,|M|) table lm_map of
+ * TwoDBasis (diatomic/basis.cpp:336-376).  Stored integrals of TwoDBasis::compute_tei
+ * (diatomic/basis.cpp:1166-1302): disjoint_{P0,P2,Q0,Q2} as arrays of nlm*nel pointers, entry
+ * [ilm*nel+iel]; in-element blocks prim_tei{00,02,20,22} as one array of 4*nlm*nel pointers, entry
+ * [4*(ilm*nel+iel) + 2a+b] for family "ab" (a, b in {0,1} standing for 0 and 2); prim_ktei likewise or NULL.
+ * P, J, K: dense host matrices in the PURE basis (first radial function of every m != 0 shell
+ * removed, diatomic/basis.cpp:482-499); exchange returns -K like the reference.
+ * ------------------------------------------------------------------------------------------ */
+int hfb200_diatomic_create(hfb200_ctx** ctx, int device, int nang, const int* lval, const int* mval, int nel,
+                           const int* first, const int* last, double Rhalf);
+int hfb200_diatomic_set_tei(hfb200_ctx* ctx, int nlm, const int* Lmap, const int* Mmap, const double* const* P0,
+                            const double* const* P2, const double* const* Q0, const double* const* Q2,
+                            const double* const* prim_tei, const double* const* prim_ktei);
+int hfb200_diatomic_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
+int hfb200_diatomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* K, int ldk);
+
 /* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
  * outputs are overwritten with exchange + correlation). */
 int hfb200_xc_eval(int device, int x_func, int c_func, int nspin, int n, double dens_thr, const double* rho,

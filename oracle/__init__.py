@@ -180,3 +180,35 @@ class AtomicOracle:
         lib().oracle_atomic_exchange(self.nang, _ip(self.lval), _ip(self.mval), self.nel, _ip(self.first), _ip(self.last),
                                      _ptr_array(self.dL), _ptr_array(self.dm1L), _ptr_array(self.ktei), _p(P), _p(K))
         return K
+
+
+class DiatomicOracle:
+    """Reference algorithm of diatomic::basis::TwoDBasis::coulomb / exchange on the CPU (oracle/chan_oracle.cpp),
+    in the dummy space; `pure` gathers / scatters as expand_boundaries / remove_boundaries do.
+    dis: 4 lists (P0, P2, Q0, Q2) indexed [ilm*nel+iel]; tei, ktei: lists indexed [4*(ilm*nel+iel) + 2a+b]."""
+
+    def __init__(self, lval, mval, first, last, Lmap, Mmap, Rhalf, dis, tei, ktei, pure):
+        ci = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        self.lval, self.mval, self.first, self.last, self.Lmap, self.Mmap = map(ci, (lval, mval, first, last, Lmap, Mmap))
+        self.Rhalf = float(Rhalf)
+        self.dis = [[np.asfortranarray(a) for a in d] for d in dis]
+        self.tei = [np.asfortranarray(a) for a in tei]
+        self.ktei = None if ktei is None else [np.asfortranarray(a) for a in ktei]
+        self.pure = np.asarray(pure)
+        self.nd = len(self.lval) * (int(self.last[-1]) + 1)
+
+    def _apply(self, fn, teis, Ppure):
+        P = np.zeros((self.nd, self.nd), order="F")
+        P[np.ix_(self.pure, self.pure)] = Ppure
+        F = np.zeros_like(P, order="F")
+        rc = fn(len(self.lval), _ip(self.lval), _ip(self.mval), len(self.first), _ip(self.first), _ip(self.last), len(self.Lmap),
+                _ip(self.Lmap), _ip(self.Mmap), ctypes.c_double(self.Rhalf), _ptr_array(self.dis[0]), _ptr_array(self.dis[1]),
+                _ptr_array(self.dis[2]), _ptr_array(self.dis[3]), _ptr_array(teis), _p(P), _p(F))
+        assert rc == 0
+        return np.asfortranarray(F[np.ix_(self.pure, self.pure)])
+
+    def coulomb(self, P):
+        return self._apply(lib().oracle_diatomic_coulomb, self.tei, P)
+
+    def exchange(self, P):
+        return self._apply(lib().oracle_diatomic_exchange, self.ktei, P)

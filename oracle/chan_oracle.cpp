@@ -183,4 +183,208 @@ int oracle_atomic_exchange(int nang, const int* lval, const int* mval, int nel, 
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// diatomic: /root/reference/src/diatomic/basis.cpp:1359-1530 (coulomb), :1532-1733 (exchange).
+// Matrices are in the DUMMY space (nang*nrad); expand/remove_boundaries is done by the caller.
+// lm families sorted (L,|M|); disjoint arrays [ilm*nel+iel]; tei/ktei [4*(ilm*nel+iel) + 2a+b].
+// ---------------------------------------------------------------------------------------------
+static double mod_coeff(int lj, int mj, int L, int M, int li, int mi) {  // general/gaunt.cpp:167-180
+  static const double const0(2.0 / 3.0 * sqrt(M_PI));
+  static const double const2(4.0 / 15.0 * sqrt(5.0 * M_PI));
+  const double cpl0 = gcoeff(L, M, 0, 0, L, M) * gcoeff(lj, mj, li, mi, L, M);
+  double cpl2 = 0.0;
+  for (int Lp = std::max(std::max(L - 2, 0), std::abs(M)); Lp <= L + 2; Lp++) cpl2 += gcoeff(Lp, M, 2, 0, L, M) * gcoeff(lj, mj, li, mi, Lp, M);
+  return const0 * cpl0 + const2 * cpl2;
+}
+static int lmind(int nlm, const int* Lmap, const int* Mmap, int L, int M) {
+  M = std::abs(M);
+  for (int r = 0; r < nlm; r++)
+    if (Lmap[r] == L && Mmap[r] == M) return r;
+  return -1;
+}
+static double LMfac(double Rhalf, int L, int M) {  // basis.cpp:1421
+  M = std::abs(M);
+  double ratio = 1.0;
+  for (int p = L + M; p > L - M; p--) ratio *= p;
+  return 4.0 * M_PI * std::pow(Rhalf, 5) * std::pow(-1.0, M) / ratio;
+}
+
+int oracle_diatomic_coulomb(int nang, const int* lval, const int* mval, int nel, const int* first, const int* last, int nlm,
+                            const int* Lmap, const int* Mmap, double Rhalf, const double* const* P0, const double* const* P2,
+                            const double* const* Q0, const double* const* Q2, const double* const* tei, const double* P, double* J) {
+  const int nrad = last[nel - 1] + 1, ntot = nang * nrad;
+  const size_t n2 = (size_t)nrad * nrad;
+  // LM channels keyed (L, M)
+  std::vector<std::pair<int, int>> LM;
+  auto LMind = [&](int L, int M) {
+    for (size_t c = 0; c < LM.size(); c++)
+      if (LM[c].first == L && LM[c].second == M) return (int)c;
+    LM.push_back({L, M});
+    return (int)LM.size() - 1;
+  };
+  std::vector<vec> Paux0, Paux2;
+  for (int k = 0; k < nang; k++)
+    for (int l = 0; l < nang; l++) {
+      const int lk = lval[k], mk = mval[k], ll = lval[l], ml = mval[l], M = mk - ml;
+      for (int L = std::max(std::abs(lk - ll) - 2, std::abs(M)); L <= lk + ll + 2; L++) {
+        const int c = LMind(L, M);
+        if ((int)Paux0.size() <= c) { Paux0.resize(c + 1, vec(n2, 0.0)); Paux2.resize(c + 1, vec(n2, 0.0)); }
+        const double c0 = mod_coeff(lk, mk, L, M, ll, ml), c2 = gcoeff(lk, mk, L, M, ll, ml);
+        for (int b = 0; b < nrad; b++)
+          for (int a = 0; a < nrad; a++) {
+            const double p = P[(size_t)(k * nrad + a) + (size_t)(l * nrad + b) * ntot];
+            if (c0 != 0.0) Paux0[c][a + (size_t)b * nrad] += c0 * p;
+            if (c2 != 0.0) Paux2[c][a + (size_t)b * nrad] += c2 * p;
+          }
+      }
+    }
+  std::vector<vec> Jaux0(LM.size(), vec(n2, 0.0)), Jaux2(LM.size(), vec(n2, 0.0));
+  for (size_t c = 0; c < LM.size(); c++) {
+    const int L = LM[c].first, M = LM[c].second, ilm = lmind(nlm, Lmap, Mmap, L, M);
+    if (ilm < 0) return -1;
+    const double fac = LMfac(Rhalf, L, M);
+    for (int jel = 0; jel < nel; jel++) {
+      const int jf = first[jel], Nj = last[jel] - jf + 1;
+      vec Ps0((size_t)Nj * Nj), Ps2((size_t)Nj * Nj);
+      for (int b = 0; b < Nj; b++)
+        for (int a = 0; a < Nj; a++) {
+          Ps0[a + b * Nj] = Paux0[c][(jf + a) + (size_t)(jf + b) * nrad];
+          Ps2[a + b * Nj] = Paux2[c][(jf + a) + (size_t)(jf + b) * nrad];
+        }
+      auto trace = [&](const double* D, const vec& Ps) {
+        double t = 0.0;
+        for (int a = 0; a < Nj; a++)
+          for (int b = 0; b < Nj; b++) t += D[a + b * Nj] * Ps[b + a * Nj];
+        return t;
+      };
+      const double jsmall0 = fac * trace(P0[ilm * nel + jel], Ps0), jbig0 = fac * trace(Q0[ilm * nel + jel], Ps0);
+      const double jsmall2 = fac * trace(P2[ilm * nel + jel], Ps2), jbig2 = fac * trace(Q2[ilm * nel + jel], Ps2);
+      for (int iel = 0; iel < nel; iel++) {
+        if (iel == jel) continue;
+        const int f = first[iel], Ni = last[iel] - f + 1;
+        const double ifac0 = iel < jel ? jbig0 - jbig2 : jsmall0 - jsmall2;
+        const double* i0 = iel < jel ? P0[ilm * nel + iel] : Q0[ilm * nel + iel];
+        const double* i2 = iel < jel ? P2[ilm * nel + iel] : Q2[ilm * nel + iel];
+        for (int b = 0; b < Ni; b++)
+          for (int a = 0; a < Ni; a++) {
+            Jaux0[c][(f + a) + (size_t)(f + b) * nrad] += i0[a + b * Ni] * ifac0;
+            Jaux2[c][(f + a) + (size_t)(f + b) * nrad] -= i2[a + b * Ni] * ifac0;
+          }
+      }
+      const size_t m2 = (size_t)Nj * Nj;
+      const double* const* T = tei + 4 * (ilm * nel + jel);
+      for (size_t cc = 0; cc < m2; cc++)
+        for (size_t r = 0; r < m2; r++) {
+          const double j0 = fac * (T[0][r + cc * m2] * Ps0[cc] - T[1][r + cc * m2] * Ps2[cc]);
+          const double j2 = fac * (-T[2][r + cc * m2] * Ps0[cc] + T[3][r + cc * m2] * Ps2[cc]);
+          const int a = (int)(r % Nj), b = (int)(r / Nj);
+          Jaux0[c][(jf + a) + (size_t)(jf + b) * nrad] += j0;
+          Jaux2[c][(jf + a) + (size_t)(jf + b) * nrad] += j2;
+        }
+    }
+  }
+  std::fill(J, J + (size_t)ntot * ntot, 0.0);
+  for (int i = 0; i < nang; i++)
+    for (int j = 0; j < nang; j++) {
+      const int li = lval[i], mi = mval[i], lj = lval[j], mj = mval[j], M = mj - mi;
+      for (int L = std::max(std::abs(lj - li) - 2, std::abs(M)); L <= lj + li + 2; L++) {
+        const int c = LMind(L, M);
+        const double c0 = mod_coeff(lj, mj, L, M, li, mi), c2 = gcoeff(lj, mj, L, M, li, mi);
+        for (int b = 0; b < nrad; b++)
+          for (int a = 0; a < nrad; a++)
+            J[(size_t)(i * nrad + a) + (size_t)(j * nrad + b) * ntot] += c0 * Jaux0[c][a + (size_t)b * nrad] + c2 * Jaux2[c][a + (size_t)b * nrad];
+      }
+    }
+  return 0;
+}
+
+int oracle_diatomic_exchange(int nang, const int* lval, const int* mval, int nel, const int* first, const int* last, int nlm,
+                             const int* Lmap, const int* Mmap, double Rhalf, const double* const* P0, const double* const* P2,
+                             const double* const* Q0, const double* const* Q2, const double* const* ktei, const double* P, double* K) {
+  const int nrad = last[nel - 1] + 1, ntot = nang * nrad;
+  const size_t n2 = (size_t)nrad * nrad;
+  std::fill(K, K + (size_t)ntot * ntot, 0.0);
+#ifdef _OPENMP
+#pragma omp parallel for collapse(2) schedule(dynamic)
+#endif
+  for (int jang = 0; jang < nang; jang++)
+    for (int kang = 0; kang < nang; kang++) {
+      const int lj = lval[jang], mj = mval[jang], lk = lval[kang], mk = mval[kang];
+      std::vector<vec> R[4];
+      for (int ab = 0; ab < 4; ab++) R[ab].assign(nlm, vec());
+      std::vector<bool> couple(nlm, false);
+      for (int iang = 0; iang < nang; iang++)
+        for (int lang = 0; lang < nang; lang++) {
+          const int li = lval[iang], mi = mval[iang], ll = lval[lang], ml = mval[lang];
+          const int M = mj - mi;
+          if (M != mk - ml) continue;
+          double nrm = 0.0;
+          for (int b = 0; b < nrad; b++)
+            for (int a = 0; a < nrad; a++) {
+              const double v = P[(size_t)(iang * nrad + a) + (size_t)(lang * nrad + b) * ntot];
+              nrm += v * v;
+            }
+          if (std::sqrt(nrm) < 10 * 2.220446049250313e-16) continue;
+          const int Lmin = std::max(std::max(std::abs(li - lj), std::abs(lk - ll)) - 2, std::abs(M));
+          const int Lmax = std::min(li + lj, lk + ll) + 2;
+          for (int L = Lmin; L <= Lmax; L++) {
+            const double mji = mod_coeff(lj, mj, L, M, li, mi), gji = gcoeff(lj, mj, L, M, li, mi);
+            const double mkl = mod_coeff(lk, mk, L, M, ll, ml), gkl = gcoeff(lk, mk, L, M, ll, ml);
+            const double cpl[4] = {mji * mkl, -mji * gkl, -gji * mkl, gji * gkl};
+            if (cpl[0] == 0.0 && cpl[1] == 0.0 && cpl[2] == 0.0 && cpl[3] == 0.0) continue;
+            const int ilm = lmind(nlm, Lmap, Mmap, L, M);
+            const double fac = LMfac(Rhalf, L, M);
+            for (int ab = 0; ab < 4; ab++) {
+              if (R[ab][ilm].empty()) R[ab][ilm].assign(n2, 0.0);
+              for (int b = 0; b < nrad; b++)
+                for (int a = 0; a < nrad; a++)
+                  R[ab][ilm][a + (size_t)b * nrad] += (fac * cpl[ab]) * P[(size_t)(iang * nrad + a) + (size_t)(lang * nrad + b) * ntot];
+            }
+            couple[ilm] = true;
+          }
+        }
+      for (int iel = 0; iel < nel; iel++)
+        for (int jel = 0; jel < nel; jel++) {
+          const int fi = first[iel], fj = first[jel], Ni = last[iel] - fi + 1, Nj = last[jel] - fj + 1;
+          vec Ksub((size_t)Ni * Nj, 0.0);
+          for (int ilm = 0; ilm < nlm; ilm++) {
+            if (!couple[ilm]) continue;
+            for (int ab = 0; ab < 4; ab++) {
+              const vec& Rm = R[ab][ilm];
+              const int a_ = ab >> 1, b_ = ab & 1;
+              if (iel == jel) {
+                const size_t m2 = (size_t)Ni * Nj;
+                const double* T = ktei[4 * (ilm * nel + iel) + ab];
+                for (int b = 0; b < Nj; b++)
+                  for (int a = 0; a < Ni; a++) {
+                    const double pv = Rm[(fi + a) + (size_t)(fj + b) * nrad];
+                    const size_t c = a + (size_t)b * Ni;
+                    for (size_t r = 0; r < m2; r++) Ksub[r] += T[r + c * m2] * pv;
+                  }
+              } else {
+                // iel > jel: iel gets Q, jel gets P (:1703-1707)
+                const double* iint = (iel > jel) ? (a_ ? Q2 : Q0)[ilm * nel + iel] : (a_ ? P2 : P0)[ilm * nel + iel];
+                const double* jint = (iel > jel) ? (b_ ? P2 : P0)[ilm * nel + jel] : (b_ ? Q2 : Q0)[ilm * nel + jel];
+                vec T((size_t)Ni * Nj, 0.0);
+                for (int k = 0; k < Nj; k++)
+                  for (int b = 0; b < Nj; b++) {
+                    const double jv = jint[k + b * Nj];
+                    for (int a = 0; a < Ni; a++) T[a + k * Ni] += Rm[(fi + a) + (size_t)(fj + b) * nrad] * jv;
+                  }
+                for (int k = 0; k < Nj; k++)
+                  for (int c = 0; c < Ni; c++) {
+                    const double tv = T[c + k * Ni];
+                    for (int a = 0; a < Ni; a++) Ksub[a + k * Ni] += iint[a + c * Ni] * tv;
+                  }
+              }
+            }
+          }
+          for (int b = 0; b < Nj; b++)
+            for (int a = 0; a < Ni; a++)
+              K[(size_t)(jang * nrad + fi + a) + (size_t)(kang * nrad + fj + b) * ntot] -= Ksub[a + b * Ni];
+        }
+    }
+  return 0;
+}
+
 }  // extern "C"
