@@ -69,6 +69,10 @@ class AtomicBasis:
         check_host(lib().hfh_atomic_get_tei(self._h, int(L), int(iel), _p(a), _p(b), _p(t), _p(k) if k is not None else None))
         return a, b, t, k
 
+    def set_shard(self, rank, nranks):
+        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""
+        check_host(lib().hfh_atomic_set_shard(self._h, int(rank), int(nranks)))
+
     def coulomb(self, P):
         P = np.asfortranarray(P, dtype=np.float64)
         J = np.zeros_like(P, order="F")

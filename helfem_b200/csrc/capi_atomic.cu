@@ -81,16 +81,19 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
     for (int l = 0; l < nang; l++) {
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;
       for (int L = std::max(std::abs(lk - ll), std::abs(M)); L <= lk + ll; L++) {
+        if (L % c->shard_n != c->shard_rank) continue;  // family owned by another rank
         const double g = angular::gaunt_coefficient(lk, mk, L, M, ll, ml);
         if (g == 0.0) continue;
         S.pair_coupl[(size_t)k * nang + l].push_back({chan_of[(size_t)L * (2 * Mmax + 1) + M + Mmax], {g, 0.0}});
       }
     }
   const int nel = c->nel;
-  S.tei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return prim_tei[r * nel + e]; };
-  if (prim_ktei) S.ktei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return prim_ktei[r * nel + e]; };
-  S.small_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return disjoint_L[r * nel + e]; };
-  S.big_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return disjoint_m1L[r * nel + e]; };
+  const int sr = c->shard_rank, sn = c->shard_n;
+  typedef const double* cptr;
+  S.tei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return r % sn == sr ? prim_tei[r * nel + e] : (cptr) nullptr; };
+  if (prim_ktei) S.ktei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return r % sn == sr ? prim_ktei[r * nel + e] : (cptr) nullptr; };
+  S.small_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return r % sn == sr ? disjoint_L[r * nel + e] : (cptr) nullptr; };
+  S.big_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return r % sn == sr ? disjoint_m1L[r * nel + e] : (cptr) nullptr; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
   const int rc = c->chan->build(S, prim_ktei != nullptr);

@@ -41,6 +41,18 @@ int hfb200_device_count(void) {
   return n;
 }
 
+/* Multi-GPU sharding of the atomic / diatomic operators: this context only holds and contracts the
+ * integral families r with r % nranks == rank (atomic: r = L; diatomic: r = index of (L,|M|)); the
+ * results of the ranks add up to the full J / K (the caller all-reduces them, NCCL over NVLink).
+ * Must be called before *_set_tei. */
+int hfb200_set_shard(hfb200_ctx* c, int rank, int nranks) {
+  if (!c || nranks < 1 || rank < 0 || rank >= nranks) { hfb::set_error("hfb200_set_shard: invalid argument"); return HFB200_EINVAL; }
+  if (c->chan) { hfb::set_error("hfb200_set_shard must precede set_tei"); return HFB200_EINVAL; }
+  c->shard_rank = rank;
+  c->shard_n = nranks;
+  return HFB200_OK;
+}
+
 void hfb200_destroy(hfb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);

@@ -116,16 +116,19 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
     for (int l = 0; l < nang; l++) {
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;
       for (int L = std::max(std::abs(lk - ll) - 2, std::abs(M)); L <= lk + ll + 2; L++) {
+        if (fam[{L, std::abs(M)}] % c->shard_n != c->shard_rank) continue;  // family owned by another rank
         const double c0 = mod_coeff(lk, mk, L, M, ll, ml), c2 = gcoeff(lk, mk, L, M, ll, ml);
         if (c0 == 0.0 && c2 == 0.0) continue;
         S.pair_coupl[(size_t)k * nang + l].push_back({chan_tmp[{fam[{L, std::abs(M)}], M}], {c0, c2}});
       }
     }
   // stacked integrals: fac [[T00, -T02], [-T20, T22]],  s = fac [P0; -P2],  b = [Q0; -Q2]
-  S.tei = [=](int r, int e, int ho, int hi, double* sg) { *sg = (ho != hi) ? -1.0 : 1.0; return prim_tei[4 * (r * nel + e) + 2 * ho + hi]; };
-  if (prim_ktei) S.ktei = [=](int r, int e, int a, int b, double* sg) { *sg = 1.0; return prim_ktei[4 * (r * nel + e) + 2 * a + b]; };
-  S.small_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return h ? P2[r * nel + e] : P0[r * nel + e]; };
-  S.big_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return h ? Q2[r * nel + e] : Q0[r * nel + e]; };
+  const int sr = c->shard_rank, sn = c->shard_n;
+  typedef const double* cptr;
+  S.tei = [=](int r, int e, int ho, int hi, double* sg) { *sg = (ho != hi) ? -1.0 : 1.0; return r % sn == sr ? prim_tei[4 * (r * nel + e) + 2 * ho + hi] : (cptr) nullptr; };
+  if (prim_ktei) S.ktei = [=](int r, int e, int a, int b, double* sg) { *sg = 1.0; return r % sn == sr ? prim_ktei[4 * (r * nel + e) + 2 * a + b] : (cptr) nullptr; };
+  S.small_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return r % sn != sr ? (cptr) nullptr : h ? P2[r * nel + e] : P0[r * nel + e]; };
+  S.big_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return r % sn != sr ? (cptr) nullptr : h ? Q2[r * nel + e] : Q0[r * nel + e]; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
   const int rc = c->chan->build(S, prim_ktei != nullptr);

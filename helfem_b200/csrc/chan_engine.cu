@@ -55,6 +55,7 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
           double sgs = 1.0, sgb = 1.0;
           const double* a = S.small_f(r, e, h, &sgs);
           const double* b = S.big_f(r, e, h, &sgb);
+          if (!a || !b) continue;  // family not owned by this shard
           for (int m = 0; m < ntri; m++) {
             const int i = tri[m].x, j = tri[m].y;
             if (j >= npe) continue;
@@ -151,6 +152,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
           double s1 = 1.0, s2 = 1.0;
           const double* a = S.small_f(r, e, h, &s1);
           const double* b = S.big_f(r, e, h, &s2);
+          if (!a || !b) continue;  // family not owned by this shard
           // signs of the stacked Coulomb vectors do not apply here: exchange signs live in the couplings
           for (int j = 0; j < npe[e]; j++)
             for (int i = 0; i < npe[e]; i++) {

@@ -81,6 +81,7 @@ struct hfb200_ctx {
   // ---- atomic / diatomic: angular basis + channel engine (chan_engine.h) ----
   std::vector<int> lval, mval;
   double Rhalf = 0.0;
+  int shard_rank = 0, shard_n = 1;  // integral families r with r % shard_n == shard_rank are owned
   hfb::ChanEngine* chan = nullptr;
   // ---- scratch ----
   hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;

@@ -61,6 +61,10 @@ class DiatomicBasis:
         check_host(lib().hfh_diatomic_get_tei(self._h, int(which), int(ilm), int(iel), _p(out)))
         return out
 
+    def set_shard(self, rank, nranks):
+        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""
+        check_host(lib().hfh_diatomic_set_shard(self._h, int(rank), int(nranks)))
+
     def coulomb(self, P):
         P = np.asfortranarray(P, dtype=np.float64)
         J = np.zeros_like(P, order="F")

@@ -109,6 +109,7 @@ hfb200_ctx* TwoDBasis::context() const {
       last[iel] = (int)l;
     }
     throw_status(hfb200_atomic_create(&ctx, device, (int)lval.size(), lval.data(), mval.data(), (int)Nel, first.data(), last.data()));
+    throw_status(hfb200_set_shard(ctx, shard_rank, shard_n));
   }
   if (!tei_uploaded && !prim_tei.empty()) {
     std::vector<const double*> a, b, t, k;

@@ -47,6 +47,8 @@ class TwoDBasis {
   const std::vector<Mat>& get_prim_tei() const { return prim_tei; }
   const std::vector<Mat>& get_prim_ktei() const { return prim_ktei; }
   int get_nL() const { return nL_stored; }
+  /// multi-GPU: this object contracts only the integral families r % nranks == rank (see hfb200_set_shard)
+  void set_shard(int rank, int nranks) { shard_rank = rank; shard_n = nranks; }
   hfb200_ctx* context() const;
 
  private:
@@ -56,6 +58,7 @@ class TwoDBasis {
   fem::RadialBasis radial;
   int nL_stored = 0;
   std::vector<Mat> disjoint_L, disjoint_m1L, prim_tei, prim_ktei;  // index [L*Nel+iel]
+  int shard_rank = 0, shard_n = 1;
   mutable hfb200_ctx* ctx = nullptr;
   mutable bool tei_uploaded = false;
 };

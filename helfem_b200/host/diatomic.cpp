@@ -245,6 +245,7 @@ hfb200_ctx* TwoDBasis::context() const {
     }
     throw_status(hfb200_diatomic_create(&ctx, device, (int)lval.size(), lval.data(), mval.data(), (int)Nel, first.data(),
                                         last.data(), Rhalf));
+    throw_status(hfb200_set_shard(ctx, shard_rank, shard_n));
   }
   if (!tei_uploaded && !prim_tei.empty()) {
     std::vector<int> Lm, Mm;

@@ -80,6 +80,8 @@ class TwoDBasis {
   const std::vector<Mat>& get_disjoint(int which) const { return disjoint[which]; }  // 0 P0, 1 P2, 2 Q0, 3 Q2
   const std::vector<Mat>& get_prim_tei() const { return prim_tei; }
   const std::vector<Mat>& get_prim_ktei() const { return prim_ktei; }
+  /// multi-GPU: this object contracts only the integral families r % nranks == rank (see hfb200_set_shard)
+  void set_shard(int rank, int nranks) { shard_rank = rank; shard_n = nranks; }
   hfb200_ctx* context() const;
 
  private:
@@ -90,6 +92,7 @@ class TwoDBasis {
   std::vector<lmidx_t> lm_map;  // sorted (L,|M|)
   std::vector<Mat> disjoint[4];
   std::vector<Mat> prim_tei, prim_ktei;
+  int shard_rank = 0, shard_n = 1;
   mutable hfb200_ctx* ctx = nullptr;
   mutable bool tei_uploaded = false;
 };

@@ -378,4 +378,15 @@ int hfh_diatomic_exchange(void* h, const double* P, double* K) {
   HFH_CATCH
 }
 
+int hfh_atomic_set_shard(void* h, int rank, int n) {
+  HFH_TRY
+  ((atomic::TwoDBasis*)h)->set_shard(rank, n);
+  HFH_CATCH
+}
+int hfh_diatomic_set_shard(void* h, int rank, int n) {
+  HFH_TRY
+  ((diatomic::TwoDBasis*)h)->set_shard(rank, n);
+  HFH_CATCH
+}
+
 }  // extern "C"

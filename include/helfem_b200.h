@@ -74,6 +74,11 @@ int hfb200_sadatom_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoin
                            const double* const* disjoint_m1L, const double* const* prim_tei,
                            const double* const* prim_ktei);
 void hfb200_destroy(hfb200_ctx* ctx);
+/* Multi-GPU sharding of the atomic / diatomic operators (one process per GPU): the context only holds and
+ * contracts the integral families r with r % nranks == rank (atomic: r = L; diatomic: r = index of
+ * (L,|M|) in lm_map); the partial J / K of the ranks add up to the full operator and are all-reduced by
+ * the caller (NCCL over NVLink).  Call before *_set_tei. */
+int hfb200_set_shard(hfb200_ctx* ctx, int rank, int nranks);
 
 /* J = coulomb(P): P, J are nrad x nrad (host). */
 int hfb200_sadatom_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
