@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhelfem_b200.so")
+# HELFEM_B200_LIB: a tuning variant built by tools/build_variant.py (A/B runs); default = the in-tree build
+LIB_PATH = os.environ.get("HELFEM_B200_LIB") or os.path.join(_HERE, "libhelfem_b200.so")
 
 _lib = None
 

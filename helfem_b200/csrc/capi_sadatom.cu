@@ -49,12 +49,12 @@ int launch_grid_fs(const SadGridParams& prm, int nwarps, size_t smem, cudaStream
 }
 
 int launch_grid(int fam, int nspin, const SadGridParams& prm, cudaStream_t st) {
-  // one warp per build; up to 8 builds share a CTA's staged tables
-  int nwarps = prm.nb < 8 ? prm.nb : 8;
-  size_t smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps);
+  // one warp per build; up to HFB_GRID_WARPS builds share a CTA's staged tables
+  int nwarps = prm.nb < HFB_GRID_WARPS ? prm.nb : HFB_GRID_WARPS;
+  size_t smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps, prm.jKP);
   while (smem > 227 * 1024 && nwarps > 1) {
     nwarps >>= 1;
-    smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps);
+    smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps, prm.jKP);
   }
   if (smem > 227 * 1024) { set_error("element tables need %zu bytes of shared memory (>227 KB)", smem); return HFB200_EINVAL; }
   if (nspin == 1) {
@@ -67,9 +67,11 @@ int launch_grid(int fam, int nspin, const SadGridParams& prm, cudaStream_t st) {
   return launch_grid_fs<xc::FAM_MGGA, 2>(prm, nwarps, smem, st);
 }
 
-int launch_coulomb(const SadJParams& q, cudaStream_t st) {
-  sad_jpack_kernel<<<dim3(q.nel, q.nb), 128, 0, st>>>(q);
-  HFB_CUDA_OK(cudaGetLastError());
+int launch_coulomb(const SadJParams& q, bool pack, cudaStream_t st) {
+  if (pack) {  // otherwise the grid kernel of the same build has already written pc / traces
+    sad_jpack_kernel<<<dim3(q.nel, q.nb), 128, 0, st>>>(q);
+    HFB_CUDA_OK(cudaGetLastError());
+  }
   const int rts = (q.MT + 3) / 4;
   if (q.nb <= 8) {
     sad_jmma_kernel<true, 1><<<dim3(q.nel * rts, 1), 256, 0, st>>>(q);
@@ -278,6 +280,13 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
   HFB_CUDA_OK(cudaSetDevice(c->device));
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
+  if (dJ_band) {
+    if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * 4 * c->jKS))) return rc;
+    if ((rc = c->dTraces.reserve((size_t)nbatch * c->nel * 2))) return rc;
+  }
+  // J and Vxc in one build: the grid kernel emits the folded density + traces of the Coulomb kernel, P is read once
+  const bool fused_pack = dJ_band && dH_band;
   if (dH_band) {
     int fam = 0;
     if (!valid_pair(x_func, c_func, &fam)) {
@@ -291,6 +300,9 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
     g.nslices = nslices; g.nb = nbatch;
     g.x_func = x_func; g.c_func = c_func; g.dens_thr = dens_thr;
     g.P = dP_band; g.H = dH_band; g.partial = c->dPartial.p;
+    g.pc = fused_pack ? c->dPtot.p : nullptr;
+    g.traces = c->dTraces.p; g.dLc = c->dLc; g.dm1Lc = c->dm1Lc; g.tri = c->dTri;
+    g.ntri = c->ntri; g.jKP = fused_pack ? 4 * c->jKS : 0; g.jMP = 8 * c->jMT;
     if ((rc = launch_grid(fam, nspin, g, st))) return rc;
     if (dScalars) {
       sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(c->dPartial.p, c->nel, dScalars);
@@ -298,15 +310,12 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
     }
   }
   if (dJ_band) {
-    if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * 4 * c->jKS))) return rc;
-    if ((rc = c->dTraces.reserve((size_t)nbatch * c->nel * 2))) return rc;
     SadJParams q;
     q.teiF = c->dTeiF; q.dLc = c->dLc; q.dm1Lc = c->dm1Lc; q.tri = c->dTri;
     q.nel = c->nel; q.np_max = c->np_max; q.ntri = c->ntri; q.MT = c->jMT; q.KS = c->jKS;
     q.nslices = nslices; q.nspin = nspin; q.nb = nbatch;
     q.P = dP_band; q.pc = c->dPtot.p; q.traces = c->dTraces.p; q.J = dJ_band;
-    if ((rc = launch_coulomb(q, st))) return rc;
+    if ((rc = launch_coulomb(q, !fused_pack, st))) return rc;
   }
   return HFB200_OK;
 }

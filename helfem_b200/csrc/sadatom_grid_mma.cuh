@@ -10,17 +10,24 @@
 //
 // A CTA owns one element: its B / dB tables (np_pad x ldq, zero padded) are staged once in
 // shared memory and shared by the CTA's warps, each of which carries its own build through
-// the three stages with warp-level synchronisation only:
-//   1. Q^T = B^T P  (points x functions; A operand = table, B operand = density block in
-//      registers), contracted with B / dB in the accumulator layout -> rho, d rho, tau per
-//      point (quad shuffles, fixed order => deterministic);
+// the stages with warp-level synchronisation only:
+//   0. the (spin, l) slices of the element block of P are streamed from HBM with fully coalesced
+//      loads (all slices of 8 column groups in flight), summed over l and parked in a per-warp
+//      shared block (row stride ldp = 4 mod 16); when the Coulomb kernel follows in the same
+//      Fock build, the triangle-folded total density and the two disjoint traces it needs
+//      (sadatom_coulomb_mma.cuh) are emitted from that block, so P is read from HBM ONCE;
+//   1. Q^T = B^T P  (points x functions; A operand = table, B operand = density block),
+//      contracted with B / dB in the accumulator layout -> rho, d rho, tau per point (one
+//      quad shuffle per point tile, fixed order => deterministic);
 //   2. XC on the points (lanes stride the points), potentials folded into quadrature weights;
 //   3. H = B (a B + g dB)^T + dB (g B + c dB)^T  [+ Hl = B dl B^T], upper tile triangle only,
-//      written to every l slice as H + l(l+1) Hl.
-// Table row stride ldq = 4 (mod 16) doubles makes all three fragment access patterns
+//      mirrored into the per-warp shared block and written to every l slice as H + l(l+1) Hl
+//      with fully coalesced stores.
+// Table row stride ldq = 4 (mod 16) doubles makes all fragment access patterns
 // shared-memory-bank-conflict free.
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdio>
 #include "xc_point.cuh"
 
 namespace hfb {
@@ -38,7 +45,22 @@ struct SadGridParams {
   const double* P;     // [nb][nspin][nslices][nel][np_max^2]
   double* H;           // same shape
   double* partial;     // [nb][nel][4]  Exc, Nel, tau integral, unused
+  // optional by-product for the Coulomb kernel that follows (null: not wanted), sadatom_coulomb_mma.cuh
+  double* pc;          // [nb][nel][jKP]  triangle-folded total density
+  double* traces;      // [nb][nel][2]    Lfac tr(dL P), Lfac tr(dm1L P)
+  const double* dLc;   // [nel][jMP]
+  const double* dm1Lc; // [nel][jMP]
+  const int2* tri;     // [ntri]
+  int ntri, jKP, jMP;
 };
+
+// tuning knobs (tools/build_variant.py): builds (= warps) per CTA, resident CTAs per SM the register budget is cut for
+#ifndef HFB_GRID_WARPS
+#define HFB_GRID_WARPS 8
+#endif
+#ifndef HFB_GRID_MINBLOCKS
+#define HFB_GRID_MINBLOCKS 2
+#endif
 
 __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
   // not volatile: the scheduler may interleave independent accumulator chains
@@ -51,14 +73,24 @@ __device__ __forceinline__ double quad_sum(double v) {
   return v;
 }
 
+/// row stride of the per-warp density / Fock block: >= np_pad and = 4 (mod 16)
+__host__ __device__ constexpr int sad_grid_ldp(int np_pad) { return np_pad <= 20 ? 20 : 36; }
+
 // FAM: highest functional family; NSPIN: 1 or 2; NT: 8-row tiles of the element block (np_pad = 8 NT).
 template <int FAM, int NSPIN, int NT>
-__global__ void __launch_bounds__(256) sad_grid_mma_kernel(SadGridParams prm) {
+__global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_grid_mma_kernel(SadGridParams prm) {
   extern __shared__ double smem[];
   constexpr bool GGA = (FAM >= xc::FAM_GGA);
   constexpr bool MGGA = (FAM >= xc::FAM_MGGA);
   constexpr int KS = 2 * NT;                   // k-steps over the functions of an element
   constexpr int NARR = 1 + (GGA ? 1 : 0) + (MGGA ? 2 : 0);  // per-spin per-point arrays
+  constexpr int LDP = sad_grid_ldp(8 * NT);
+  constexpr int PBLK = 8 * NT * LDP;           // one density / Fock block
+  constexpr int NBLK = MGGA ? 2 : 1;           // + the l(l+1)-weighted one
+  // coalesced block transfers: LW lanes walk down a column, 32/LW columns per pass
+  constexpr int LW = (NT == 1) ? 8 : (NT == 2 ? 16 : 32);
+  constexpr int CPI = 32 / LW;
+  constexpr int NPASS = 8 * NT / CPI;
   const int el = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   const int gid = lane >> 2, t4 = lane & 3;
@@ -67,7 +99,12 @@ __global__ void __launch_bounds__(256) sad_grid_mma_kernel(SadGridParams prm) {
 
   double* sB = smem;
   double* sdB = sB + tabsz;  // only touched if GGA
-  double* scratch = sB + (GGA ? 2 : 1) * tabsz + (size_t)warp * (NSPIN * NARR * nq8);
+  // Coulomb by-product constants of this element: disjoint_L | disjoint_m1L (triangle packed) | (i,j) of m
+  double* sDL = sB + (GGA ? 2 : 1) * tabsz;
+  double* sDM = sDL + prm.jKP;
+  int2* sTri = reinterpret_cast<int2*>(sDM + prm.jKP);
+  double* scratch = sDL + 3 * prm.jKP + (size_t)warp * (NSPIN * NARR * nq8 + NBLK * PBLK);
+  double* pblk = scratch + NSPIN * NARR * nq8;
 
   // ---- stage the element tables (whole CTA) ----
   {
@@ -77,80 +114,161 @@ __global__ void __launch_bounds__(256) sad_grid_mma_kernel(SadGridParams prm) {
       const double* gdB = prm.dBt + (size_t)el * tabsz;
       for (int k = tid; k < tabsz; k += blockDim.x) sdB[k] = gdB[k];
     }
+    if (prm.pc != nullptr) {
+      for (int m = tid; m < prm.jKP; m += blockDim.x) {
+        const bool ok = m < prm.ntri;
+        sDL[m] = ok ? prm.dLc[(size_t)el * prm.jMP + m] : 0.0;
+        sDM[m] = ok ? prm.dm1Lc[(size_t)el * prm.jMP + m] : 0.0;
+        sTri[m] = ok ? prm.tri[m] : make_int2(0, 0);
+      }
+    }
   }
   __syncthreads();
   const int b = blockIdx.y * nwarps + warp;
   if (b >= prm.nb) return;  // no block-level synchronisation below
 
+#ifdef HFB_GRID_PROFILE
+  long long tk[8]; int tki = 0;
+#define HFB_TICK() tk[tki++] = clock64()
+#else
+#define HFB_TICK()
+#endif
+  HFB_TICK();
   const size_t slice_stride = (size_t)prm.nel * np2;
   const int MT = nq8 >> 3;
+  const int brow = lane & (LW - 1), bcol0 = lane / LW;  // this lane's row / first column in block transfers
+  const bool brow_ok = brow < np;
 
-  // ================= stage 1: density, gradient, tau on the points =================
-  for (int k = lane; k < NSPIN * NARR * nq8; k += 32) scratch[k] = 0.0;
-  __syncwarp();
+  // ================= stages 0 + 1: density, gradient, tau on the points =================
 #pragma unroll 1
   for (int s = 0; s < NSPIN; s++) {
     const double* gP = prm.P + ((size_t)(b * NSPIN + s) * prm.nslices * prm.nel + el) * np2;
     double* aR = scratch + (size_t)s * NARR * nq8;  // rho | g | t1 | t2
-#pragma unroll 1
-    for (int ni = 0; ni < NT; ni++) {
-      // B operand: Bop[k][n] = P(n, k), n = 8 ni + gid, k = 4 ks + t4  (summed over l)
-      double pf[KS], plf[MGGA ? KS : 1];
-      const int n = 8 * ni + gid;
+    // ---- stage 0: sum the l slices of the block into shared memory ----
+    {
+      double acc[NPASS], accl[MGGA ? NPASS : 1];
+#pragma unroll
+      for (int it = 0; it < NPASS; it++) { acc[it] = 0.0; if (MGGA) accl[it] = 0.0; }
+      for (int l = 0; l < prm.nslices; l++) {
+        const double* src = gP + (size_t)l * slice_stride + brow;
+        double v[NPASS];
+#pragma unroll
+        for (int it = 0; it < NPASS; it++) {
+          const int col = it * CPI + bcol0;
+          v[it] = (brow_ok && col < np) ? __ldg(src + col * np) : 0.0;
+        }
+        const double ll = (double)(l * (l + 1));
+#pragma unroll
+        for (int it = 0; it < NPASS; it++) {
+          acc[it] += v[it];
+          if (MGGA) accl[it] = fma(ll, v[it], accl[it]);
+        }
+      }
+      __syncwarp();  // previous users of the block (stage 1 of the other spin) are done
+      if (brow < 8 * NT) {
+#pragma unroll
+        for (int it = 0; it < NPASS; it++) {
+          const int col = it * CPI + bcol0;
+          pblk[col * LDP + brow] = acc[it];
+          if (MGGA) pblk[PBLK + col * LDP + brow] = accl[it];
+        }
+      }
+      __syncwarp();
+    }
+    if (s == 0) { HFB_TICK(); }
+    // ---- by-product: folded total density and disjoint traces for the Coulomb kernel ----
+    if (prm.pc != nullptr) {
+      double* gpc = prm.pc + ((size_t)b * prm.nel + el) * prm.jKP;
+      double ts = 0.0, tb = 0.0;
+      for (int m = lane; m < prm.jKP; m += 32) {
+        const int2 ij = sTri[m];
+        double v = 0.0;
+        if (m < prm.ntri) {
+          v = pblk[ij.y * LDP + ij.x];
+          if (ij.x != ij.y) v += pblk[ij.x * LDP + ij.y];
+          if (NSPIN == 2 && s > 0) v += gpc[m];
+        }
+        ts = fma(sDL[m], v, ts);
+        tb = fma(sDM[m], v, tb);
+        gpc[m] = v;
+      }
+      if (s == NSPIN - 1) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          ts += __shfl_xor_sync(0xffffffffu, ts, o);
+          tb += __shfl_xor_sync(0xffffffffu, tb, o);
+        }
+        if (lane == 0) {
+          const double Lfac = 4.0 * HFB_PI;
+          prm.traces[((size_t)b * prm.nel + el) * 2 + 0] = Lfac * ts;
+          prm.traces[((size_t)b * prm.nel + el) * 2 + 1] = Lfac * tb;
+        }
+      }
+    }
+    if (s == 0) { HFB_TICK(); }
+    // ---- stage 1: B operand fragments Bop[k][n] = P(n, k), n = 8 ni + gid, k = 4 ks + t4 ----
+    // held in registers across the point tiles when they fit, else re-read from the shared block per use
+    constexpr bool PREG = (NT * KS * (MGGA ? 2 : 1) <= 16);
+    double pf[PREG ? NT : 1][PREG ? KS : 1], plf[(PREG && MGGA) ? NT : 1][(PREG && MGGA) ? KS : 1];
+    const double* pfs = pblk + t4 * LDP + gid;
+    if (PREG) {
+#pragma unroll
+      for (int ni = 0; ni < NT; ni++)
+#pragma unroll
+        for (int ks = 0; ks < KS; ks++) {
+          pf[ni][ks] = pfs[4 * ks * LDP + 8 * ni];
+          if (MGGA) plf[ni][ks] = pfs[PBLK + 4 * ks * LDP + 8 * ni];
+        }
+    }
+#pragma unroll 2
+    for (int mi = 0; mi < MT; mi++) {
+      const double* ab = sB + (size_t)t4 * ldq + 8 * mi + gid;
+      const double* ad = sdB + (size_t)t4 * ldq + 8 * mi + gid;
+      double av[KS], adv[MGGA ? KS : 1];
 #pragma unroll
       for (int ks = 0; ks < KS; ks++) {
-        const int k = 4 * ks + t4;
-        double p = 0.0, pl = 0.0;
-        if (n < np && k < np) {
-          const double* src = gP + n + (size_t)k * np;
-          for (int l = 0; l < prm.nslices; l++) {
-            const double v = __ldg(src + (size_t)l * slice_stride);
-            p += v;
-            if (MGGA) pl = fma((double)(l * (l + 1)), v, pl);
-          }
-        }
-        pf[ks] = p;
-        if (MGGA) plf[ks] = pl;
+        av[ks] = ab[(size_t)4 * ks * ldq];
+        if (MGGA) adv[ks] = ad[(size_t)4 * ks * ldq];
       }
-      const double* mb0 = sB + (size_t)(8 * ni + 2 * t4) * ldq + gid;
-      const double* md0 = sdB + (size_t)(8 * ni + 2 * t4) * ldq + gid;
-#pragma unroll 2
-      for (int mi = 0; mi < MT; mi++) {
-        const double* ab = sB + (size_t)t4 * ldq + 8 * mi + gid;
-        const double* ad = sdB + (size_t)t4 * ldq + 8 * mi + gid;
+      double rho = 0.0, g = 0.0, t1 = 0.0, t2 = 0.0;
+#pragma unroll
+      for (int ni = 0; ni < NT; ni++) {
         double q0 = 0.0, q1 = 0.0, qp0 = 0.0, qp1 = 0.0, ql0 = 0.0, ql1 = 0.0;
 #pragma unroll
         for (int ks = 0; ks < KS; ks++) {
-          const double a = ab[(size_t)4 * ks * ldq];
-          dmma(q0, q1, a, pf[ks]);
+          const double pv = PREG ? pf[PREG ? ni : 0][PREG ? ks : 0] : pfs[4 * ks * LDP + 8 * ni];
+          dmma(q0, q1, av[ks], pv);
           if (MGGA) {
-            dmma(qp0, qp1, ad[(size_t)4 * ks * ldq], pf[ks]);
-            dmma(ql0, ql1, a, plf[ks]);
+            dmma(qp0, qp1, adv[ks], pv);
+            dmma(ql0, ql1, av[ks], (PREG && MGGA) ? plf[PREG ? ni : 0][PREG ? ks : 0] : pfs[PBLK + 4 * ks * LDP + 8 * ni]);
           }
         }
-        const double b0 = mb0[8 * mi], b1 = mb0[ldq + 8 * mi];
-        double rho = fma(q1, b1, q0 * b0), g = 0.0, t1 = 0.0, t2 = 0.0;
+        const double* mb0 = sB + (size_t)(8 * ni + 2 * t4) * ldq + gid + 8 * mi;
+        const double b0 = mb0[0], b1 = mb0[ldq];
+        rho = fma(q1, b1, fma(q0, b0, rho));
         if (GGA) {
-          const double d0 = md0[8 * mi], d1 = md0[ldq + 8 * mi];
-          g = fma(q1, d1, q0 * d0);
+          const double* md0 = sdB + (size_t)(8 * ni + 2 * t4) * ldq + gid + 8 * mi;
+          const double d0 = md0[0], d1 = md0[ldq];
+          g = fma(q1, d1, fma(q0, d0, g));
           if (MGGA) {
-            t1 = fma(qp1, d1, qp0 * d0);
-            t2 = fma(ql1, b1, ql0 * b0);
+            t1 = fma(qp1, d1, fma(qp0, d0, t1));
+            t2 = fma(ql1, b1, fma(ql0, b0, t2));
           }
         }
-        rho = quad_sum(rho);
-        if (GGA) g = quad_sum(g);
-        if (MGGA) { t1 = quad_sum(t1); t2 = quad_sum(t2); }
-        if (t4 == 0) {
-          const int p = 8 * mi + gid;
-          aR[p] += rho;
-          if (GGA) aR[nq8 + p] += g;
-          if (MGGA) { aR[2 * nq8 + p] += t1; aR[3 * nq8 + p] += t2; }
-        }
+      }
+      rho = quad_sum(rho);
+      if (GGA) g = quad_sum(g);
+      if (MGGA) { t1 = quad_sum(t1); t2 = quad_sum(t2); }
+      if (t4 == 0) {
+        const int p = 8 * mi + gid;
+        aR[p] = rho;
+        if (GGA) aR[nq8 + p] = g;
+        if (MGGA) { aR[2 * nq8 + p] = t1; aR[3 * nq8 + p] = t2; }
       }
     }
   }
   __syncwarp();
+  HFB_TICK();
 
   // ================= stage 2: XC on the points =================
   double my_exc = 0.0, my_nel = 0.0, my_tau = 0.0;
@@ -224,6 +342,7 @@ __global__ void __launch_bounds__(256) sad_grid_mma_kernel(SadGridParams prm) {
     out[0] = my_exc; out[1] = my_nel; out[2] = my_tau; out[3] = 0.0;
   }
   __syncwarp();
+  HFB_TICK();
 
   // ================= stage 3: Fock blocks =================
   constexpr int NTRI = NT * (NT + 1) / 2;
@@ -231,63 +350,148 @@ __global__ void __launch_bounds__(256) sad_grid_mma_kernel(SadGridParams prm) {
 #pragma unroll 1
   for (int s = 0; s < NSPIN; s++) {
     const double* wa = scratch + (size_t)s * NARR * nq8 + t4;
-    double h[NTRI][2], hl[MGGA ? NTRI : 1][2];
-#pragma unroll
-    for (int t = 0; t < NTRI; t++) { h[t][0] = 0.0; h[t][1] = 0.0; if (MGGA) { hl[t][0] = 0.0; hl[t][1] = 0.0; } }
     const double* tb = sB + (size_t)gid * ldq + t4;
     const double* td = sdB + (size_t)gid * ldq + t4;
-#pragma unroll 1
-    for (int ks = 0; ks < KP; ks++) {
-      const double a = wa[4 * ks];
-      const double g = GGA ? wa[nq8 + 4 * ks] : 0.0;
-      const double c = MGGA ? wa[2 * nq8 + 4 * ks] : 0.0;
-      const double dl = MGGA ? wa[3 * nq8 + 4 * ks] : 0.0;
-      double bt[NT], dbt[GGA ? NT : 1], X[NT], Y[GGA ? NT : 1], Z[MGGA ? NT : 1];
+    // GGA: H = a B B^T + g (B dB^T + dB B^T) = W + W^T with W = B (a/2 B + g dB)^T -- ONE product over all
+    // NT^2 tiles (then mirrored through the shared block) instead of two over the upper tile triangle.
+    constexpr bool WSYM = GGA && !MGGA;
+    if constexpr (WSYM) {
+      constexpr int KSPL = (NT <= 2) ? 2 : 1;  // K split in two accumulator sets: twice the independent DMMA chains
+      double w[KSPL][NT * NT][2];
 #pragma unroll
-      for (int t = 0; t < NT; t++) {
-        bt[t] = tb[(size_t)8 * t * ldq + 4 * ks];
-        if (GGA) {
-          dbt[t] = td[(size_t)8 * t * ldq + 4 * ks];
-          X[t] = fma(g, dbt[t], a * bt[t]);
-          Y[t] = MGGA ? fma(c, dbt[t], g * bt[t]) : g * bt[t];
-        } else {
-          X[t] = a * bt[t];
+      for (int q = 0; q < KSPL; q++)
+#pragma unroll
+        for (int t = 0; t < NT * NT; t++) { w[q][t][0] = 0.0; w[q][t][1] = 0.0; }
+#pragma unroll 1
+      for (int ks0 = 0; ks0 < KP; ks0 += KSPL) {
+#pragma unroll
+        for (int q = 0; q < KSPL; q++) {
+          const int ks = ks0 + q;  // KP = nq8/4 is even
+          const double a = 0.5 * wa[4 * ks];
+          const double g = wa[nq8 + 4 * ks];
+          double bt[NT], X[NT];
+#pragma unroll
+          for (int t = 0; t < NT; t++) {
+            bt[t] = tb[(size_t)8 * t * ldq + 4 * ks];
+            X[t] = fma(g, td[(size_t)8 * t * ldq + 4 * ks], a * bt[t]);
+          }
+#pragma unroll
+          for (int mi = 0; mi < NT; mi++)
+#pragma unroll
+            for (int ni = 0; ni < NT; ni++) dmma(w[q][mi * NT + ni][0], w[q][mi * NT + ni][1], bt[mi], X[ni]);
         }
-        if (MGGA) Z[t] = dl * bt[t];
       }
-      int tt = 0;
+      if (s == 0) { HFB_TICK(); }
 #pragma unroll
       for (int mi = 0; mi < NT; mi++)
 #pragma unroll
-        for (int ni = mi; ni < NT; ni++) {
-          dmma(h[tt][0], h[tt][1], bt[mi], X[ni]);
-          if (GGA) dmma(h[tt][0], h[tt][1], dbt[mi], Y[ni]);
-          if (MGGA) dmma(hl[tt][0], hl[tt][1], bt[mi], Z[ni]);
-          tt++;
+        for (int ni = 0; ni < NT; ni++)
+#pragma unroll
+          for (int cc = 0; cc < 2; cc++) {
+            double v = w[0][mi * NT + ni][cc];
+            if (KSPL > 1) v += w[KSPL - 1][mi * NT + ni][cc];
+            pblk[(8 * ni + 2 * t4 + cc) * LDP + 8 * mi + gid] = v;
+          }
+      __syncwarp();
+    } else {
+      // separate accumulators for the B X^T and dB Y^T products: twice the independent DMMA chains
+      constexpr bool SPLIT = GGA && NT <= 2;
+      double h[NTRI][2], h2[SPLIT ? NTRI : 1][2], hl[MGGA ? NTRI : 1][2];
+  #pragma unroll
+      for (int t = 0; t < NTRI; t++) {
+        h[t][0] = 0.0; h[t][1] = 0.0;
+        if (SPLIT) { h2[t][0] = 0.0; h2[t][1] = 0.0; }
+        if (MGGA) { hl[t][0] = 0.0; hl[t][1] = 0.0; }
+      }
+      const double* tb = sB + (size_t)gid * ldq + t4;
+      const double* td = sdB + (size_t)gid * ldq + t4;
+  #pragma unroll 2
+      for (int ks = 0; ks < KP; ks++) {
+        const double a = wa[4 * ks];
+        const double g = GGA ? wa[nq8 + 4 * ks] : 0.0;
+        const double c = MGGA ? wa[2 * nq8 + 4 * ks] : 0.0;
+        const double dl = MGGA ? wa[3 * nq8 + 4 * ks] : 0.0;
+        double bt[NT], dbt[GGA ? NT : 1], X[NT], Y[GGA ? NT : 1], Z[MGGA ? NT : 1];
+  #pragma unroll
+        for (int t = 0; t < NT; t++) {
+          bt[t] = tb[(size_t)8 * t * ldq + 4 * ks];
+          if (GGA) {
+            dbt[t] = td[(size_t)8 * t * ldq + 4 * ks];
+            X[t] = fma(g, dbt[t], a * bt[t]);
+            Y[t] = MGGA ? fma(c, dbt[t], g * bt[t]) : g * bt[t];
+          } else {
+            X[t] = a * bt[t];
+          }
+          if (MGGA) Z[t] = dl * bt[t];
         }
-    }
-    // write H(i,j) (and the mirrored element for off-diagonal tiles) to every l slice
-    double* gH = prm.H + ((size_t)(b * NSPIN + s) * prm.nslices * prm.nel + el) * np2;
-    int tt = 0;
-#pragma unroll
-    for (int mi = 0; mi < NT; mi++)
-#pragma unroll
-      for (int ni = mi; ni < NT; ni++) {
-        const int i = 8 * mi + gid;
-#pragma unroll
-        for (int cc = 0; cc < 2; cc++) {
-          const int j = 8 * ni + 2 * t4 + cc;
-          if (i < np && j < np) {
-            for (int l = 0; l < prm.nslices; l++) {
-              const double val = MGGA ? fma((double)(l * (l + 1)), hl[tt][cc], h[tt][cc]) : h[tt][cc];
-              gH[(size_t)l * slice_stride + i + (size_t)j * np] = val;
-              if (ni > mi) gH[(size_t)l * slice_stride + j + (size_t)i * np] = val;
+        int tt = 0;
+  #pragma unroll
+        for (int mi = 0; mi < NT; mi++)
+  #pragma unroll
+          for (int ni = mi; ni < NT; ni++) {
+            dmma(h[tt][0], h[tt][1], bt[mi], X[ni]);
+            if (GGA) {
+              if (SPLIT) dmma(h2[tt][0], h2[tt][1], dbt[mi], Y[ni]);
+              else dmma(h[tt][0], h[tt][1], dbt[mi], Y[ni]);
+            }
+            if (MGGA) dmma(hl[tt][0], hl[tt][1], bt[mi], Z[ni]);
+            tt++;
+          }
+      }
+      if (SPLIT) {
+  #pragma unroll
+        for (int t = 0; t < NTRI; t++) { h[t][0] += h2[t][0]; h[t][1] += h2[t][1]; }
+      }
+      if (s == 0) { HFB_TICK(); }
+      // H(i,j) and its mirror image into the per-warp block, then coalesced stores to every l slice
+      int tt = 0;
+  #pragma unroll
+      for (int mi = 0; mi < NT; mi++)
+  #pragma unroll
+        for (int ni = mi; ni < NT; ni++) {
+          const int i = 8 * mi + gid;
+  #pragma unroll
+          for (int cc = 0; cc < 2; cc++) {
+            const int j = 8 * ni + 2 * t4 + cc;
+            pblk[j * LDP + i] = h[tt][cc];
+            if (MGGA) pblk[PBLK + j * LDP + i] = hl[tt][cc];
+            if (ni > mi) {
+              pblk[i * LDP + j] = h[tt][cc];
+              if (MGGA) pblk[PBLK + i * LDP + j] = hl[tt][cc];
             }
           }
+          tt++;
         }
-        tt++;
+      __syncwarp();
+    }
+    double* gH = prm.H + ((size_t)(b * NSPIN + s) * prm.nslices * prm.nel + el) * np2;
+    {
+      double hv[NPASS], hlv[MGGA ? NPASS : 1];
+#pragma unroll
+      for (int it = 0; it < NPASS; it++) {
+        const int col = it * CPI + bcol0;
+        hv[it] = (brow < 8 * NT) ? pblk[col * LDP + brow] : 0.0;
+        if (WSYM && brow < 8 * NT) hv[it] += pblk[brow * LDP + col];
+        if (MGGA) hlv[it] = (brow < 8 * NT) ? pblk[PBLK + col * LDP + brow] : 0.0;
       }
+      for (int l = 0; l < prm.nslices; l++) {
+        double* dst = gH + (size_t)l * slice_stride + brow;
+        const double ll = (double)(l * (l + 1));
+#pragma unroll
+        for (int it = 0; it < NPASS; it++) {
+          const int col = it * CPI + bcol0;
+          if (brow_ok && col < np) dst[col * np] = MGGA ? fma(ll, hlv[it], hv[it]) : hv[it];
+        }
+      }
+    }
+    __syncwarp();  // the block is reused by the next spin
   }
+#ifdef HFB_GRID_PROFILE
+  HFB_TICK();
+  if (lane == 0 && el == 3 && (b % 97) == 0)
+    printf("grid profile b=%d: load %lld  jpack %lld  dens %lld  xc %lld  fock %lld  store %lld cycles (first spin for load/fock split)\n", b,
+           tk[1] - tk[0], tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5]);
+#endif
 }
 
 inline int sad_grid_ldq(int nq) {
@@ -296,10 +500,11 @@ inline int sad_grid_ldq(int nq) {
   while ((ldq & 15) != 4) ldq++;
   return ldq;
 }
-inline size_t sad_grid_mma_smem_bytes(int fam, int nspin, int np_pad, int nq8, int ldq, int nwarps) {
+inline size_t sad_grid_mma_smem_bytes(int fam, int nspin, int np_pad, int nq8, int ldq, int nwarps, int jKP) {
   const bool gga = fam >= xc::FAM_GGA, mgga = fam >= xc::FAM_MGGA;
   const int narr = 1 + (gga ? 1 : 0) + (mgga ? 2 : 0);
-  return ((size_t)np_pad * ldq * (gga ? 2 : 1) + (size_t)nwarps * nspin * narr * nq8) * sizeof(double);
+  const size_t blk = (size_t)(mgga ? 2 : 1) * np_pad * sad_grid_ldp(np_pad);
+  return ((size_t)np_pad * ldq * (gga ? 2 : 1) + 3 * (size_t)jKP + (size_t)nwarps * (nspin * narr * nq8 + blk)) * sizeof(double);
 }
 
 // [nb][nel][4] partial scalars -> [nb][4], fixed order

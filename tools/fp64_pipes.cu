@@ -37,9 +37,22 @@ __global__ void __launch_bounds__(256) kern(double* out, int iters, double seed)
     } else if (MODE == 2) {
 #pragma unroll
       for (int i = 0; i < 4; i++) dmma1688(acc + 4 * i, a + (i & 1) * 4, b + (i & 1) * 2);
-    } else {
+    } else if (MODE == 3) {
 #pragma unroll
       for (int i = 0; i < 4; i++) dmma16816(acc + 4 * i, a, b);
+    } else if (MODE == 4) {  // mix: 8 DFMA + 4 DMMA.8x8x4 per iteration (do the two share one pipe?)
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        acc[8 + 2 * i] = fma(acc[8 + 2 * i], a[i], b[i]);
+        dmma884(acc[2 * i], acc[2 * i + 1], a[i + 4], b[i]);
+        acc[9 + 2 * i] = fma(acc[9 + 2 * i], a[i], b[i]);
+      }
+    } else if (MODE == 5) {  // one dependent DFMA chain per thread (latency)
+#pragma unroll
+      for (int i = 0; i < 16; i++) acc[0] = fma(acc[0], a[i & 7], b[i & 3]);
+    } else {                 // one dependent DMMA chain per warp (latency)
+#pragma unroll
+      for (int i = 0; i < 16; i++) dmma884(acc[0], acc[1], a[i & 7], b[i & 3]);
     }
   }
   double s = 0;
@@ -49,19 +62,20 @@ __global__ void __launch_bounds__(256) kern(double* out, int iters, double seed)
 }
 
 template <int MODE>
-double run(int blocks, int iters, double flops_per_thread_iter) {
+double run(int blocks, int iters, double flops_per_thread_iter, int threads = 256, float* ms_out = nullptr) {
   double* out;
   cudaMalloc(&out, sizeof(double) * blocks * 256);
-  kern<MODE><<<blocks, 256>>>(out, 10, 1e-3);
+  kern<MODE><<<blocks, threads>>>(out, 10, 1e-3);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0);
-  kern<MODE><<<blocks, 256>>>(out, iters, 1e-3);
+  kern<MODE><<<blocks, threads>>>(out, iters, 1e-3);
   cudaEventRecord(e1);
   cudaEventSynchronize(e1);
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   cudaFree(out);
-  return flops_per_thread_iter * iters * blocks * 256.0 / (ms * 1e-3) / 1e12;
+  if (ms_out) *ms_out = ms;
+  return flops_per_thread_iter * iters * blocks * (double)threads / (ms * 1e-3) / 1e12;
 }
 
 int main() {
@@ -70,6 +84,16 @@ int main() {
   printf("{\"dfma_tflops\": %.2f, ", run<0>(blocks, iters, 32.0));
   printf("\"dmma_m8n8k4_tflops\": %.2f, ", run<1>(blocks, iters, 8 * 16.0));
   printf("\"dmma_m16n8k8_tflops\": %.2f, ", run<2>(blocks, iters, 4 * 64.0));
-  printf("\"dmma_m16n8k16_tflops\": %.2f}\n", run<3>(blocks, iters, 4 * 128.0));
+  printf("\"dmma_m16n8k16_tflops\": %.2f, ", run<3>(blocks, iters, 4 * 128.0));
+  // mix: if DFMA and DMMA ran on separate pipes this would exceed either peak
+  printf("\"mix_8dfma_4dmma_tflops\": %.2f, ", run<4>(blocks, iters, 8 * 2.0 + 4 * 16.0));
+  // dependent-issue latencies: one warp per SM sub-partition, one chain, 16 ops per iteration
+  int clk_khz = 0;
+  cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0);
+  float ms = 0;
+  run<5>(148, iters, 32.0, 32, &ms);
+  printf("\"dfma_dependent_latency_cycles\": %.1f, ", ms * 1e-3 * clk_khz * 1e3 / (16.0 * iters));
+  run<6>(148, iters, 32.0, 32, &ms);
+  printf("\"dmma884_dependent_latency_cycles\": %.1f, \"clock_khz_assumed\": %d}\n", ms * 1e-3 * clk_khz * 1e3 / (16.0 * iters), clk_khz);
   return 0;
 }
