@@ -264,9 +264,13 @@ def run_gpu(args, w, rank, world, local_rank):
         ms = float(t.item())
     value = nb * world * args.steps / (ms * 1e-3)
 
-    if args.kernels_only:  # for ncu: just the timed steps, nothing else
+    if args.kernels_only:  # for ncu / tuning runs: just the timed device steps, nothing else
+        out = {"kernels_only": True, "ms_per_step": ms / args.steps, "value": value}
+        if args.split:
+            out["ms_grid"] = timed(lambda: step(J=False), args.steps) / args.steps
+            out["ms_coulomb"] = timed(lambda: step(H=False), args.steps) / args.steps
         if rank == 0:
-            print(json.dumps({"kernels_only": True, "ms_per_step": ms / args.steps, "value": value}), flush=True)
+            print(json.dumps(out), flush=True)
         return
 
     # ---- per-kernel timing (rank 0 reports): the grid/XC kernel and the Coulomb kernels on their own ----
@@ -386,6 +390,7 @@ def main():
     ap.add_argument("--workload", default="kr_pbe_cfg2", choices=list(WORKLOADS))
     ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
     ap.add_argument("--kernels-only", action="store_true", help="run only the timed device steps (ncu captures)")
+    ap.add_argument("--split", action="store_true", help="with --kernels-only: also time the grid and the Coulomb kernels alone")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

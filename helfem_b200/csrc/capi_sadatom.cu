@@ -9,6 +9,12 @@
 
 using namespace hfb;
 
+namespace hfb {  // sadatom_grid_{lda,gga,mgga}.cu
+int launch_grid_lda(int nspin, const SadGridParams& prm, cudaStream_t st);
+int launch_grid_gga(int nspin, const SadGridParams& prm, cudaStream_t st);
+int launch_grid_mgga(int nspin, const SadGridParams& prm, cudaStream_t st);
+}  // namespace hfb
+
 namespace {
 
 template <class T>
@@ -26,50 +32,15 @@ bool valid_pair(int x_func, int c_func, int* fam) {
   return *fam != 0;
 }
 
-template <int FAM, int NSPIN, int NT>
-int launch_grid_nt(const SadGridParams& prm, int nwarps, size_t smem, cudaStream_t st) {
-  dim3 grid(prm.nel, (prm.nb + nwarps - 1) / nwarps);
-  HFB_CUDA_OK(cudaFuncSetAttribute(sad_grid_mma_kernel<FAM, NSPIN, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  sad_grid_mma_kernel<FAM, NSPIN, NT><<<grid, 32 * nwarps, smem, st>>>(prm);
-  HFB_CUDA_OK(cudaGetLastError());
-  return 0;
-}
-
-template <int FAM, int NSPIN>
-int launch_grid_fs(const SadGridParams& prm, int nwarps, size_t smem, cudaStream_t st) {
-  switch (prm.np_pad / 8) {
-    case 1: return launch_grid_nt<FAM, NSPIN, 1>(prm, nwarps, smem, st);
-    case 2: return launch_grid_nt<FAM, NSPIN, 2>(prm, nwarps, smem, st);
-    case 3: return launch_grid_nt<FAM, NSPIN, 3>(prm, nwarps, smem, st);
-    case 4: return launch_grid_nt<FAM, NSPIN, 4>(prm, nwarps, smem, st);
-    default:
-      set_error("more than 32 functions per element are not supported by the grid kernel");
-      return HFB200_EINVAL;
-  }
-}
-
 int launch_grid(int fam, int nspin, const SadGridParams& prm, cudaStream_t st) {
-  // one warp per build; up to HFB_GRID_WARPS builds share a CTA's staged tables
-  int nwarps = prm.nb < HFB_GRID_WARPS ? prm.nb : HFB_GRID_WARPS;
-  size_t smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps, prm.jKP);
-  while (smem > 227 * 1024 && nwarps > 1) {
-    nwarps >>= 1;
-    smem = sad_grid_mma_smem_bytes(fam, nspin, prm.np_pad, prm.nq8, prm.ldq, nwarps, prm.jKP);
-  }
-  if (smem > 227 * 1024) { set_error("element tables need %zu bytes of shared memory (>227 KB)", smem); return HFB200_EINVAL; }
-  if (nspin == 1) {
-    if (fam == xc::FAM_LDA) return launch_grid_fs<xc::FAM_LDA, 1>(prm, nwarps, smem, st);
-    if (fam == xc::FAM_GGA) return launch_grid_fs<xc::FAM_GGA, 1>(prm, nwarps, smem, st);
-    return launch_grid_fs<xc::FAM_MGGA, 1>(prm, nwarps, smem, st);
-  }
-  if (fam == xc::FAM_LDA) return launch_grid_fs<xc::FAM_LDA, 2>(prm, nwarps, smem, st);
-  if (fam == xc::FAM_GGA) return launch_grid_fs<xc::FAM_GGA, 2>(prm, nwarps, smem, st);
-  return launch_grid_fs<xc::FAM_MGGA, 2>(prm, nwarps, smem, st);
+  if (fam == xc::FAM_LDA) return launch_grid_lda(nspin, prm, st);
+  if (fam == xc::FAM_GGA) return launch_grid_gga(nspin, prm, st);
+  return launch_grid_mgga(nspin, prm, st);
 }
 
 int launch_coulomb(const SadJParams& q, bool pack, cudaStream_t st) {
   if (pack) {  // otherwise the grid kernel of the same build has already written pc / traces
-    sad_jpack_kernel<<<dim3(q.nel, q.nb), 128, 0, st>>>(q);
+    sad_jpack_kernel<<<dim3(q.nel, (q.nb + 3) / 4), 128, 0, st>>>(q);
     HFB_CUDA_OK(cudaGetLastError());
   }
   const int rts = (q.MT + 3) / 4;
@@ -78,7 +49,13 @@ int launch_coulomb(const SadJParams& q, bool pack, cudaStream_t st) {
   } else if (q.nb <= 16) {
     sad_jmma_kernel<true, 2><<<dim3(q.nel * rts, 1), 256, 0, st>>>(q);
   } else {
-    sad_jmma_kernel<false, 2><<<dim3(q.nel * rts, (q.nb + 127) / 128), 256, 0, st>>>(q);
+#ifndef HFB_JMMA_NTW
+#define HFB_JMMA_NTW 2
+#endif
+    const size_t smem = (size_t)4 * q.KS * 32 * sizeof(double);
+    if (smem > 48 * 1024)
+      HFB_CUDA_OK(cudaFuncSetAttribute(sad_jmma_smem_kernel<HFB_JMMA_NTW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sad_jmma_smem_kernel<HFB_JMMA_NTW><<<dim3(q.nel * rts, (q.nb + 64 * HFB_JMMA_NTW - 1) / (64 * HFB_JMMA_NTW)), 256, smem, st>>>(q);
   }
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -178,7 +155,7 @@ int hfb200_sadatom_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_
   // ---- Coulomb path (L = 0 only, sadatom/basis.cpp:306): triangle-packed, fragment-ordered ----
   {
     const int ntri = np * (np + 1) / 2;
-    const int MP = (ntri + 7) & ~7, KP = (ntri + 3) & ~3, MT = MP / 8, KS = KP / 4;
+    const int MP = (ntri + 7) & ~7, KP = MP, MT = MP / 8, KS = KP / 4;  // KS even (16-byte operand loads)
     c->ntri = ntri; c->jMT = MT; c->jKS = KS;
     std::vector<int2> tri(ntri);
     for (int j = 0; j < np; j++)
@@ -200,7 +177,7 @@ int hfb200_sadatom_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_
           const int k = tri[kk].x, l = tri[kk].y;
           if (l >= npe) continue;
           const double v = t[(size_t)(i + j * npe) + (size_t)(k + l * npe) * n2];
-          const int mt = m >> 3, ks = kk >> 2, lane = (m & 7) * 4 + (kk & 3);
+          const int mt = m >> 3, ks = kk % KS, lane = (m & 7) * 4 + kk / KS;  // column kk -> k-step kk % KS, slot kk / KS
           F[(((size_t)e * MT + mt) * KS + ks) * 32 + lane] = v;
         }
       }

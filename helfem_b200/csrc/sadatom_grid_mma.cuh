@@ -52,14 +52,17 @@ struct SadGridParams {
   const double* dm1Lc; // [nel][jMP]
   const int2* tri;     // [ntri]
   int ntri, jKP, jMP;
+  int gpc;             // build groups (of blockDim/32 builds) a CTA walks through with its tables staged once
 };
 
 // tuning knobs (tools/build_variant.py): builds (= warps) per CTA, resident CTAs per SM the register budget is cut for
 #ifndef HFB_GRID_WARPS
 #define HFB_GRID_WARPS 8
 #endif
+// default: 3 CTAs (24 warps) per SM where the kernel fits 80 registers without spilling -- the compile-time
+// LDA / GGA pairs, unpolarised, up to 16 functions per element -- else 2
 #ifndef HFB_GRID_MINBLOCKS
-#define HFB_GRID_MINBLOCKS 2
+#define HFB_GRID_MINBLOCKS ((FAM < xc::FAM_MGGA && NSPIN == 1 && NT <= 2 && PAIR == 1) ? 3 : 2)
 #endif
 
 __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
@@ -76,8 +79,17 @@ __device__ __forceinline__ double quad_sum(double v) {
 /// row stride of the per-warp density / Fock block: >= np_pad and = 4 (mod 16)
 __host__ __device__ constexpr int sad_grid_ldp(int np_pad) { return np_pad <= 20 ? 20 : 36; }
 
-// FAM: highest functional family; NSPIN: 1 or 2; NT: 8-row tiles of the element block (np_pad = 8 NT).
-template <int FAM, int NSPIN, int NT>
+/// The functional pair a family is usually run with: kernels specialised on it (PAIR = 1) fold the functional
+/// switch at compile time (a third of the code, half the registers of the XC stage); any other pair of the
+/// family takes the PAIR = 0 instantiation that switches on prm.x_func / prm.c_func at run time.
+template <int FAM> struct CanonicalPair {
+  static constexpr int x = (FAM == xc::FAM_LDA) ? xc::XC_LDA_X : (FAM == xc::FAM_GGA ? xc::XC_GGA_X_PBE : xc::XC_MGGA_X_R2SCAN);
+  static constexpr int c = (FAM == xc::FAM_LDA) ? xc::XC_LDA_C_PW : (FAM == xc::FAM_GGA ? xc::XC_GGA_C_PBE : xc::XC_MGGA_C_R2SCAN);
+};
+
+// FAM: highest functional family; NSPIN: 1 or 2; NT: 8-row tiles of the element block (np_pad = 8 NT);
+// PAIR: 1 = functional ids are CanonicalPair<FAM>, 0 = read from prm.
+template <int FAM, int NSPIN, int NT, int PAIR>
 __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_grid_mma_kernel(SadGridParams prm) {
   extern __shared__ double smem[];
   constexpr bool GGA = (FAM >= xc::FAM_GGA);
@@ -103,9 +115,38 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
   double* sDL = sB + (GGA ? 2 : 1) * tabsz;
   double* sDM = sDL + prm.jKP;
   int2* sTri = reinterpret_cast<int2*>(sDM + prm.jKP);
-  double* scratch = sDL + 3 * prm.jKP + (size_t)warp * (NSPIN * NARR * nq8 + NBLK * PBLK);
-  double* pblk = scratch + NSPIN * NARR * nq8;
+  double* sR = sDM + 2 * prm.jKP;  // quadrature radii | weights of this element
+  double* sW = sR + nq8;
+  // per warp: point arrays [NSPIN][NARR][nq8] | per-point Exc, Nel, tau integrands [3][nq8] | density / Fock block(s)
+#ifdef HFB_GRID_ALIAS_SPT  // experiment: integrand arrays share the density / Fock block (needs 3 nq8 <= NBLK PBLK)
+  const int wstride = NSPIN * NARR * nq8 + NBLK * PBLK;
+  double* wbase = sDL + 3 * prm.jKP + 2 * nq8;
+  double* scratch = wbase + (size_t)warp * wstride;
+  double* spt = scratch + NSPIN * NARR * nq8;
+  double* pblk = spt;
+#else
+  const int wstride = (NSPIN * NARR + 3) * nq8 + NBLK * PBLK;
+  double* wbase = sDL + 3 * prm.jKP + 2 * nq8;
+  double* scratch = wbase + (size_t)warp * wstride;
+  double* spt = scratch + NSPIN * NARR * nq8;
+  double* pblk = spt + 3 * nq8;
+#endif
 
+#ifndef HFB_GRID_NO_ENTRY_PREFETCH
+  // ---- start pulling this warp's density blocks out of HBM while the CTA stages its tables ----
+  {
+    const int b0 = (int)blockIdx.y * prm.gpc * nwarps + warp;
+    if (b0 < prm.nb) {
+      const int nblk = NSPIN * prm.nslices;
+      const char* blk0 = reinterpret_cast<const char*>(prm.P + ((size_t)b0 * nblk * prm.nel + el) * np2);
+      const int nline = (np2 * 8 + 127) >> 7;
+      for (int k = lane; k < nblk * nline; k += 32) {
+        const int blk = k / nline, ln = k - blk * nline;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(blk0 + (size_t)blk * prm.nel * np2 * 8 + (size_t)ln * 128));
+      }
+    }
+  }
+#endif
   // ---- stage the element tables (whole CTA) ----
   {
     const double* gB = prm.Bt + (size_t)el * tabsz;
@@ -122,14 +163,16 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
         sTri[m] = ok ? prm.tri[m] : make_int2(0, 0);
       }
     }
+    for (int p = tid; p < nq; p += blockDim.x) {
+      sR[p] = prm.r[(size_t)el * nq + p];
+      sW[p] = prm.wrad[(size_t)el * nq + p];
+    }
   }
   __syncthreads();
-  const int b = blockIdx.y * nwarps + warp;
-  if (b >= prm.nb) return;  // no block-level synchronisation below
 
 #ifdef HFB_GRID_PROFILE
   long long tk[8]; int tki = 0;
-#define HFB_TICK() tk[tki++] = clock64()
+#define HFB_TICK() do { if (tki < 8) tk[tki++] = clock64(); } while (0)
 #else
 #define HFB_TICK()
 #endif
@@ -139,9 +182,29 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
   const int brow = lane & (LW - 1), bcol0 = lane / LW;  // this lane's row / first column in block transfers
   const bool brow_ok = brow < np;
 
+  // ---- the CTA walks through prm.gpc groups of nwarps builds (one build per warp) ----
+#pragma unroll 1
+  for (int gi = 0; gi < prm.gpc; gi++) {
+  const int bbase = ((int)blockIdx.y * prm.gpc + gi) * nwarps;
+  if (bbase >= prm.nb) break;  // block-uniform
+  const int b = bbase + warp;
+  const bool active = b < prm.nb;  // idle warps of the last group only keep the block barriers company
+  // pull the density blocks of this warp's NEXT build towards L2 while this one is worked on
+#ifdef HFB_GRID_PREFETCH
+  if (gi + 1 < prm.gpc && b + nwarps < prm.nb) {
+    const int nblk = NSPIN * prm.nslices;
+    const char* nxt = reinterpret_cast<const char*>(prm.P + ((size_t)(b + nwarps) * nblk * prm.nel + el) * np2);
+    const int nline = (np2 * 8 + 127) >> 7;
+    for (int k = lane; k < nblk * nline; k += 32) {
+      const int blk = k / nline, ln = k - blk * nline;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + (size_t)blk * slice_stride * 8 + (size_t)ln * 128));
+    }
+  }
+#endif
+
   // ================= stages 0 + 1: density, gradient, tau on the points =================
 #pragma unroll 1
-  for (int s = 0; s < NSPIN; s++) {
+  for (int s = 0; s < (active ? NSPIN : 0); s++) {
     const double* gP = prm.P + ((size_t)(b * NSPIN + s) * prm.nslices * prm.nel + el) * np2;
     double* aR = scratch + (size_t)s * NARR * nq8;  // rho | g | t1 | t2
     // ---- stage 0: sum the l slices of the block into shared memory ----
@@ -267,36 +330,65 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
       }
     }
   }
+#ifndef HFB_GRID_NO_POOL
+  __syncthreads();
+#else
   __syncwarp();
+#endif
   HFB_TICK();
 
-  // ================= stage 2: XC on the points =================
-  double my_exc = 0.0, my_nel = 0.0, my_tau = 0.0;
+  // ================= stage 2: XC on the points of ALL the CTA's builds, pooled over its threads =================
+  // (nq is rarely a multiple of 32: per-warp passes would leave a quarter of the FP64 lanes idle in the last one)
   {
+    const int xf = PAIR ? CanonicalPair<FAM>::x : prm.x_func;
+    const int cf = PAIR ? CanonicalPair<FAM>::c : prm.c_func;
     const xc::XcThresholds thr = xc::make_thresholds(prm.dens_thr);
-    double* a0 = scratch;
-    double* a1 = scratch + (size_t)NARR * nq8;  // spin b (NSPIN == 2)
-    for (int p = lane; p < nq8; p += 32) {
-      if (p >= nq) {
-#pragma unroll
-        for (int k = 0; k < NARR; k++) { a0[k * nq8 + p] = 0.0; if (NSPIN == 2) a1[k * nq8 + p] = 0.0; }
-        continue;
-      }
-      const double rr = prm.r[(size_t)el * nq + p];
-      const double wr = prm.wrad[(size_t)el * nq + p];
+#ifdef HFB_GRID_NO_POOL  // experiment: every warp evaluates its own build's points, no block barriers
+    for (int p = lane; p < (active ? nq : 0); p += 32) {
+      double* a0 = scratch;
+      double* a1 = a0 + (size_t)NARR * nq8;
+      double* sp = spt;
+      const double rr = sR[p];
+      const double wr = sW[p];
       const double w4 = 4.0 * HFB_PI * wr;
       const double wtot = w4 * (rr * rr);
+#else
+    const int nbw = min(nwarps, prm.nb - bbase);  // builds of this group
+    const int npts = nbw * nq, nthr = blockDim.x;
+    // F full passes of the whole CTA, then the remainder on the LAST warps only; just the warps whose builds the
+    // remainder touches (and the ones running it) wait for it, on their own named barrier
+    const int F = npts / nthr, R = npts - F * nthr;
+    const int wrem = nwarps - ((R + 31) >> 5);
+    const int wmin = R ? min((F * nthr) / nq, wrem) : nwarps;
+#pragma unroll 1
+    for (int pass = 0; pass <= F; pass++) {
+      int gp = pass * nthr + tid;
+      if (pass == F) {
+        __syncthreads();  // every full pass is done
+        if (warp < wrem) break;
+        gp -= wrem * 32;
+        if (gp >= npts) continue;
+      }
+      const int w = gp / nq, p = gp - w * nq;
+      double* a0 = wbase + (size_t)w * wstride;
+      double* a1 = a0 + (size_t)NARR * nq8;  // spin b (NSPIN == 2)
+      double* sp = a0 + (size_t)NSPIN * NARR * nq8;
+      const double rr = sR[p];
+      const double wr = sW[p];
+      const double w4 = 4.0 * HFB_PI * wr;
+      const double wtot = w4 * (rr * rr);
+#endif
       if (NSPIN == 1) {
         const double rho = a0[p];
         const double gr = GGA ? 2.0 * a0[nq8 + p] : 0.0;
         const double sigma = gr * gr;
         const double tau = MGGA ? 0.5 * (a0[2 * nq8 + p] + fmax(a0[3 * nq8 + p] / (rr * rr), 0.0)) : 0.0;
         double exc = 0.0, vrho = 0.0, vsigma = 0.0, vtau = 0.0;
-        xc::xc_point_unpol<FAM>(prm.x_func, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
-        xc::xc_point_unpol<FAM>(prm.c_func, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
-        my_exc += wtot * exc * rho;
-        my_nel += wtot * rho;
-        my_tau += wtot * tau;
+        xc::xc_point_unpol<FAM>(xf, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
+        xc::xc_point_unpol<FAM>(cf, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
+        sp[p] = wtot * exc * rho;
+        sp[nq8 + p] = wtot * rho;
+        sp[2 * nq8 + p] = wtot * tau;
         a0[p] = wtot * vrho;
         if (GGA) a0[nq8 + p] = 2.0 * wtot * vsigma * gr;
         if (MGGA) { a0[2 * nq8 + p] = wtot * 0.5 * vtau; a0[3 * nq8 + p] = vtau * (0.5 * w4); }
@@ -310,11 +402,11 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
           tau[1] = 0.5 * (a1[2 * nq8 + p] + fmax(a1[3 * nq8 + p] / (rr * rr), 0.0));
         }
         double exc = 0.0, vrho[2] = {0.0, 0.0}, vsigma[3] = {0.0, 0.0, 0.0}, vtau[2] = {0.0, 0.0};
-        xc::xc_point_pol<FAM>(prm.x_func, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
-        xc::xc_point_pol<FAM>(prm.c_func, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
-        my_exc += wtot * exc * (rho[0] + rho[1]);
-        my_nel += wtot * (rho[0] + rho[1]);
-        my_tau += wtot * (tau[0] + tau[1]);
+        xc::xc_point_pol<FAM>(xf, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
+        xc::xc_point_pol<FAM>(cf, thr, rho, sigma, tau, exc, vrho, vsigma, vtau);
+        sp[p] = wtot * exc * (rho[0] + rho[1]);
+        sp[nq8 + p] = wtot * (rho[0] + rho[1]);
+        sp[2 * nq8 + p] = wtot * (tau[0] + tau[1]);
         a0[p] = wtot * vrho[0];
         a1[p] = wtot * vrho[1];
         if (GGA) {
@@ -329,19 +421,32 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
         }
       }
     }
+#ifndef HFB_GRID_NO_POOL
+    if (warp >= wmin) asm volatile("bar.sync 1, %0;" ::"r"((nwarps - wmin) * 32) : "memory");
+#else
+    __syncwarp();
+#endif
   }
-  // warp reduction of the three scalars (fixed tree => run-to-run deterministic)
+  if (active) {
+  // the three scalars of this warp's build: fixed lane striding + shuffle tree => run-to-run deterministic
+  {
+    double my_exc = 0.0, my_nel = 0.0, my_tau = 0.0;
+    for (int p = lane; p < nq; p += 32) {
+      my_exc += spt[p];
+      my_nel += spt[nq8 + p];
+      my_tau += spt[2 * nq8 + p];
+    }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    my_exc += __shfl_xor_sync(0xffffffffu, my_exc, o);
-    my_nel += __shfl_xor_sync(0xffffffffu, my_nel, o);
-    my_tau += __shfl_xor_sync(0xffffffffu, my_tau, o);
+    for (int o = 16; o > 0; o >>= 1) {
+      my_exc += __shfl_xor_sync(0xffffffffu, my_exc, o);
+      my_nel += __shfl_xor_sync(0xffffffffu, my_nel, o);
+      my_tau += __shfl_xor_sync(0xffffffffu, my_tau, o);
+    }
+    if (lane == 0) {
+      double* out = prm.partial + ((size_t)b * prm.nel + el) * 4;
+      out[0] = my_exc; out[1] = my_nel; out[2] = my_tau; out[3] = 0.0;
+    }
   }
-  if (lane == 0) {
-    double* out = prm.partial + ((size_t)b * prm.nel + el) * 4;
-    out[0] = my_exc; out[1] = my_nel; out[2] = my_tau; out[3] = 0.0;
-  }
-  __syncwarp();
   HFB_TICK();
 
   // ================= stage 3: Fock blocks =================
@@ -486,12 +591,14 @@ __global__ void __launch_bounds__(32 * HFB_GRID_WARPS, HFB_GRID_MINBLOCKS) sad_g
     }
     __syncwarp();  // the block is reused by the next spin
   }
+  }  // if (active)
 #ifdef HFB_GRID_PROFILE
   HFB_TICK();
-  if (lane == 0 && el == 3 && (b % 97) == 0)
+  if (gi == 0 && lane == 0 && el == 3 && (b % 97) == 0)
     printf("grid profile b=%d: load %lld  jpack %lld  dens %lld  xc %lld  fock %lld  store %lld cycles (first spin for load/fock split)\n", b,
            tk[1] - tk[0], tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5]);
 #endif
+  }  // groups
 }
 
 inline int sad_grid_ldq(int nq) {
@@ -504,7 +611,11 @@ inline size_t sad_grid_mma_smem_bytes(int fam, int nspin, int np_pad, int nq8, i
   const bool gga = fam >= xc::FAM_GGA, mgga = fam >= xc::FAM_MGGA;
   const int narr = 1 + (gga ? 1 : 0) + (mgga ? 2 : 0);
   const size_t blk = (size_t)(mgga ? 2 : 1) * np_pad * sad_grid_ldp(np_pad);
-  return ((size_t)np_pad * ldq * (gga ? 2 : 1) + 3 * (size_t)jKP + (size_t)nwarps * (nspin * narr * nq8 + blk)) * sizeof(double);
+#ifdef HFB_GRID_ALIAS_SPT
+  return ((size_t)np_pad * ldq * (gga ? 2 : 1) + 3 * (size_t)jKP + 2 * (size_t)nq8 + (size_t)nwarps * (nspin * narr * nq8 + blk)) * sizeof(double);
+#else
+  return ((size_t)np_pad * ldq * (gga ? 2 : 1) + 3 * (size_t)jKP + 2 * (size_t)nq8 + (size_t)nwarps * ((nspin * narr + 3) * nq8 + blk)) * sizeof(double);
+#endif
 }
 
 // [nb][nel][4] partial scalars -> [nb][4], fixed order
