@@ -113,5 +113,5 @@ def device_count():
 
 
 from .sadatom import SadatomBasis  # noqa: E402,F401
-from .atomic import AtomicBasis  # noqa: E402,F401
-from .diatomic import DiatomicBasis  # noqa: E402,F401
+from .atomic import AtomicBasis, AtomicDFTGrid  # noqa: E402,F401
+from .diatomic import DiatomicBasis, DiatomicDFTGrid  # noqa: E402,F401

@@ -85,3 +85,45 @@ class AtomicBasis:
         K = np.zeros_like(P, order="F")
         check_host(lib().hfh_atomic_exchange(self._h, _p(P), _p(K)))
         return K
+
+
+class _ProductGrid:
+    """ctypes view of hfb::{atomic,diatomic}::DFTGrid (helfem_b200/host/dftgrid.h), mirrors of
+    helfem::{atomic,diatomic}::dftgrid::DFTGrid (/root/reference/src/atomic/dftgrid.h:160-187)."""
+    _prefix = None
+
+    def __init__(self, basis, lang, mang):
+        L = lib()
+        self._basis = basis
+        self._h = ctypes.c_void_p()
+        getattr(L, self._prefix + "_grid_free").argtypes = [ctypes.c_void_p]
+        getattr(L, self._prefix + "_grid_free").restype = None
+        check_host(getattr(L, self._prefix + "_grid_new")(ctypes.byref(self._h), basis._h, int(lang), int(mang)))
+        self.lang, self.mang = lang, mang
+
+    def __del__(self):
+        try:
+            if self._h:
+                getattr(lib(), self._prefix + "_grid_free")(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def eval_Fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True):
+        """returns (H, Exc, Nel, Ekin) or (Ha, Hb, Exc, Nel, Ekin)"""
+        P = np.asfortranarray(P, dtype=np.float64)
+        H = np.zeros_like(P, order="F")
+        sc = np.zeros(3)
+        fn = getattr(lib(), self._prefix + "_grid_eval")
+        if Pb is None:
+            check_host(fn(self._h, self._basis._h, int(x_func), int(c_func), 1, _p(P), None, ctypes.c_double(thr), _p(H), None, 0, _p(sc)))
+            return H, sc[0], sc[1], sc[2]
+        Pb = np.asfortranarray(Pb, dtype=np.float64)
+        Hb = np.zeros_like(P, order="F")
+        check_host(fn(self._h, self._basis._h, int(x_func), int(c_func), 2, _p(P), _p(Pb), ctypes.c_double(thr), _p(H), _p(Hb),
+                      int(bool(beta)), _p(sc)))
+        return H, Hb, sc[0], sc[1], sc[2]
+
+
+class AtomicDFTGrid(_ProductGrid):
+    _prefix = "hfh_atomic"

@@ -3,6 +3,7 @@
 #include "../../include/helfem_b200.h"
 #include "chan_engine.h"
 #include "context.h"
+#include "grid2d.h"
 #include "xc_functionals.cuh"
 
 namespace hfb {
@@ -68,6 +69,7 @@ void hfb200_destroy(hfb200_ctx* c) {
   c->hIn.release();
   c->hOut.release();
   if (c->chan) { c->chan->release(); delete c->chan; }
+  if (c->g2d) { c->g2d->release(); delete c->g2d; }
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }

@@ -55,6 +55,7 @@ struct PinBuf {
 
 enum CtxKind { CTX_SADATOM = 1, CTX_ATOMIC = 2, CTX_DIATOMIC = 3 };
 struct ChanEngine;
+struct Grid2D;
 
 }  // namespace hfb
 
@@ -83,6 +84,7 @@ struct hfb200_ctx {
   double Rhalf = 0.0;
   int shard_rank = 0, shard_n = 1;  // integral families r with r % shard_n == shard_rank are owned
   hfb::ChanEngine* chan = nullptr;
+  hfb::Grid2D* g2d = nullptr;  // product-grid XC engine (grid2d.h)
   // ---- scratch ----
   hfb::DevBuf dP, dH, dJ, dPtot, dTraces, dPartial, dScalars, dK;
   hfb::PinBuf hIn, hOut;

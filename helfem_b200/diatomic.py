@@ -77,3 +77,22 @@ class DiatomicBasis:
         K = np.zeros_like(P, order="F")
         check_host(lib().hfh_diatomic_exchange(self._h, _p(P), _p(K)))
         return K
+
+    def radial(self, iel):
+        """r (= mu), wrad, bf, df of one element on its quadrature points (radial.get_r / get_wrad / get_bf / get_df,
+        /root/reference/src/diatomic/basis.cpp:266-285)."""
+        L = lib()
+        nq = L.hfh_diatomic_nquad(self._h)
+        npe = int(self.last[iel] - self.first[iel] + 1)
+        r, w = np.zeros(nq), np.zeros(nq)
+        bf, df = np.zeros((nq, npe), order="F"), np.zeros((nq, npe), order="F")
+        check_host(L.hfh_diatomic_radial(self._h, int(iel), _p(r), _p(w), _p(bf), _p(df)))
+        return r, w, bf, df
+
+
+from .atomic import _ProductGrid  # noqa: E402
+
+
+class DiatomicDFTGrid(_ProductGrid):
+    """hfb::diatomic::DFTGrid, mirror of helfem::diatomic::dftgrid::DFTGrid (/root/reference/src/diatomic/dftgrid.h:160-187)."""
+    _prefix = "hfh_diatomic"

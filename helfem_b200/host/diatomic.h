@@ -28,6 +28,15 @@ class RadialBasis {
   size_t Nprim(size_t iel) const { return fem.get_nprim(iel); }
   int get_nquad() const { return (int)xq.size(); }
   void get_idx(size_t iel, size_t& f, size_t& l) const { fem.get_idx(iel, f, l); }
+  /// B(mu), dB/dmu at the quadrature points (nq x Nprim(iel)); mu values and weights (basis.cpp:266-285)
+  Mat get_bf(size_t iel) const { return fem.eval_dnf(xq, 0, iel); }
+  Mat get_df(size_t iel) const { return fem.eval_dnf(xq, 1, iel); }
+  Vec get_r(size_t iel) const { return fem.eval_coord(xq, iel); }
+  Vec get_wrad(size_t iel) const {
+    Vec w(wq);
+    for (double& v : w) v *= fem.scaling_factor(iel);
+    return w;
+  }
   /// Legendre tables on every quadrature mu (outer points and the sub-interval points of the inner
   /// integrals), what LegendreTable holds in the reference (basis.cpp:229-264,394-398)
   void compute_legendre(int Lmax, int Mmax);

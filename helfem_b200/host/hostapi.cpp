@@ -8,6 +8,7 @@
 #include "../../include/helfem_b200.h"
 #include "angular.h"
 #include "atomic.h"
+#include "dftgrid.h"
 #include "diatomic.h"
 #include "legendre.h"
 #include "sadatom.h"
@@ -24,6 +25,26 @@ static thread_local std::string g_msg;
   catch (const std::exception& e) { g_msg = e.what(); return 3; }     \
   return 0;
 
+template <class Grid, class Basis>
+static int grid_eval(void* g, void* b, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr, double* Ha,
+                     double* Hb, int beta, double* scal3) {
+  HFH_TRY
+  const size_t n = ((Basis*)b)->Nbf();
+  Mat P1(n, n), P2, H1, H2;
+  memcpy(P1.ptr(), Pa, n * n * sizeof(double));
+  double exc = 0, nel = 0, ekin = 0;
+  if (nspin == 1) {
+    ((Grid*)g)->eval_Fxc(x_func, Vec(), c_func, Vec(), P1, H1, exc, nel, ekin, thr);
+  } else {
+    P2 = Mat(n, n);
+    memcpy(P2.ptr(), Pb, n * n * sizeof(double));
+    ((Grid*)g)->eval_Fxc(x_func, Vec(), c_func, Vec(), P1, P2, H1, H2, exc, nel, ekin, beta != 0, thr);
+    if (Hb) memcpy(Hb, H2.ptr(), n * n * sizeof(double));
+  }
+  memcpy(Ha, H1.ptr(), n * n * sizeof(double));
+  scal3[0] = exc; scal3[1] = nel; scal3[2] = ekin;
+  HFH_CATCH
+}
 extern "C" {
 
 const char* hfh_last_error(void) { return g_msg.c_str(); }
@@ -377,6 +398,41 @@ int hfh_diatomic_exchange(void* h, const double* P, double* K) {
   memcpy(K, Km.ptr(), n * n * sizeof(double));
   HFH_CATCH
 }
+
+// ---- product-grid DFT (atomic / diatomic DFTGrid) ----
+int hfh_atomic_grid_new(void** out, void* basis, int lang, int mang) {
+  HFH_TRY
+  *out = new atomic::DFTGrid((atomic::TwoDBasis*)basis, lang, mang);
+  HFH_CATCH
+}
+void hfh_atomic_grid_free(void* g) { delete (atomic::DFTGrid*)g; }
+int hfh_atomic_grid_eval(void* g, void* basis, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
+                         double* Ha, double* Hb, int beta, double* scal3) {
+  return grid_eval<atomic::DFTGrid, atomic::TwoDBasis>(g, basis, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
+}
+int hfh_diatomic_grid_new(void** out, void* basis, int lang, int mang) {
+  HFH_TRY
+  *out = new diatomic::DFTGrid((diatomic::TwoDBasis*)basis, lang, mang);
+  HFH_CATCH
+}
+void hfh_diatomic_grid_free(void* g) { delete (diatomic::DFTGrid*)g; }
+int hfh_diatomic_grid_eval(void* g, void* basis, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
+                           double* Ha, double* Hb, int beta, double* scal3) {
+  return grid_eval<diatomic::DFTGrid, diatomic::TwoDBasis>(g, basis, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
+}
+/// radial tables of one element: r, wrad (nq), bf, df (nq x np_el)
+int hfh_diatomic_radial(void* h, int iel, double* r, double* wrad, double* bf, double* df) {
+  HFH_TRY
+  const auto& rad = ((diatomic::TwoDBasis*)h)->get_radial();
+  const Vec rv = rad.get_r(iel), wv = rad.get_wrad(iel);
+  const Mat b = rad.get_bf(iel), d = rad.get_df(iel);
+  if (r) memcpy(r, rv.data(), rv.size() * sizeof(double));
+  if (wrad) memcpy(wrad, wv.data(), wv.size() * sizeof(double));
+  if (bf) memcpy(bf, b.ptr(), b.size() * sizeof(double));
+  if (df) memcpy(df, d.ptr(), d.size() * sizeof(double));
+  HFH_CATCH
+}
+int hfh_diatomic_nquad(void* h) { return ((diatomic::TwoDBasis*)h)->get_radial().get_nquad(); }
 
 int hfh_atomic_set_shard(void* h, int rank, int n) {
   HFH_TRY

@@ -10,6 +10,7 @@
  *   helfem::atomic::basis::TwoDBasis::coulomb/exchange atomic/TwoDBasis.cpp:817,957 -> hfb200_atomic_coulomb/_exchange
  *   helfem::atomic::dftgrid::DFTGrid::eval_Fxc(...)    atomic/dftgrid.cpp:810,872  -> hfb200_atomic_eval_fxc
  *   helfem::diatomic::basis::TwoDBasis::coulomb/exchange diatomic/basis.cpp:1359,1532 -> hfb200_diatomic_*
+ *   helfem::diatomic::dftgrid::DFTGrid::eval_Fxc(...)  diatomic/dftgrid.cpp:769,812 -> hfb200_diatomic_eval_fxc
  *
  * Conventions: all matrices are FP64 column-major with an explicit leading dimension (what
  * arma::mat::memptr() gives); every function returns 0 on success and a negative HFB200_E*
@@ -145,6 +146,30 @@ int hfb200_diatomic_set_tei(hfb200_ctx* ctx, int nlm, const int* Lmap, const int
                             const double* const* prim_tei, const double* const* prim_ktei);
 int hfb200_diatomic_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
 int hfb200_diatomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* K, int ldk);
+
+/* ------------------------------------------------------------------------------------------
+ * DFTGrid::eval_Fxc of the `atomic` and `diatomic` programs (angular x radial product grid).
+ *   atomic::dftgrid::DFTGrid::eval_Fxc     atomic/dftgrid.cpp:810 (restricted), :872 (unrestricted)
+ *   diatomic::dftgrid::DFTGrid::eval_Fxc   diatomic/dftgrid.cpp:769, :812
+ * hfb200_set_grid uploads the constants DFTGridWorker::compute_bf rebuilds on every call in the
+ * reference (atomic/dftgrid.cpp:710-796, diatomic/dftgrid.cpp:669-755), once per context (atomic or
+ * diatomic):  r, wrad: nel*nq (radial.get_r / get_wrad);  bf, df: per element (nq x np_el) column-major,
+ * concatenated (radial.get_bf / get_df);  the compound angular rule of angular::angular_chebyshev(lang, mang)
+ * (general/angular.cpp:64-71): cth, wang [nangpts];  ylm, dth_ylm: (nang x nangpts) complex as (re,im)
+ * pairs, entry [a + nang*ia]: Y_l^m and its theta derivative (atomic/TwoDBasis.cpp:1407-1419) at point ia.
+ * eval_fxc: atomic matrices are dense (nang*nrad)^2; diatomic ones are in the PURE basis like
+ * hfb200_diatomic_coulomb.  nspin = 1: Pa = P, Ha = H (Pb, Hb ignored).  nspin = 2: beta = 0 skips Hb
+ * (the reference's `bool beta`).  Outputs are overwritten (H.zeros in the reference).  Ekin = integral of
+ * tau (0 unless meta-GGA, atomic/dftgrid.cpp:262-275).
+ * ------------------------------------------------------------------------------------------ */
+int hfb200_set_grid(hfb200_ctx* ctx, int nq, const double* r, const double* wrad, const double* bf, const double* df,
+                    int nangpts, const double* cth, const double* wang, const double* ylm, const double* dth_ylm);
+int hfb200_atomic_eval_fxc(hfb200_ctx* ctx, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, int ldp,
+                           double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin);
+int hfb200_diatomic_eval_fxc(hfb200_ctx* ctx, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, int ldp,
+                             double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin);
+/* number of kernels the last product-grid eval_fxc launched (bench accounting) */
+int hfb200_grid_launches(hfb200_ctx* ctx);
 
 /* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
  * outputs are overwritten with exchange + correlation). */

@@ -5,6 +5,8 @@ cpu_baseline / --impl reference legs -- never by helfem_b200 (the product).
   fem_oracle.py        numpy restatement of the finite-element setup (tables + stored integrals)
   xc_oracle.hpp        XC functionals, complex-step derivatives
   hotpath_oracle.cpp   coulomb / exchange / eval_Fxc loops (liboracle.so, built by `make -C oracle`)
+  chan_oracle.cpp      atomic / diatomic coulomb and exchange
+  grid2d_oracle.cpp    atomic / diatomic DFTGrid::eval_Fxc on the angular x radial product grid
 
 Parity pins: see DESIGN.md section "Oracle".  XC values are "parity unpinned" upstream (libxc is an
 un-vendored, unversioned dependency of the reference and none of its tests holds an XC value).
@@ -212,3 +214,83 @@ class DiatomicOracle:
 
     def exchange(self, P):
         return self._apply(lib().oracle_diatomic_exchange, self.ktei, P)
+
+
+def angular_grid(lang, mang):
+    """angular::angular_chebyshev (/root/reference/src/general/angular.cpp:22-45,64-71): Chebyshev rule in cos(theta)
+    (fem_oracle.chebyshev) x uniform phi, point index i*nphi + j."""
+    from . import fem_oracle
+    x, w = fem_oracle.chebyshev(lang)
+    dphi = 2.0 * np.pi / mang
+    cth = np.repeat(x, mang)
+    phi = np.tile(np.arange(mang) * dphi, lang)
+    return cth, phi, np.repeat(w, mang) * dphi
+
+
+def ylm_table(lval, mval, cth, phi, shift=0):
+    """Y_l^{m+shift}(theta, phi) with the Condon-Shortley phase (what gsl_sf_legendre_sphPlm * e^{i m phi} gives,
+    /root/reference/src/general/spherical_harmonics.cpp:25-41) from scipy; (nang x npts) complex, zero where m+shift > l."""
+    from scipy.special import sph_harm_y
+    th = np.arccos(cth)
+    out = np.zeros((len(lval), len(cth)), dtype=np.complex128)
+    for a, (l, m) in enumerate(zip(lval, mval)):
+        if abs(m + shift) <= l:
+            out[a] = sph_harm_y(int(l), int(m + shift), th, phi)
+    return out
+
+
+class Grid2DOracle:
+    """Reference algorithm of atomic / diatomic DFTGrid::eval_Fxc on the CPU (oracle/grid2d_oracle.cpp), in the
+    full product ("dummy") space.  kind: 0 atomic, 1 diatomic.  r, wrad, bf, df: per-element lists
+    (radial.get_r / get_wrad / get_bf / get_df); pure: optional index list (expand / remove_boundaries)."""
+
+    def __init__(self, kind, lval, mval, first, last, r, wrad, bf, df, lang, mang, Rhalf=0.0, pure=None):
+        ci = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        self.kind, self.Rhalf = int(kind), float(Rhalf)
+        self.lval, self.mval, self.first, self.last = map(ci, (lval, mval, first, last))
+        self.nel, self.nang = len(self.first), len(self.lval)
+        self.nrad = int(self.last[-1]) + 1
+        self.nq = len(r[0])
+        self.r = np.ascontiguousarray(np.concatenate(r))
+        self.wrad = np.ascontiguousarray(np.concatenate(wrad))
+        self.bf = np.concatenate([np.asfortranarray(b).reshape(-1, order="F") for b in bf])
+        self.df = np.concatenate([np.asfortranarray(b).reshape(-1, order="F") for b in df])
+        self.cth, self.phi, self.wang = (np.ascontiguousarray(a) for a in angular_grid(lang, mang))
+        # memory order [a + nang*ia] as (re, im) pairs
+        self.Y = np.ascontiguousarray(ylm_table(self.lval, self.mval, self.cth, self.phi, 0).T)
+        self.Y1 = np.ascontiguousarray(ylm_table(self.lval, self.mval, self.cth, self.phi, 1).T)
+        self.pure = None if pure is None else np.asarray(pure)
+        self.nd = self.nang * self.nrad
+
+    def _expand(self, P):
+        if self.pure is None:
+            return np.asfortranarray(P, dtype=np.float64)
+        out = np.zeros((self.nd, self.nd), order="F")
+        out[np.ix_(self.pure, self.pure)] = P
+        return out
+
+    def _remove(self, H):
+        return H if self.pure is None else np.asfortranarray(H[np.ix_(self.pure, self.pure)])
+
+    def eval_fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True):
+        """returns (H, Exc, Nel, Ekin) or (Ha, Hb, Exc, Nel, Ekin)"""
+        Pa = self._expand(P)
+        nspin = 1 if Pb is None else 2
+        Pbx = None if Pb is None else self._expand(Pb)
+        Ha = np.zeros_like(Pa, order="F")
+        Hb = None if Pb is None else np.zeros_like(Pa, order="F")
+        exc, nel, ekin = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+        Yv = self.Y.view(np.float64)
+        Y1v = self.Y1.view(np.float64)
+        rc = lib().oracle_grid2d_eval_fxc(self.kind, ctypes.c_double(self.Rhalf), self.nang, _ip(self.lval), _ip(self.mval),
+                                          self.nel, self.nq, _ip(self.first), _ip(self.last), self.nrad, _p(self.r),
+                                          _p(self.wrad), _p(self.bf), _p(self.df), len(self.cth), _p(self.cth), _p(self.phi),
+                                          _p(self.wang), _p(Yv), _p(Y1v), int(x_func), int(c_func), nspin, _p(Pa),
+                                          _p(Pbx) if Pbx is not None else None, ctypes.c_double(thr), _p(Ha),
+                                          _p(Hb) if Hb is not None else None, int(bool(beta)), ctypes.byref(exc),
+                                          ctypes.byref(nel), ctypes.byref(ekin))
+        if rc != 0:
+            raise RuntimeError("oracle: functional not restated")
+        if Pb is None:
+            return self._remove(Ha), exc.value, nel.value, ekin.value
+        return self._remove(Ha), self._remove(Hb), exc.value, nel.value, ekin.value

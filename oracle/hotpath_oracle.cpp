@@ -69,6 +69,7 @@ struct Tables {
 extern "C" {
 
 double oracle_gaunt(int L, int M, int l, int m, int lp, int mp) { return gaunt(L, M, l, m, lp, mp); }
+int oracle_xc_family(int func) { return oracle_xc::family(func); }
 
 void oracle_xc_unpol(int func, int n, double thr, const double* rho, const double* sigma, const double* tau,
                      double* exc, double* vrho, double* vsigma, double* vtau) {
