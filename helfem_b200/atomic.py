@@ -112,15 +112,17 @@ class _ProductGrid:
     def eval_Fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True):
         """returns (H, Exc, Nel, Ekin) or (Ha, Hb, Exc, Nel, Ekin)"""
         P = np.asfortranarray(P, dtype=np.float64)
+        if P.ndim != 2 or P.shape[0] != P.shape[1] or (Pb is not None and np.shape(Pb) != P.shape):
+            raise ValueError("density matrices must be square and of equal shape")
         H = np.zeros_like(P, order="F")
         sc = np.zeros(3)
         fn = getattr(lib(), self._prefix + "_grid_eval")
         if Pb is None:
-            check_host(fn(self._h, self._basis._h, int(x_func), int(c_func), 1, _p(P), None, ctypes.c_double(thr), _p(H), None, 0, _p(sc)))
+            check_host(fn(self._h, self._basis._h, int(P.shape[0]), int(x_func), int(c_func), 1, _p(P), None, ctypes.c_double(thr), _p(H), None, 0, _p(sc)))
             return H, sc[0], sc[1], sc[2]
         Pb = np.asfortranarray(Pb, dtype=np.float64)
         Hb = np.zeros_like(P, order="F")
-        check_host(fn(self._h, self._basis._h, int(x_func), int(c_func), 2, _p(P), _p(Pb), ctypes.c_double(thr), _p(H), _p(Hb),
+        check_host(fn(self._h, self._basis._h, int(P.shape[0]), int(x_func), int(c_func), 2, _p(P), _p(Pb), ctypes.c_double(thr), _p(H), _p(Hb),
                       int(bool(beta)), _p(sc)))
         return H, Hb, sc[0], sc[1], sc[2]
 

@@ -26,10 +26,11 @@ static thread_local std::string g_msg;
   return 0;
 
 template <class Grid, class Basis>
-static int grid_eval(void* g, void* b, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr, double* Ha,
-                     double* Hb, int beta, double* scal3) {
+static int grid_eval(void* g, void* b, int nrows, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
+                     double* Ha, double* Hb, int beta, double* scal3) {
   HFH_TRY
-  const size_t n = ((Basis*)b)->Nbf();
+  (void)b;
+  const size_t n = (size_t)nrows;  // the mirror class checks it against the basis like the reference does
   Mat P1(n, n), P2, H1, H2;
   memcpy(P1.ptr(), Pa, n * n * sizeof(double));
   double exc = 0, nel = 0, ekin = 0;
@@ -406,9 +407,9 @@ int hfh_atomic_grid_new(void** out, void* basis, int lang, int mang) {
   HFH_CATCH
 }
 void hfh_atomic_grid_free(void* g) { delete (atomic::DFTGrid*)g; }
-int hfh_atomic_grid_eval(void* g, void* basis, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
+int hfh_atomic_grid_eval(void* g, void* basis, int nrows, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
                          double* Ha, double* Hb, int beta, double* scal3) {
-  return grid_eval<atomic::DFTGrid, atomic::TwoDBasis>(g, basis, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
+  return grid_eval<atomic::DFTGrid, atomic::TwoDBasis>(g, basis, nrows, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
 }
 int hfh_diatomic_grid_new(void** out, void* basis, int lang, int mang) {
   HFH_TRY
@@ -416,9 +417,9 @@ int hfh_diatomic_grid_new(void** out, void* basis, int lang, int mang) {
   HFH_CATCH
 }
 void hfh_diatomic_grid_free(void* g) { delete (diatomic::DFTGrid*)g; }
-int hfh_diatomic_grid_eval(void* g, void* basis, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
+int hfh_diatomic_grid_eval(void* g, void* basis, int nrows, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, double thr,
                            double* Ha, double* Hb, int beta, double* scal3) {
-  return grid_eval<diatomic::DFTGrid, diatomic::TwoDBasis>(g, basis, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
+  return grid_eval<diatomic::DFTGrid, diatomic::TwoDBasis>(g, basis, nrows, x_func, c_func, nspin, Pa, Pb, thr, Ha, Hb, beta, scal3);
 }
 /// radial tables of one element: r, wrad (nq), bf, df (nq x np_el)
 int hfh_diatomic_radial(void* h, int iel, double* r, double* wrad, double* bf, double* df) {
