@@ -26,6 +26,8 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
@@ -38,6 +40,23 @@ WORKLOADS = {
     "ne_pbe_small": dict(Z=10, primbas=4, nnodes=15, nelem=5, taylor=-1, lmax=2, x=101, c=130, nspin=1,
                          desc="small smoke case"),
 }
+
+
+def ncu_traffic(workload, kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same
+    workload (profiles/ncu_traffic.json, written from the .ncu-rep by tools/ncu_summary.py); None if not captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p))[workload][kernel]
+    except Exception:
+        return None
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
 def peaks():
@@ -169,6 +188,7 @@ def run_reference(args, w, rank):
     b = make_basis_host_only(w)
     o = oracle_from_basis(b)
     dens = make_densities(b, w)
+    oracle.lib().oracle_set_num_threads(host_threads())  # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every core
     nthreads = oracle.lib().oracle_num_threads()
     one = cpu_builds(o, w, dens, 1)
     per_step = max(1, min(args.batch, int(2.0 / max(one, 1e-6))))  # ~2 s of CPU work per step
@@ -350,18 +370,21 @@ def run_gpu(args, w, rank, world, local_rank):
         kflops = alg["j_flops"] * nb
     achieved = kbytes / (kms * 1e-3) / 1e9
     roofline = {"kernel": kname, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / hbm_peak, "traffic": ncu_traffic(args.workload, kname), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": kbytes, "ms_per_launch": kms,
                 "fp64_tflops_algorithmic": kflops / (kms * 1e-3) / 1e12,
                 "ms_grid_kernel": ms_grid, "ms_coulomb_kernels": ms_j}
     # CPU baseline: the oracle port on this box's host cores, bounded sample
-    import oracle
-    o = oracle_from_basis(b)
-    one = cpu_builds(o, w, dens, 1)
-    nsample = max(2, min(200, int(10.0 / max(one, 1e-6))))
-    tc = cpu_builds(o, w, dens, nsample)
-    cpu = {"value": nsample / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
-           "sample": "%d Fock builds (coulomb + eval_Fxc) of the same workload" % nsample}
+    cpu = None
+    if world == 1:  # reported at N = 1 only
+        import oracle
+        oracle.lib().oracle_set_num_threads(host_threads())
+        o = oracle_from_basis(b)
+        one = cpu_builds(o, w, dens, 1)
+        nsample = max(2, min(200, int(10.0 / max(one, 1e-6))))
+        tc = cpu_builds(o, w, dens, nsample)
+        cpu = {"value": nsample / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
+               "sample": "%d Fock builds (coulomb + eval_Fxc) of the same workload" % nsample}
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",

@@ -347,4 +347,13 @@ int oracle_num_threads(void) {
 #endif
 }
 
+/// bench.py under torchrun inherits OMP_NUM_THREADS=1; the CPU arm asks for all host threads explicitly
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 }  // extern "C"
