@@ -2,6 +2,7 @@
 #include "chan_engine.h"
 
 #include <algorithm>
+#include <cstdint>
 #include <cstring>
 #include <map>
 #include "../../include/helfem_b200.h"
@@ -125,13 +126,13 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
   return 0;
 }
 
-// Exchange tables: K-ordered in-element integrals, full-square disjoint factors, and per output angular
-// pair (j,k) the list of (input pair (i,l), family, coefficient[a][b]) with
-//   coef_ab = fac_r * (-1)^{a != b} * c^a_c(j,i) * c^b_c(k,l),   c = channel shared by both pairs
+// Exchange tables (chan_exchange.cuh): K-ordered in-element integrals swizzled into DMMA A-fragment order,
+// full-square disjoint factors, and the coupling rows  (channel c, j) -> (i, c^0_c(j,i), c^1_c(j,i))
 // (atomic/TwoDBasis.cpp:1023-1059, diatomic/basis.cpp:1604-1650).
 int ChanEngine::build_exchange(const ChanSpec& S) {
-  const int nel = S.nel, nang = S.nang, st = S.stack, nr = S.nr, np = prm.np, np2 = prm.np2;
+  const int nel = S.nel, nang = S.nang, st = S.stack, nr = S.nr, np = prm.np, np2 = prm.np2, st2 = st * st;
   xprm.nel = nel; xprm.np = np; xprm.np2 = np2; xprm.stack = st; xprm.nrad = nrad; xprm.nang = nang;
+  if (np > 32) { set_error("exchange: more than 32 radial functions per element are not supported"); return HFB200_EINVAL; }
   int rc;
   std::vector<int> npe(nel), elem_of(2 * (size_t)nrad, -1);
   for (int e = 0; e < nel; e++) {
@@ -143,6 +144,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     }
   }
   if ((rc = up(this, &xprm.first, first)) || (rc = up(this, &xprm.npe, npe)) || (rc = up(this, &xprm.elem_of, elem_of))) return rc;
+  fam_fac = S.fac;
   // disjoint factors, zero padded squares
   {
     std::vector<double> sm((size_t)nr * nel * st * np2, 0.0), bg((size_t)nr * nel * st * np2, 0.0);
@@ -162,90 +164,167 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
         }
     if ((rc = up(this, &xprm.small_f, sm)) || (rc = up(this, &xprm.big_f, bg))) return rc;
   }
-  // K-ordered integrals, zero padded, one (family, element, a, b) block at a time
+  // K-ordered integrals: rows (j,k) x cols (i,l), zero padded to np, in A-fragment order [mtile][kstep][lane]
   {
-    const size_t blk = (size_t)np2 * np2;
+    const int MT = (np2 + 7) / 8, KS = (np2 + 3) / 4;
+    int LDK = 4 * KS;
+    while ((LDK & 15) != 4) LDK++;
+    xprm.MT = MT; xprm.KS = KS; xprm.LDK = LDK;
+    const size_t blk = (size_t)MT * KS * 32;
     double* d = nullptr;
-    HFB_CUDA_OK(cudaMalloc(&d, (size_t)nr * nel * st * st * blk * sizeof(double)));
+    HFB_CUDA_OK(cudaMalloc(&d, (size_t)nr * nel * st2 * blk * sizeof(double)));
     owned.push_back(d);
-    xprm.ktei = d;
-    std::vector<double> stage(blk);
-    for (int r = 0; r < nr; r++)
-      for (int e = 0; e < nel; e++)
-        for (int a = 0; a < st; a++)
-          for (int b = 0; b < st; b++) {
-            double sg = 1.0;
-            const double* t = S.ktei(r, e, a, b, &sg);
-            double* dst = d + ((((size_t)r * nel + e) * st + a) * st + b) * blk;
-            if (!t) { HFB_CUDA_OK(cudaMemset(dst, 0, blk * sizeof(double))); continue; }
-            const int n = npe[e];
-            if (n == np) {
-              HFB_CUDA_OK(cudaMemcpy(dst, t, blk * sizeof(double), cudaMemcpyHostToDevice));
-            } else {
-              std::fill(stage.begin(), stage.end(), 0.0);
-              const size_t n2 = (size_t)n * n;
-              for (int cs = 0; cs < n; cs++)
-                for (int cf = 0; cf < n; cf++)
-                  for (int rs = 0; rs < n; rs++)
-                    for (int rf = 0; rf < n; rf++)
-                      stage[(size_t)(rf + rs * np) + (size_t)(cf + cs * np) * np2] = t[(size_t)(rf + rs * n) + (size_t)(cf + cs * n) * n2];
-              HFB_CUDA_OK(cudaMemcpy(dst, stage.data(), blk * sizeof(double), cudaMemcpyHostToDevice));
-            }
-          }
-  }
-  // coupling lists
-  {
-    struct Ent { int in, r; double c[4]; };
-    std::vector<int> xptr(1, 0), xin, xr, out_list;
-    std::vector<double> xcoef;
-    for (int j = 0; j < nang; j++)
-      for (int k = 0; k < nang; k++) {
-        std::vector<Ent> ents;
-        for (int i = 0; i < nang; i++) {
-          const auto& cji = S.pair_coupl[j * nang + i];
-          if (cji.empty()) continue;
-          for (int l = 0; l < nang; l++) {
-            const auto& ckl = S.pair_coupl[k * nang + l];
-            for (const auto& A : cji)
-              for (const auto& B : ckl) {
-                if (A.chan != B.chan) continue;
-                const int r = S.chan_r[A.chan];
-                Ent en;
-                en.in = i * nang + l;
-                en.r = r;
-                bool any = false;
-                for (int a = 0; a < 2; a++)
-                  for (int b = 0; b < 2; b++) {
-                    double v = 0.0;
-                    if (a < st && b < st) v = S.fac[r] * (a != b ? -1.0 : 1.0) * A.coef[a] * B.coef[b];
-                    en.c[2 * a + b] = v;
-                    any = any || v != 0.0;
-                  }
-                if (any) ents.push_back(en);
+    xprm.teiK = d;
+    HFB_CUDA_OK(cudaMemset(d, 0, (size_t)nr * nel * st2 * blk * sizeof(double)));
+    const int nstage = 16;
+    std::vector<std::vector<double>> stage(nstage, std::vector<double>(blk));
+    const long nblk = (long)nr * nel * st2;
+    for (long b0 = 0; b0 < nblk; b0 += nstage) {
+      const int nb = (int)std::min<long>(nstage, nblk - b0);
+      std::vector<char> present(nb, 0);
+#pragma omp parallel for schedule(dynamic)
+      for (int q = 0; q < nb; q++) {
+        const long id = b0 + q;
+        const int ab = (int)(id % st2), e = (int)((id / st2) % nel), r = (int)(id / ((long)st2 * nel));
+        double sg = 1.0;
+        const double* t = S.ktei(r, e, ab / st, ab % st, &sg);
+        if (!t) continue;
+        present[q] = 1;
+        std::vector<double>& F = stage[q];
+        std::fill(F.begin(), F.end(), 0.0);
+        const int n = npe[e];
+        const size_t n2 = (size_t)n * n;
+        for (int cs = 0; cs < n; cs++)
+          for (int cf = 0; cf < n; cf++) {
+            const int k = cf + cs * np;
+            const double* col = t + (size_t)(cf + cs * n) * n2;
+            for (int rs = 0; rs < n; rs++)
+              for (int rf = 0; rf < n; rf++) {
+                const int m = rf + rs * np;
+                F[((size_t)(m >> 3) * KS + (k >> 2)) * 32 + (m & 7) * 4 + (k & 3)] = col[rf + rs * n];
               }
           }
-        }
-        if (ents.empty()) continue;
-        std::stable_sort(ents.begin(), ents.end(), [](const Ent& x, const Ent& y) { return x.r < y.r; });
-        out_list.push_back(j * nang + k);
-        for (const auto& en : ents) {
-          xin.push_back(en.in);
-          xr.push_back(en.r);
-          // kernel reads coefficient (a,b) at a*stack + b
-          double cc[4] = {0, 0, 0, 0};
-          for (int a = 0; a < st; a++)
-            for (int b = 0; b < st; b++) cc[a * st + b] = en.c[2 * a + b];
-          xcoef.insert(xcoef.end(), cc, cc + 4);
-        }
-        xptr.push_back((int)xin.size());
       }
-    nout = (int)out_list.size();
-    out_pairs_host = out_list;
-    if ((rc = up(this, &xprm.xptr, xptr)) || (rc = up(this, &xprm.xin, xin)) || (rc = up(this, &xprm.xr, xr)) ||
-        (rc = up(this, &xprm.xcoef, xcoef)) || (rc = up(this, &xprm.out_list, out_list)))
-      return rc;
+      for (int q = 0; q < nb; q++)
+        if (present[q]) HFB_CUDA_OK(cudaMemcpy(d + (size_t)(b0 + q) * blk, stage[q].data(), blk * sizeof(double), cudaMemcpyHostToDevice));
+    }
   }
+  // coupling rows by channel
+  {
+    std::vector<int> cnt((size_t)nchan * nang + 1, 0);
+    for (int j = 0; j < nang; j++)
+      for (int i = 0; i < nang; i++)
+        for (const auto& cp : S.pair_coupl[(size_t)j * nang + i])
+          if (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0)) cnt[(size_t)cp.chan * nang + j + 1]++;
+    for (size_t q = 0; q < (size_t)nchan * nang; q++) cnt[q + 1] += cnt[q];
+    xrowptr = cnt;
+    xrow_i.assign(cnt.back(), 0);
+    std::vector<double> coef(2 * (size_t)cnt.back(), 0.0);
+    std::vector<int> fill(cnt.begin(), cnt.end() - 1);
+    for (int j = 0; j < nang; j++)
+      for (int i = 0; i < nang; i++)  // i ascending within a row
+        for (const auto& cp : S.pair_coupl[(size_t)j * nang + i])
+          if (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0)) {
+            const int pos = fill[(size_t)cp.chan * nang + j]++;
+            xrow_i[pos] = i;
+            coef[2 * (size_t)pos] = cp.coef[0];
+            coef[2 * (size_t)pos + 1] = st == 2 ? cp.coef[1] : 0.0;
+          }
+    std::vector<int2> rows;
+    fam_row0.assign(nr + 1, 0);
+    nch_max = 1;
+    for (int r = 0; r < nr; r++) {
+      nch_max = std::max(nch_max, fam_c0_host[r + 1] - fam_c0_host[r]);
+      for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
+        for (int j = 0; j < nang; j++)
+          if (xrowptr[(size_t)c * nang + j + 1] > xrowptr[(size_t)c * nang + j]) rows.push_back(make_int2(c, j));
+      fam_row0[r + 1] = (int)rows.size();
+    }
+    const int2* drows = nullptr;
+    if ((rc = up(this, &xprm.rowptr, xrowptr)) || (rc = up(this, &xprm.row_i, xrow_i)) || (rc = up(this, &xprm.row_coef, coef)) ||
+        (rc = up(this, &drows, rows)))
+      return rc;
+    dRows = const_cast<int2*>(drows);
+  }
+  {
+    unsigned char* p = nullptr;
+    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang));
+    owned.push_back(p);
+    dNzP = p;
+    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nch_max * nang * nang));
+    owned.push_back(p);
+    dWmask = p;
+    if (hNzP) cudaFreeHost(hNzP);
+    HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang));
+  }
+  mask_cached.clear();
   have_k = true;
+  return 0;
+}
+
+// Output blocks of every family for one sparsity pattern of P: (j,k) is an item of family r when some channel
+// c of r has rows (c,j), (c,k) and a non-zero block P[i,l] with i in row (c,j), l in row (c,k).
+int ChanEngine::build_items(const unsigned char* nz) {
+  const int nang = xprm.nang, nr = prm.nr, nw = (nang + 63) / 64;
+  std::vector<uint64_t> nzrow((size_t)nang * nw, 0);  // nzrow[i] = { l : P[i,l] != 0 }
+  for (int i = 0; i < nang; i++)
+    for (int l = 0; l < nang; l++)
+      if (nz[(size_t)i * nang + l]) nzrow[(size_t)i * nw + (l >> 6)] |= (uint64_t)1 << (l & 63);
+  std::vector<std::vector<int2>> fam_items(nr);
+#pragma omp parallel
+  {
+    std::vector<uint64_t> lset((size_t)nang * nw), rowset((size_t)nang * nw);
+    std::vector<unsigned char> hit((size_t)nang * nang);
+    std::vector<int> js;
+#pragma omp for schedule(dynamic)
+    for (int r = 0; r < nr; r++) {
+      if (fam_row0[r + 1] == fam_row0[r]) continue;
+      std::fill(hit.begin(), hit.end(), 0);
+      for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++) {
+        js.clear();
+        for (int j = 0; j < nang; j++) {
+          const int e0 = xrowptr[(size_t)c * nang + j], e1 = xrowptr[(size_t)c * nang + j + 1];
+          if (e0 == e1) continue;
+          js.push_back(j);
+          uint64_t* ls = &lset[(size_t)j * nw];
+          uint64_t* rs = &rowset[(size_t)j * nw];
+          for (int w = 0; w < nw; w++) { ls[w] = 0; rs[w] = 0; }
+          for (int e = e0; e < e1; e++) {
+            const int i = xrow_i[e];
+            rs[i >> 6] |= (uint64_t)1 << (i & 63);
+            for (int w = 0; w < nw; w++) ls[w] |= nzrow[(size_t)i * nw + w];
+          }
+        }
+        for (int j : js)
+          for (int k : js) {
+            if (hit[(size_t)j * nang + k]) continue;
+            uint64_t any = 0;
+            for (int w = 0; w < nw; w++) any |= lset[(size_t)j * nw + w] & rowset[(size_t)k * nw + w];
+            if (any) hit[(size_t)j * nang + k] = 1;
+          }
+      }
+      for (int j = 0; j < nang; j++)
+        for (int k = 0; k < nang; k++)
+          if (hit[(size_t)j * nang + k]) fam_items[r].push_back(make_int2(j, k));
+    }
+  }
+  fam_item0.assign(nr + 1, 0);
+  max_items = 0;
+  for (int r = 0; r < nr; r++) {
+    fam_item0[r + 1] = fam_item0[r] + (int)fam_items[r].size();
+    max_items = std::max(max_items, (int)fam_items[r].size());
+  }
+  std::vector<int2> all;
+  all.reserve(fam_item0[nr]);
+  for (int r = 0; r < nr; r++) all.insert(all.end(), fam_items[r].begin(), fam_items[r].end());
+  if (all.size() > items_cap) {
+    if (dItems) cudaFree(dItems);
+    dItems = nullptr;
+    items_cap = 0;
+    HFB_CUDA_OK(cudaMalloc(&dItems, std::max<size_t>(all.size(), 1) * sizeof(int2)));
+    items_cap = std::max<size_t>(all.size(), 1);
+  }
+  if (!all.empty()) HFB_CUDA_OK(cudaMemcpy(dItems, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
   return 0;
 }
 
@@ -311,26 +390,89 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
   return 0;
 }
 
+namespace {
+template <int NI>
+int launch_x3(const ChanXParams& q, int r, int nitems, size_t smem, cudaStream_t st) {
+  const dim3 grid((nitems + NI - 1) / NI, q.nel * q.nel);
+  const int ntl = (q.np + 7) / 8;
+#define HFB_X3(NTL)                                                                                                   \
+  {                                                                                                                   \
+    static bool attr_set = false;                                                                                     \
+    if (!attr_set) {                                                                                                  \
+      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
+      attr_set = true;                                                                                                \
+    }                                                                                                                 \
+    chan_x3_kernel<NI, NTL><<<grid, 256, smem, st>>>(q, r, nitems);                                                   \
+  }
+  switch (ntl) {
+    case 1: HFB_X3(1) break;
+    case 2: HFB_X3(2) break;
+    case 3: HFB_X3(3) break;
+    default: HFB_X3(4) break;
+  }
+#undef HFB_X3
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
 // -K = exchange(P), dense host matrices.
 int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad;
+  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
+  const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
   int rc;
   if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) ||
-      (rc = dKblocks.reserve((size_t)std::max(nout, 1) * nel * nel * np2)))
+      (rc = dW.reserve((size_t)nch_max * stack * nang2 * nrad2)))
     return rc;
   HFB_CUDA_OK(cudaMemcpy2DAsync(dPdense.p, ntot * sizeof(double), P, ldp * sizeof(double), ntot * sizeof(double), ntot,
                                 cudaMemcpyHostToDevice, st));
   HFB_CUDA_OK(cudaMemsetAsync(dKdense.p, 0, (size_t)ntot * ntot * sizeof(double), st));
-  if (nout > 0) {
+  // block mask of P; the item lists are rebuilt only when the sparsity pattern changes
+  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPdense.p, ntot, nrad, nang, dNzP);
+  HFB_CUDA_OK(cudaGetLastError());
+  HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2, cudaMemcpyDeviceToHost, st));
+  HFB_CUDA_OK(cudaStreamSynchronize(st));
+  if (mask_cached.size() != nang2 || memcmp(mask_cached.data(), hNzP, nang2) != 0) {
+    if ((rc = build_items(hNzP))) return rc;
+    mask_cached.assign(hNzP, hNzP + nang2);
+  }
+  if (max_items > 0) {
+    const size_t need_r = (size_t)max_items * st2 * nel * nel * np2;
+    if (need_r > dRsub.cap) {
+      if ((rc = dRsub.reserve(need_r))) return rc;
+      HFB_CUDA_OK(cudaMemsetAsync(dRsub.p, 0, need_r * sizeof(double), st));  // padding positions stay zero for good
+    }
+    if ((rc = dKblocks.reserve((size_t)max_items * nel * nel * np2))) return rc;
     ChanXParams q = xprm;
-    q.P = dPdense.p; q.ldp = ntot; q.blocks = dKblocks.p;
-    const size_t smem = (size_t)(prm.stack * prm.stack + 2) * np2 * sizeof(double);
-    HFB_CUDA_OK(cudaFuncSetAttribute(chan_exchange_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    chan_exchange_block_kernel<<<dim3(nel * nel, nout), 256, smem, st>>>(q);
-    HFB_CUDA_OK(cudaGetLastError());
-    chan_exchange_assemble_kernel<<<148 * 8, 256, 0, st>>>(q, nout, dKdense.p, ntot);
-    HFB_CUDA_OK(cudaGetLastError());
+    q.P = dPdense.p; q.ldp = ntot; q.nzP = dNzP; q.W = dW.p; q.Wmask = dWmask; q.Rsub = dRsub.p; q.blocks = dKblocks.p;
+    q.K = dKdense.p; q.ldk = ntot;
+    // x3 tile: NI items per CTA, as many as the shared-memory tile allows
+    const int ntl = (prm.np + 7) / 8;
+    const size_t ybytes = (size_t)8 * 8 * ntl * (8 * ntl + 1) * sizeof(double);
+    int NI = 32;
+    while (NI > 8 && (size_t)NI * q.LDK * sizeof(double) > 200 * 1024) NI >>= 1;
+    const size_t smem = std::max((size_t)NI * q.LDK * sizeof(double), ybytes);
+    if (smem > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
+    const int nchunk = (int)((nrad2 + 256 * CHX_EPT - 1) / (256 * CHX_EPT));
+    for (int r = 0; r < prm.nr; r++) {
+      const int nrows = fam_row0[r + 1] - fam_row0[r], nitems = fam_item0[r + 1] - fam_item0[r];
+      if (nrows == 0 || nitems == 0) continue;
+      const int c0 = fam_c0_host[r], nch = fam_c0_host[r + 1] - c0;
+      const int2* items = dItems + fam_item0[r];
+      HFB_CUDA_OK(cudaMemsetAsync(dWmask, 0, (size_t)nch * nang2, st));
+      chan_x1_kernel<<<dim3(nrows, std::min(nang, 8)), 256, 0, st>>>(q, dRows + fam_row0[r], c0);
+      HFB_CUDA_OK(cudaGetLastError());
+      chan_x2_kernel<<<dim3(nitems, nchunk), 256, 0, st>>>(q, items, c0, nch, fam_fac[r]);
+      HFB_CUDA_OK(cudaGetLastError());
+      if (NI == 32) rc = launch_x3<32>(q, r, nitems, smem, st);
+      else if (NI == 16) rc = launch_x3<16>(q, r, nitems, smem, st);
+      else rc = launch_x3<8>(q, r, nitems, smem, st);
+      if (rc) return rc;
+      const size_t work = (size_t)nitems * nrad2;
+      chan_x4_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(q, items, nitems);
+      HFB_CUDA_OK(cudaGetLastError());
+    }
   }
   HFB_CUDA_OK(cudaMemcpy2DAsync(K, ldk * sizeof(double), dKdense.p, ntot * sizeof(double), ntot * sizeof(double), ntot,
                                 cudaMemcpyDeviceToHost, st));
@@ -341,7 +483,12 @@ int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cud
 void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
-  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks}) b->release();
+  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRsub}) b->release();
+  if (dItems) cudaFree(dItems);
+  dItems = nullptr;
+  items_cap = 0;
+  if (hNzP) cudaFreeHost(hNzP);
+  hNzP = nullptr;
   hIn.release();
   hOut.release();
 }

@@ -39,12 +39,24 @@ struct ChanEngine {
   DevBuf dP, dPc, dTr, dJc, dJ;
   PinBuf hIn, hOut;
   std::vector<int> fam_c0_host, out_pairs_host;
-  // exchange tables
+  // exchange tables (chan_exchange.cuh)
   bool have_k = false;
   ChanXParams xprm{};
-  int nout = 0;
-  DevBuf dPdense, dKdense, dKblocks;
+  int nch_max = 0, x3_ni = 32;
+  std::vector<double> fam_fac;                      // [nr]
+  std::vector<int> xrowptr, xrow_i;                 // host copy of the coupling rows (item lists are derived from them)
+  std::vector<int> fam_row0;                        // [nr+1] range of each family in dRows
+  int2* dRows = nullptr;                            // (channel, j) of every non-empty coupling row, grouped by family
+  // per sparsity pattern of P: the output blocks ("items") of every family
+  std::vector<unsigned char> mask_cached;
+  std::vector<int> fam_item0;                       // [nr+1]
+  int2* dItems = nullptr;
+  size_t items_cap = 0;
+  int max_items = 0;
+  unsigned char *dNzP = nullptr, *dWmask = nullptr, *hNzP = nullptr;
+  DevBuf dPdense, dKdense, dKblocks, dW, dRsub;
 
+  int build_items(const unsigned char* nz);
   int build_exchange(const ChanSpec& spec);
   int build(const ChanSpec& spec, bool with_exchange);
   int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st);

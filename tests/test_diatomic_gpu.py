@@ -81,3 +81,24 @@ def test_diatomic_missing_tei_is_logic_error(native):
     b = hb.DiatomicBasis(1, 1, 1.4, nelem=1, nnodes=4, lmax=0, mmax=0)
     with pytest.raises(ValueError):
         b.coulomb(np.zeros((b.nbf, b.nbf)))
+
+
+@pytest.mark.parametrize("case", ["n2_l2m1", "co_l3m2"])
+def test_diatomic_exchange_block_sparse_density(native, case):
+    """An m-diagonal density (what an SCF of a linear molecule produces): the zero angular blocks of P are skipped
+    through the block mask and the per-pattern output lists; a second pattern on the same basis rebuilds them."""
+    b, o, P = setup_case(case)
+    pure = b.pure_indices()
+    m = np.array([b.mval[p // b.nrad] for p in pure])
+    Pm = np.asfortranarray(P * (m[:, None] == m[None, :]))
+    K, Ko = b.exchange(Pm), o.exchange(Pm)
+    assert np.max(np.abs(K - Ko)) <= tol(Ko)
+    # sigma-only density: most output blocks vanish
+    Ps = np.asfortranarray(P * ((m[:, None] == 0) & (m[None, :] == 0)))
+    K, Ko = b.exchange(Ps), o.exchange(Ps)
+    assert np.max(np.abs(K - Ko)) <= tol(Ko)
+    # and back to the dense pattern
+    K, Ko = b.exchange(P), o.exchange(P)
+    assert np.max(np.abs(K - Ko)) <= tol(Ko)
+    Z = b.exchange(np.zeros_like(P))
+    assert np.max(np.abs(Z)) == 0.0
