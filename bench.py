@@ -37,6 +37,15 @@ WORKLOADS = {
                         desc="gensap --Z Kr --nelem 20 --nnodes 15 --primbas 4 --method gga_x_pbe-gga_c_pbe (configs[1])"),
     "rn_r2scan_cfg3": dict(Z=86, primbas=5, nnodes=15, nelem=40, taylor=20, lmax=3, x=497, c=498, nspin=2,
                            desc="gensap --Z Rn --nelem 40 --nnodes 15 --primbas 5 --method mgga_x_r2scan-mgga_c_r2scan (configs[2])"),
+    # Hartree-Fock builds of the atomic / diatomic programs: coulomb(P) + exchange(P) through the channel engine
+    "ne_hf_cfg1": dict(kind="atomic", Z=10, lmax=0, mmax=0, nelem=10, nnodes=15, primbas=4, nocc=5,
+                       desc="atomic --Z Ne --lmax 0 --mmax 0 --nelem 10 --nnodes 15 --primbas 4 --method HF (configs[0])"),
+    "n2_hf_cfg4": dict(kind="diatomic", Z1=7, Z2=7, Rbond=2.068, lmax=24, mmax=6, nelem=5, nnodes=15, primbas=4,
+                       desc="diatomic --Z1 N --Z2 N --Rbond 2.068 --lmax 24 --mmax 6 --nelem 5 --nnodes 15 --primbas 4 --method HF (configs[3])"),
+    "n2_hf_l12m3": dict(kind="diatomic", Z1=7, Z2=7, Rbond=2.068, lmax=12, mmax=3, nelem=5, nnodes=15, primbas=4,
+                        desc="diatomic N2, lmax 12, mmax 3, 5 elements (half-size version of configs[3])"),
+    "n2_hf_l4m1": dict(kind="diatomic", Z1=7, Z2=7, Rbond=2.068, lmax=4, mmax=1, nelem=3, nnodes=10, primbas=4,
+                       desc="diatomic N2, lmax 4, mmax 1, 3 elements (small case the CPU oracle finishes in seconds)"),
     "ne_pbe_small": dict(Z=10, primbas=4, nnodes=15, nelem=5, taylor=-1, lmax=2, x=101, c=130, nspin=1,
                          desc="small smoke case"),
 }
@@ -404,6 +413,181 @@ def run_gpu(args, w, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------
+# atomic / diatomic Hartree-Fock builds: J + K through the Gaunt-coupled channel engine
+# ------------------------------------------------------------------------------------------------
+FP64_TFLOPS_MEASURED = 35.5  # cuBLAS DGEMM 8192^3 on this pool's B200, profiles/r01_fp64_peak.json (MEASURED_PEAKS.json has no FP64 entry)
+
+
+def chan_orbitals(b, kind, rank):
+    """Synthetic occupied orbitals, each pure in m (what an SCF of an atom / linear molecule produces): smooth seeded
+    coefficients decaying with l and with the radial index.  Returns C (ndim x norb) in the operator's index space."""
+    from util import splitmix64
+    nrad, nang = b.nrad, b.nang
+    ndim = nang * nrad
+    occ_m = [0, 0, 0, 0, 0, 1, -1] if (kind == "diatomic" and int(np.max(np.abs(b.mval))) >= 1) else [0] * 5
+    cols = []
+    for q, m in enumerate(occ_m):
+        c = np.zeros((nang, nrad))
+        sel = np.where(b.mval == m)[0]
+        noise = splitmix64(len(sel) * nrad, seed=100 + q + 17 * rank).reshape(len(sel), nrad)
+        c[sel] = noise * np.exp(-0.35 * b.lval[sel])[:, None] * np.exp(-0.06 * np.arange(nrad))[None, :]
+        if kind == "diatomic" and m != 0:
+            c[sel, 0] = 0.0  # boundary function of the m != 0 shells (diatomic/basis.cpp:482-499)
+        cols.append(c.reshape(ndim))
+    return np.stack(cols, axis=1)
+
+
+def run_chan(args, w, rank, world, local_rank):
+    import torch
+    import helfem_b200 as hb
+    if not torch.cuda.is_available() or hb.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: helfem_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    kind = w["kind"]
+    t0 = time.perf_counter()
+    if kind == "atomic":
+        b = hb.AtomicBasis(w["Z"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"], lmax=w["lmax"], mmax=w["mmax"],
+                           device=local_rank)
+    else:
+        b = hb.DiatomicBasis(w["Z1"], w["Z2"], w["Rbond"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"],
+                             lmax=w["lmax"], mmax=w["mmax"], device=local_rank)
+    sharded = bool(args.shard) and world > 1
+    if sharded:
+        b.set_shard(rank, world)  # integral families r % world == rank; partial operators are all-reduced (NCCL)
+    b.compute_tei(True)
+    t_tei = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    n = b.chan_dim()  # uploads the integral tables
+    t_upload = time.perf_counter() - t0
+    C = torch.from_numpy(chan_orbitals(b, kind, 0 if sharded else rank)).cuda()
+    dP = (2.0 * C @ C.T).contiguous()  # symmetric, so row- and column-major coincide
+    dJ = torch.zeros_like(dP)
+    dK = torch.zeros_like(dP)
+    stream = torch.cuda.current_stream()
+    sh = stream.cuda_stream
+
+    def step(J=True, K=True):
+        if J:
+            b.coulomb_device(dP.data_ptr(), dJ.data_ptr(), n, sh)
+        if K:
+            b.exchange_device(dP.data_ptr(), dK.data_ptr(), n, sh)
+        if sharded:
+            if J:
+                dist.all_reduce(dJ)
+            if K:
+                dist.all_reduce(dK)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    t0 = time.perf_counter()
+    step()
+    torch.cuda.synchronize()
+    t_first = time.perf_counter() - t0  # includes the one-off output-list build for this sparsity pattern
+    for _ in range(max(args.warmup, 3) - 1):
+        step()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ms = timed(step, args.steps)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    units = 1 if sharded else world
+    value = units * args.steps / (ms * 1e-3)
+    ms_j = timed(lambda: step(K=False), args.steps) / args.steps
+    ms_k = timed(lambda: step(J=False), args.steps) / args.steps
+    b.set_profile(True)
+    step(J=False)
+    torch.cuda.synchronize()
+    items, x3_flops, stage = b.exchange_stats()
+    b.set_profile(False)
+    if args.kernels_only:
+        if rank == 0:
+            print(json.dumps({"kernels_only": True, "ms_per_step": ms / args.steps, "ms_coulomb": ms_j, "ms_exchange": ms_k,
+                              "stage_ms": stage, "items": items}), flush=True)
+        return
+
+    # ---- end to end: dense HOST matrices through the reference-facing calls (coulomb + exchange) ----
+    Ph = dP.cpu().numpy()
+    if kind == "diatomic":
+        idx = b.pure_indices()
+        Ph = np.asfortranarray(Ph[np.ix_(idx, idx)])
+    else:
+        Ph = np.asfortranarray(Ph)
+    ne2e = 1 if n > 8000 else 3
+    b.coulomb(Ph); b.exchange(Ph)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(ne2e):
+        Jh = b.coulomb(Ph)
+        Kh = b.exchange(Ph)
+    t_e2e = (time.perf_counter() - t0) / ne2e
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    nb = Ph.shape[0]
+    cpu = None
+    if world == 1 and nb <= 2500 and kind == "diatomic":
+        import oracle
+        oracle.lib().oracle_set_num_threads(host_threads())
+        dis = [[b.tei(ww, r, e) for r in range(b.nlm) for e in range(b.nel)] for ww in range(4)]
+        tei = [b.tei(4 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
+        ktei = [b.tei(8 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
+        o = oracle.DiatomicOracle(b.lval, b.mval, b.first, b.last, b.Lmap, b.Mmap, b.Rhalf, dis, tei, ktei, b.pure_indices())
+        t0 = time.perf_counter()
+        Jo, Ko = o.coulomb(Ph), o.exchange(Ph)
+        tc = time.perf_counter() - t0
+        cpu = {"value": 1.0 / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
+               "sample": "1 Fock build (coulomb + exchange) of the same workload",
+               "max_dJ": float(np.max(np.abs(Jh - Jo))), "max_dK": float(np.max(np.abs(Kh - Ko)))}
+    tf = x3_flops / (stage[3] * 1e-3) / 1e12 if stage[3] > 0 else None
+    roofline = {"kernel": "chan_x3_kernel", "bound": "tensor", "achieved": tf, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s",
+                "frac": (tf / FP64_TFLOPS_MEASURED) if tf else None, "traffic": ncu_traffic(args.workload, "chan_x3_kernel"),
+                "peak_source": "measured cuBLAS DGEMM FP64 (profiles/r01_fp64_peak.json); tcgen05 has no FP64 kind, DMMA.8x8x4 is the FP64 tensor path",
+                "algorithmic_flops_per_build": x3_flops, "ms_per_build": stage[3],
+                "exchange_stage_ms": dict(zip(["mask", "x1_left_angular", "x2_right_angular", "x3_radial_dmma", "x4_assemble"], stage)),
+                "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items}
+    line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "operators": "coulomb + exchange (HF)", "ndim": n, "nbf": nb,
+                       "nang": int(b.nang), "nrad": int(b.nrad),
+                       "l2": "dense P/J/K = %.0f MB per build%s" % (3 * n * n * 8 / 1e6, "" if 3 * n * n * 8 > 126e6 else " (fits L2: launch-bound regime)"),
+                       "partition": ("integral families sharded over ranks, NCCL all-reduce of J and K" if sharded
+                                     else "independent builds per rank, no data-path collective"),
+                       "setup_s": {"compute_tei_host": t_tei, "upload": t_upload, "first_build": t_first}},
+            "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": units / t_e2e, "unit": "builds/s", "h2d_bytes_per_step": 2 * nb * nb * 8, "d2h_bytes_per_step": 2 * nb * nb * 8,
+                    "api": "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis)"},
+            "gpu_launches": int(args.steps * (5 + 1 + 4 * (b.nlm if kind == "diatomic" else b.nL))), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -414,12 +598,21 @@ def main():
     ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
     ap.add_argument("--kernels-only", action="store_true", help="run only the timed device steps (ncu captures)")
     ap.add_argument("--split", action="store_true", help="with --kernels-only: also time the grid and the Coulomb kernels alone")
+    ap.add_argument("--shard", action="store_true", help="atomic/diatomic workloads, N>1: shard the integral families over the ranks "
+                    "and all-reduce J and K (strong scaling) instead of independent builds per rank")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     w = WORKLOADS[args.workload]
-    if args.impl == "reference":
+    if w.get("kind") in ("atomic", "diatomic"):
+        if args.impl == "reference":
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "CPU arm of the atomic/diatomic workloads is the oracle leg inside "
+                                  "the b200 line (cpu_baseline) at sizes the oracle finishes; default workload has the full arm"}))
+            return
+        run_chan(args, w, rank, world, local_rank)
+    elif args.impl == "reference":
         run_reference(args, w, rank)
     else:
         run_gpu(args, w, rank, world, local_rank)

@@ -4,7 +4,7 @@ import ctypes
 
 import numpy as np
 
-from . import lib, check_host, _p, _ip
+from . import lib, check, check_host, _p, _ip
 
 
 class AtomicBasis:
@@ -68,6 +68,34 @@ class AtomicBasis:
         k = np.zeros((npe * npe, npe * npe), order="F") if self.have_ktei else None
         check_host(lib().hfh_atomic_get_tei(self._h, int(L), int(iel), _p(a), _p(b), _p(t), _p(k) if k is not None else None))
         return a, b, t, k
+
+    def context(self):
+        """The hfb200_ctx of this basis (device tables are uploaded on first use)."""
+        ctx = ctypes.c_void_p()
+        check_host(lib().hfh_atomic_context(self._h, ctypes.byref(ctx)))
+        return ctx
+
+    def chan_dim(self):
+        n = ctypes.c_int()
+        check(lib().hfb200_chan_dim(self.context(), ctypes.byref(n)))
+        return n.value
+
+    def coulomb_device(self, dP, dJ, n, stream=0):
+        """Device-resident coulomb: dP, dJ = device pointers of dense (n x n) matrices, n = chan_dim()."""
+        check(lib().hfb200_chan_coulomb_device(self.context(), ctypes.c_void_p(dP), int(n), ctypes.c_void_p(dJ), int(n),
+                                                ctypes.c_void_p(stream)))
+
+    def exchange_device(self, dP, dK, n, stream=0):
+        check(lib().hfb200_chan_exchange_device(self.context(), ctypes.c_void_p(dP), int(n), ctypes.c_void_p(dK), int(n),
+                                                 ctypes.c_void_p(stream)))
+
+    def exchange_stats(self):
+        items, fl, ms = ctypes.c_longlong(), ctypes.c_double(), (ctypes.c_double * 5)()
+        check(lib().hfb200_chan_exchange_stats(self.context(), ctypes.byref(items), ctypes.byref(fl), ms))
+        return items.value, fl.value, list(ms)
+
+    def set_profile(self, on=True):
+        check(lib().hfb200_chan_set_profile(self.context(), int(bool(on))))
 
     def set_shard(self, rank, nranks):
         """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""

@@ -77,6 +77,8 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
     }
   // ket couplings (:845-864); the bra side (:932-952) uses the list of the transposed pair
   S.pair_coupl.assign((size_t)nang * nang, {});
+  angular::gaunt_coefficient(2 * lmax, 0, 2 * lmax, 0, 0, 0);  // size the shared Gaunt table before the parallel loop
+#pragma omp parallel for schedule(dynamic)
   for (int k = 0; k < nang; k++)
     for (int l = 0; l < nang; l++) {
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;

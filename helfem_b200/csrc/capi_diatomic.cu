@@ -112,14 +112,23 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   }
   // couplings (basis.cpp:1380-1403): coef[0] = cos^2-modified, coef[1] = plain Gaunt
   S.pair_coupl.assign((size_t)nang * nang, {});
+  {
+    int lmx = 0, mmx = 0;
+    for (int k = 0; k < nang; k++) { lmx = std::max(lmx, c->lval[k]); mmx = std::max(mmx, std::abs(c->mval[k])); }
+    gcoeff(2 * lmx + 4, 2 * mmx, 2 * lmx + 4, 2 * mmx, 0, 0);  // size the shared Gaunt table once, before the parallel loop
+  }
+  const std::map<std::pair<int, int>, int>& cfam = fam;
+  const std::map<std::pair<int, int>, int>& cchan = chan_tmp;
+#pragma omp parallel for schedule(dynamic)
   for (int k = 0; k < nang; k++)
     for (int l = 0; l < nang; l++) {
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;
       for (int L = std::max(std::abs(lk - ll) - 2, std::abs(M)); L <= lk + ll + 2; L++) {
-        if (fam[{L, std::abs(M)}] % c->shard_n != c->shard_rank) continue;  // family owned by another rank
+        const int r = cfam.find({L, std::abs(M)})->second;
+        if (r % c->shard_n != c->shard_rank) continue;  // family owned by another rank
         const double c0 = mod_coeff(lk, mk, L, M, ll, ml), c2 = gcoeff(lk, mk, L, M, ll, ml);
         if (c0 == 0.0 && c2 == 0.0) continue;
-        S.pair_coupl[(size_t)k * nang + l].push_back({chan_tmp[{fam[{L, std::abs(M)}], M}], {c0, c2}});
+        S.pair_coupl[(size_t)k * nang + l].push_back({cchan.find({r, M})->second, {c0, c2}});
       }
     }
   // stacked integrals: fac [[T00, -T02], [-T20, T22]],  s = fac [P0; -P2],  b = [Q0; -Q2]

@@ -121,6 +121,17 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
       return rc;
     fam_c0_host = fam_c0;
   }
+  {
+    std::vector<int> npe(nel), elem_of(2 * (size_t)nrad, -1);
+    for (int e = 0; e < nel; e++) {
+      npe[e] = last[e] - first[e] + 1;
+      for (int a = first[e]; a <= last[e]; a++) {
+        if (elem_of[2 * a] < 0) elem_of[2 * a] = e;
+        else if (elem_of[2 * a + 1] < 0) elem_of[2 * a + 1] = e;
+      }
+    }
+    if ((rc = up(this, &dFirstJ, first)) || (rc = up(this, &dNpeJ, npe)) || (rc = up(this, &dElemOfJ, elem_of))) return rc;
+  }
   have_k = false;
   if (with_exchange && S.ktei) return build_exchange(S);
   return 0;
@@ -354,23 +365,7 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
       }
     }
   HFB_CUDA_OK(cudaMemcpyAsync(dP.p, hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, st));
-  ChanParams q = prm;
-  q.nb = 1; q.P = dP.p; q.pc = dPc.p; q.traces = dTr.p; q.jc = dJc.p; q.J = dJ.p;
-  chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
-  HFB_CUDA_OK(cudaGetLastError());
-  int maxcol = 1;
-  for (int r = 0; r < prm.nr; r++) maxcol = std::max(maxcol, fam_c0_host[r + 1] - fam_c0_host[r]);
-  const int rts = (prm.MT + 3) / 4;
-  if (maxcol <= 8) {
-    chan_jmma_kernel<true, 1><<<dim3(nel * rts, 1, prm.nr), 256, 0, st>>>(q);
-  } else if (maxcol <= 16) {
-    chan_jmma_kernel<true, 2><<<dim3(nel * rts, 1, prm.nr), 256, 0, st>>>(q);
-  } else {
-    chan_jmma_kernel<false, 2><<<dim3(nel * rts, (maxcol + 127) / 128, prm.nr), 256, 0, st>>>(q);
-  }
-  HFB_CUDA_OK(cudaGetLastError());
-  chan_post_kernel<<<dim3(nel, npair, 1), 128, 0, st>>>(q);
-  HFB_CUDA_OK(cudaGetLastError());
+  if ((rc = coulomb_kernels(nang, st))) return rc;
   HFB_CUDA_OK(cudaMemcpyAsync(hOut.p, dJ.p, nband * sizeof(double), cudaMemcpyDeviceToHost, st));
   const int ntot = nang * nrad;
 #pragma omp parallel for schedule(static)
@@ -416,20 +411,83 @@ int launch_x3(const ChanXParams& q, int r, int nitems, size_t smem, cudaStream_t
 }
 }  // namespace
 
+// pre / DMMA / post kernels on the device bands dP -> dJ (buffers reserved by the caller)
+int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
+  (void)nang;
+  const int nel = prm.nel;
+  ChanParams q = prm;
+  q.nb = 1; q.P = dP.p; q.pc = dPc.p; q.traces = dTr.p; q.jc = dJc.p; q.J = dJ.p;
+  chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
+  HFB_CUDA_OK(cudaGetLastError());
+  int maxcol = 1;
+  for (int r = 0; r < prm.nr; r++) maxcol = std::max(maxcol, fam_c0_host[r + 1] - fam_c0_host[r]);
+  const int rts = (prm.MT + 3) / 4;
+  if (maxcol <= 8) {
+    chan_jmma_kernel<true, 1><<<dim3(nel * rts, 1, prm.nr), 256, 0, st>>>(q);
+  } else if (maxcol <= 16) {
+    chan_jmma_kernel<true, 2><<<dim3(nel * rts, 1, prm.nr), 256, 0, st>>>(q);
+  } else {
+    chan_jmma_kernel<false, 2><<<dim3(nel * rts, (maxcol + 127) / 128, prm.nr), 256, 0, st>>>(q);
+  }
+  HFB_CUDA_OK(cudaGetLastError());
+  chan_post_kernel<<<dim3(nel * npair, 1, 1), 128, 0, st>>>(q);
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st) {
+  const int nel = prm.nel, np2 = prm.np2, nang = (int)std::lround(std::sqrt((double)npair));
+  const size_t nband = (size_t)npair * nel * np2;
+  const int KP = 4 * prm.KS, MP = 8 * prm.MT;
+  int rc;
+  if ((rc = dP.reserve(nband)) || (rc = dJ.reserve(nband)) || (rc = dPc.reserve((size_t)nchan * nel * KP)) ||
+      (rc = dTr.reserve((size_t)nchan * nel * 2)) || (rc = dJc.reserve((size_t)nchan * nel * MP)))
+    return rc;
+  chan_band_pack_kernel<<<dim3(nel * npair), 128, 0, st>>>(prm, dFirstJ, dNpeJ, nang, nrad, dPm, ldp, dP.p);
+  HFB_CUDA_OK(cudaGetLastError());
+  if ((rc = coulomb_kernels(nang, st))) return rc;
+  const size_t work = (size_t)npair * nrad * nrad;
+  chan_band_unpack_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(prm, dFirstJ, dElemOfJ, nang, nrad, dJ.p, dJm, ldj);
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 // -K = exchange(P), dense host matrices.
 int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
   const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
   const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
   int rc;
-  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) ||
-      (rc = dW.reserve((size_t)nch_max * stack * nang2 * nrad2)))
-    return rc;
+  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot))) return rc;
   HFB_CUDA_OK(cudaMemcpy2DAsync(dPdense.p, ntot * sizeof(double), P, ldp * sizeof(double), ntot * sizeof(double), ntot,
                                 cudaMemcpyHostToDevice, st));
-  HFB_CUDA_OK(cudaMemsetAsync(dKdense.p, 0, (size_t)ntot * ntot * sizeof(double), st));
+  if ((rc = exchange_device(dPdense.p, ntot, dKdense.p, ntot, st))) return rc;
+  HFB_CUDA_OK(cudaMemcpy2DAsync(K, ldk * sizeof(double), dKdense.p, ntot * sizeof(double), ntot * sizeof(double), ntot,
+                                cudaMemcpyDeviceToHost, st));
+  HFB_CUDA_OK(cudaStreamSynchronize(st));
+  (void)nel; (void)np2; (void)st2; (void)nang2; (void)nrad2;
+  return 0;
+}
+
+int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ldkm, cudaStream_t st) {
+  if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
+  const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
+  int rc;
+  if ((rc = dW.reserve((size_t)nch_max * stack * nang2 * nrad2))) return rc;
+  HFB_CUDA_OK(cudaMemset2DAsync(dKm, (size_t)ldkm * sizeof(double), 0, (size_t)ntot * sizeof(double), ntot, st));
+  size_t ev_used = 0;
+  std::vector<std::pair<int, size_t>> ev_marks;  // (stage, index of the start event; the end event follows)
+  auto tick = [&](int stage, bool begin) {
+    if (!profile_stages) return;
+    if (ev_used == ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); ev_pool.push_back(e); }
+    if (begin) ev_marks.push_back({stage, ev_used});
+    cudaEventRecord(ev_pool[ev_used++], st);
+  };
   // block mask of P; the item lists are rebuilt only when the sparsity pattern changes
-  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPdense.p, ntot, nrad, nang, dNzP);
+  tick(0, true);
+  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP);
+  tick(0, false);
   HFB_CUDA_OK(cudaGetLastError());
   HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2, cudaMemcpyDeviceToHost, st));
   HFB_CUDA_OK(cudaStreamSynchronize(st));
@@ -445,8 +503,8 @@ int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cud
     }
     if ((rc = dKblocks.reserve((size_t)max_items * nel * nel * np2))) return rc;
     ChanXParams q = xprm;
-    q.P = dPdense.p; q.ldp = ntot; q.nzP = dNzP; q.W = dW.p; q.Wmask = dWmask; q.Rsub = dRsub.p; q.blocks = dKblocks.p;
-    q.K = dKdense.p; q.ldk = ntot;
+    q.P = dPm; q.ldp = ldpm; q.nzP = dNzP; q.W = dW.p; q.Wmask = dWmask; q.Rsub = dRsub.p; q.blocks = dKblocks.p;
+    q.K = dKm; q.ldk = ldkm;
     // x3 tile: NI items per CTA, as many as the shared-memory tile allows
     const int ntl = (prm.np + 7) / 8;
     const size_t ybytes = (size_t)8 * 8 * ntl * (8 * ntl + 1) * sizeof(double);
@@ -455,28 +513,56 @@ int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cud
     const size_t smem = std::max((size_t)NI * q.LDK * sizeof(double), ybytes);
     if (smem > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 256 * CHX_EPT - 1) / (256 * CHX_EPT));
+    last_items = 0;
+    last_x3_flops = 0.0;
     for (int r = 0; r < prm.nr; r++) {
       const int nrows = fam_row0[r + 1] - fam_row0[r], nitems = fam_item0[r + 1] - fam_item0[r];
       if (nrows == 0 || nitems == 0) continue;
+      last_items += nitems;
       const int c0 = fam_c0_host[r], nch = fam_c0_host[r + 1] - c0;
       const int2* items = dItems + fam_item0[r];
+      tick(1, true);
       HFB_CUDA_OK(cudaMemsetAsync(dWmask, 0, (size_t)nch * nang2, st));
       chan_x1_kernel<<<dim3(nrows, std::min(nang, 8)), 256, 0, st>>>(q, dRows + fam_row0[r], c0);
       HFB_CUDA_OK(cudaGetLastError());
+      tick(1, false);
+      tick(2, true);
       chan_x2_kernel<<<dim3(nitems, nchunk), 256, 0, st>>>(q, items, c0, nch, fam_fac[r]);
       HFB_CUDA_OK(cudaGetLastError());
+      tick(2, false);
+      tick(3, true);
       if (NI == 32) rc = launch_x3<32>(q, r, nitems, smem, st);
       else if (NI == 16) rc = launch_x3<16>(q, r, nitems, smem, st);
       else rc = launch_x3<8>(q, r, nitems, smem, st);
       if (rc) return rc;
+      tick(3, false);
+      tick(4, true);
       const size_t work = (size_t)nitems * nrad2;
       chan_x4_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(q, items, nitems);
       HFB_CUDA_OK(cudaGetLastError());
+      tick(4, false);
+    }
+    if (profile_stages) {
+      HFB_CUDA_OK(cudaStreamSynchronize(st));
+      for (float& v : stage_ms) v = 0.f;
+      for (const auto& mk : ev_marks) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev_pool[mk.second], ev_pool[mk.second + 1]);
+        stage_ms[mk.first] += ms;
+      }
     }
   }
-  HFB_CUDA_OK(cudaMemcpy2DAsync(K, ldk * sizeof(double), dKdense.p, ntot * sizeof(double), ntot * sizeof(double), ntot,
-                                cudaMemcpyDeviceToHost, st));
-  HFB_CUDA_OK(cudaStreamSynchronize(st));
+  // algorithmic flops of the radial contraction (x3) per output block and family: same-element products
+  // 2 np_e^4 and two (np x np x np) products per ordered pair of different elements, per stack combination
+  {
+    double per = 0.0;
+    for (int a = 0; a < nel; a++)
+      for (int b = 0; b < nel; b++) {
+        const double na = last[a] - first[a] + 1, nb = last[b] - first[b] + 1;
+        per += (a == b) ? 2.0 * na * na * na * na : 2.0 * na * na * nb + 2.0 * na * nb * nb;
+      }
+    last_x3_flops = per * st2 * (double)last_items;
+  }
   return 0;
 }
 
@@ -489,8 +575,42 @@ void ChanEngine::release() {
   items_cap = 0;
   if (hNzP) cudaFreeHost(hNzP);
   hNzP = nullptr;
+  for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+  ev_pool.clear();
   hIn.release();
   hOut.release();
 }
 
 }  // namespace hfb
+
+// ---- C ABI: device-resident operator calls of the atomic / diatomic contexts (include/helfem_b200.h) ----
+extern "C" {
+int hfb200_chan_dim(hfb200_ctx* c, int* ndim) {
+  if (!c || !c->chan || !ndim) { hfb::set_error("hfb200_chan_dim: no channel engine (call set_tei first)"); return HFB200_EINVAL; }
+  *ndim = (int)c->lval.size() * c->chan->nrad;
+  return HFB200_OK;
+}
+int hfb200_chan_coulomb_device(hfb200_ctx* c, const double* dP, int ldp, double* dJ, int ldj, void* stream) {
+  if (!c || !c->chan || !dP || !dJ) { hfb::set_error("hfb200_chan_coulomb_device: invalid argument"); return HFB200_EINVAL; }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  return c->chan->coulomb_device(dP, ldp, dJ, ldj, stream ? (cudaStream_t)stream : c->stream);
+}
+int hfb200_chan_exchange_device(hfb200_ctx* c, const double* dP, int ldp, double* dK, int ldk, void* stream) {
+  if (!c || !c->chan || !dP || !dK) { hfb::set_error("hfb200_chan_exchange_device: invalid argument"); return HFB200_EINVAL; }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  return c->chan->exchange_device(dP, ldp, dK, ldk, stream ? (cudaStream_t)stream : c->stream);
+}
+int hfb200_chan_exchange_stats(hfb200_ctx* c, long long* items, double* x3_flops, double* stage_ms) {
+  if (!c || !c->chan) { hfb::set_error("hfb200_chan_exchange_stats: invalid argument"); return HFB200_EINVAL; }
+  if (items) *items = c->chan->last_items;
+  if (x3_flops) *x3_flops = c->chan->last_x3_flops;
+  if (stage_ms)
+    for (int q = 0; q < 5; q++) stage_ms[q] = c->chan->stage_ms[q];
+  return HFB200_OK;
+}
+int hfb200_chan_set_profile(hfb200_ctx* c, int on) {
+  if (!c || !c->chan) { hfb::set_error("hfb200_chan_set_profile: invalid argument"); return HFB200_EINVAL; }
+  c->chan->profile_stages = on != 0;
+  return HFB200_OK;
+}
+}

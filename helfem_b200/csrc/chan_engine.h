@@ -61,6 +61,18 @@ struct ChanEngine {
   int build(const ChanSpec& spec, bool with_exchange);
   int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st);
   int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st);
+  // device-resident variants: dense (nang*nrad)^2 matrices already in HBM; every kernel of the operator, no PCIe
+  int coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st);
+  int exchange_device(const double* dPm, int ldp, double* dKm, int ldk, cudaStream_t st);
+  int coulomb_kernels(int nang, cudaStream_t st);
+  const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;
+  // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
+  long long last_items = 0;
+  double last_x3_flops = 0.0;
+  // optional per-stage device timing of exchange_device (x0 mask, x1, x2, x3, x4), summed over families
+  bool profile_stages = false;
+  float stage_ms[5] = {0, 0, 0, 0, 0};
+  std::vector<cudaEvent_t> ev_pool;
   void release();
 };
 

@@ -199,9 +199,9 @@ __global__ void __launch_bounds__(256) chan_jmma_kernel(ChanParams prm) {
     }
 }
 
-// grid (nel, npair, nb), 128 threads
+// grid (nel * npair, 1, nb), 128 threads
 static __global__ void __launch_bounds__(128) chan_post_kernel(ChanParams prm) {
-  const int el = blockIdx.x, pr = blockIdx.y, b = blockIdx.z;
+  const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, b = blockIdx.z;
   const int np = prm.np, np2 = prm.np2, MP = 8 * prm.MT;
   const int e0 = prm.post_ptr[pr], e1 = prm.post_ptr[pr + 1];
   double* out = prm.J + (((size_t)b * prm.npair + pr) * prm.nel + el) * np2;
@@ -216,6 +216,34 @@ static __global__ void __launch_bounds__(128) chan_post_kernel(ChanParams prm) {
       if (prm.stack == 2) v = fma(prm.post_coef[2 * e + 1], src[prm.ntri + m], v);
     }
     out[k] = v;
+  }
+}
+
+// Device-resident operator calls: gather the element-diagonal band of every angular pair out of a dense matrix,
+// grid (nel * npair), and the inverse (a radial index pair lies in at most two common elements), grid-stride.
+static __global__ void __launch_bounds__(128) chan_band_pack_kernel(ChanParams prm, const int* first, const int* npe, int nang, int nrad,
+                                                                    const double* D, int ld, double* band) {
+  const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, k = pr / nang, l = pr % nang;
+  const int f = first[el], n = npe[el], np = prm.np;
+  double* dst = band + ((size_t)pr * prm.nel + el) * prm.np2;
+  for (int q = threadIdx.x; q < prm.np2; q += blockDim.x) {
+    const int i = q % np, j = q / np;
+    dst[q] = (i < n && j < n) ? D[(size_t)(k * nrad + f + i) + (size_t)(l * nrad + f + j) * ld] : 0.0;
+  }
+}
+static __global__ void chan_band_unpack_kernel(ChanParams prm, const int* first, const int* elem_of, int nang, int nrad,
+                                               const double* band, double* D, int ld) {
+  const size_t per = (size_t)nrad * nrad, total = per * prm.npair;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int pr = (int)(idx / per), a = (int)(idx % nrad), b = (int)((idx / nrad) % nrad);
+    double s = 0.0;
+    for (int x = 0; x < 2; x++) {
+      const int e = elem_of[2 * a + x];
+      if (e < 0) continue;
+      if (e == elem_of[2 * b] || e == elem_of[2 * b + 1])
+        s += band[((size_t)pr * prm.nel + e) * prm.np2 + (a - first[e]) + (b - first[e]) * prm.np];
+    }
+    D[(size_t)((pr / nang) * nrad + a) + (size_t)((pr % nang) * nrad + b) * ld] = s;
   }
 }
 

@@ -1,5 +1,7 @@
 #include "angular.h"
+#include <atomic>
 #include <cmath>
+#include <mutex>
 #include "fem.h"
 
 namespace hfb {
@@ -63,10 +65,42 @@ void gauss_legendre(int n, Vec& x, Vec& w) {
   }
 }
 
-static double sph_signed(int l, int m, double x) {
-  if (m >= 0) return sph_plm(l, m, x);
-  return ((-m) % 2 ? -1.0 : 1.0) * sph_plm(l, -m, x);
+// Gauss-Legendre rule + normalised associated Legendre functions on its nodes, shared by every Gaunt evaluation:
+// one rule that is exact for all products up to 3 lmax replaces a rule (and a Newton solve) per coefficient.
+namespace {
+struct GauntTable {
+  int lmax = -1, mmax = -1, n = 0;
+  Vec w;                    // 2 pi w_i
+  std::vector<double> S;    // [m][l][i], m >= 0, zero for l < m
+  const double* row(int l, int mabs) const { return S.data() + ((size_t)mabs * (lmax + 1) + l) * n; }
+};
+std::atomic<const GauntTable*> g_table{nullptr};
+std::mutex g_table_mutex;
+
+const GauntTable* gaunt_table(int lneed, int mneed) {
+  const GauntTable* t = g_table.load(std::memory_order_acquire);
+  if (t && t->lmax >= lneed && t->mmax >= mneed) return t;
+  std::lock_guard<std::mutex> lock(g_table_mutex);
+  t = g_table.load(std::memory_order_acquire);
+  if (t && t->lmax >= lneed && t->mmax >= mneed) return t;
+  GauntTable* nt = new GauntTable();
+  nt->lmax = std::max(lneed, t ? t->lmax : 8);
+  nt->mmax = std::min(nt->lmax, std::max(mneed, t ? t->mmax : 4));
+  nt->n = (3 * nt->lmax) / 2 + 2;
+  Vec x;
+  gauss_legendre(nt->n, x, nt->w);
+  for (double& v : nt->w) v *= 2.0 * M_PI;
+  nt->S.assign((size_t)(nt->mmax + 1) * (nt->lmax + 1) * nt->n, 0.0);
+  std::vector<double> tmp(nt->lmax + 1);
+  for (int m = 0; m <= nt->mmax; m++)
+    for (int i = 0; i < nt->n; i++) {
+      sph_plm_array(nt->lmax, m, x[i], tmp.data());
+      for (int l = m; l <= nt->lmax; l++) nt->S[((size_t)m * (nt->lmax + 1) + l) * nt->n + i] = tmp[l - m];
+    }
+  g_table.store(nt, std::memory_order_release);  // the superseded table stays alive for concurrent readers
+  return nt;
 }
+}  // namespace
 
 double gaunt_coefficient(int L, int M, int l, int m, int lp, int mp) {
   if (M != m + mp) return 0.0;
@@ -74,12 +108,17 @@ double gaunt_coefficient(int L, int M, int l, int m, int lp, int mp) {
   if (std::abs(M) > L || std::abs(m) > l || std::abs(mp) > lp) return 0.0;
   if ((L + l + lp) % 2) return 0.0;  // parity: (L l lp; 0 0 0) vanishes
   // The theta integrand is a polynomial of degree L+l+lp in x (total power of sin is even).
-  const int n = (L + l + lp) / 2 + 1;
-  Vec x, w;
-  gauss_legendre(n, x, w);
+  const int aM = std::abs(M), am = std::abs(m), amp = std::abs(mp);
+  const GauntTable* t = gaunt_table(std::max(L, std::max(l, lp)), std::max(aM, std::max(am, amp)));
+  const double *s1 = t->row(L, aM), *s2 = t->row(l, am), *s3 = t->row(lp, amp);
   long double s = 0.0L;
-  for (int i = 0; i < n; i++) s += (long double)w[i] * sph_signed(L, M, x[i]) * sph_signed(l, m, x[i]) * sph_signed(lp, mp, x[i]);
-  return (double)(2.0L * M_PIl * s);
+  for (int i = 0; i < t->n; i++) s += (long double)(t->w[i] * s1[i]) * (long double)(s2[i] * s3[i]);
+  // S_{l,-m} = (-1)^m S_{l,m}
+  int sign = 0;
+  if (M < 0) sign += aM;
+  if (m < 0) sign += am;
+  if (mp < 0) sign += amp;
+  return (sign % 2) ? (double)(-s) : (double)s;
 }
 
 double modified_gaunt_coefficient(int lj, int mj, int L, int M, int li, int mi) {

@@ -178,6 +178,16 @@ int hfh_sadatom_get_tei(void* h, int L, int iel, double* disL, double* dism1L, d
   }
   HFH_CATCH
 }
+int hfh_atomic_context(void* h, hfb200_ctx** ctx) {
+  HFH_TRY
+  *ctx = ((atomic::TwoDBasis*)h)->context();
+  HFH_CATCH
+}
+int hfh_diatomic_context(void* h, hfb200_ctx** ctx) {
+  HFH_TRY
+  *ctx = ((diatomic::TwoDBasis*)h)->context();
+  HFH_CATCH
+}
 int hfh_sadatom_context(void* h, hfb200_ctx** ctx) {
   HFH_TRY
   *ctx = ((sadatom::TwoDBasis*)h)->context();

@@ -147,6 +147,19 @@ int hfb200_diatomic_set_tei(hfb200_ctx* ctx, int nlm, const int* Lmap, const int
 int hfb200_diatomic_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
 int hfb200_diatomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* K, int ldk);
 
+/* Device-resident variants of the atomic / diatomic operators: dP, dJ, dK are DEVICE pointers to dense
+ * column-major matrices of dimension hfb200_chan_dim() = nang*nrad (atomic: the operator basis itself,
+ * atomic/TwoDBasis.cpp:290-300; diatomic: the "dummy" basis of expand_boundaries, diatomic/basis.cpp:1755-1773),
+ * `stream` a cudaStream_t (NULL: the context's stream).  Same kernels as the host-matrix calls above without the
+ * PCIe legs; the work is enqueued on `stream` (exchange synchronises it once to read back the block mask of P).
+ * hfb200_chan_exchange_stats: output blocks (summed over integral families) and algorithmic flops of the
+ * radial contraction of the last exchange call; stage_ms is filled when hfb200_chan_set_profile(ctx, 1) is on. */
+int hfb200_chan_dim(hfb200_ctx* ctx, int* ndim);
+int hfb200_chan_coulomb_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dJ, int ldj, void* stream);
+int hfb200_chan_exchange_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dK, int ldk, void* stream);
+int hfb200_chan_exchange_stats(hfb200_ctx* ctx, long long* items, double* x3_flops, double* stage_ms /* [5] or NULL */);
+int hfb200_chan_set_profile(hfb200_ctx* ctx, int on); /* per-stage CUDA-event timing of exchange (mask, x1..x4) */
+
 /* ------------------------------------------------------------------------------------------
  * DFTGrid::eval_Fxc of the `atomic` and `diatomic` programs (angular x radial product grid).
  *   atomic::dftgrid::DFTGrid::eval_Fxc     atomic/dftgrid.cpp:810 (restricted), :872 (unrestricted)
