@@ -469,8 +469,12 @@ def run_chan(args, w, rank, world, local_rank):
     dP = (2.0 * C @ C.T).contiguous()  # symmetric, so row- and column-major coincide
     dJ = torch.zeros_like(dP)
     dK = torch.zeros_like(dP)
+    torch.cuda.synchronize()
+    # a real (non-default) stream: the C ABI reads a NULL stream as "the context's own stream"
+    torch.cuda.set_stream(torch.cuda.Stream())
     stream = torch.cuda.current_stream()
     sh = stream.cuda_stream
+    assert sh != 0
 
     def step(J=True, K=True):
         if J:

@@ -66,6 +66,7 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   ChanSpec S;
   S.nel = c->nel; S.nang = nang; S.stack = 1; S.nr = nL;
   S.first = c->first; S.last = c->last;
+  S.ang_group = c->mval;
   S.fac.resize(nL);
   for (int L = 0; L < nL; L++) S.fac[L] = 4.0 * M_PI / (2 * L + 1);
   // channels (L, M), sorted by L (atomic/TwoDBasis.cpp:836-842)

@@ -87,6 +87,7 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   ChanSpec S;
   S.nel = nel; S.nang = nang; S.stack = 2; S.nr = nlm;
   S.first = c->first; S.last = c->last;
+  S.ang_group = c->mval;
   S.fac.resize(nlm);
   for (int r = 0; r < nlm; r++) {
     // LMfac = 4 pi Rh^5 (-1)^M (L-|M|)!/(L+|M|)!   (basis.cpp:1421)
@@ -152,19 +153,11 @@ static int diatomic_apply(hfb200_ctx* c, bool exchange, const double* P, int ldp
   const int npure = (int)idx.size(), nd = (int)c->lval.size() * c->nrad;
   if (ldp < npure || ldf < npure) { set_error("Matrix does not have expected size!"); return HFB200_EINVAL; }
   HFB_CUDA_OK(cudaSetDevice(c->device));
-  // expand_boundaries (basis.cpp:1755-1773)
-  std::vector<double> Pd((size_t)nd * nd, 0.0), Fd((size_t)nd * nd);
-#pragma omp parallel for schedule(static)
-  for (int j = 0; j < npure; j++)
-    for (int i = 0; i < npure; i++) Pd[(size_t)idx[i] + (size_t)idx[j] * nd] = P[(size_t)i + (size_t)j * ldp];
-  const int rc = exchange ? c->chan->exchange_dense(Pd.data(), nd, Fd.data(), nd, c->stream)
-                          : c->chan->coulomb_dense(Pd.data(), nd, Fd.data(), nd, c->stream);
-  if (rc) return rc;
-  // remove_boundaries (basis.cpp:1735-1753)
-#pragma omp parallel for schedule(static)
-  for (int j = 0; j < npure; j++)
-    for (int i = 0; i < npure; i++) F[(size_t)i + (size_t)j * ldf] = Fd[(size_t)idx[i] + (size_t)idx[j] * nd];
-  return HFB200_OK;
+  // expand_boundaries / remove_boundaries (basis.cpp:1735-1773) are folded into the engine's pack / unpack passes
+  std::vector<int> map(nd, -1);
+  for (int i = 0; i < npure; i++) map[idx[i]] = i;
+  return exchange ? c->chan->exchange_dense(P, ldp, F, ldf, c->stream, map.data(), npure)
+                  : c->chan->coulomb_dense(P, ldp, F, ldf, c->stream, map.data(), npure);
 }
 
 int hfb200_diatomic_coulomb(hfb200_ctx* c, const double* P, int ldp, double* J, int ldj) {

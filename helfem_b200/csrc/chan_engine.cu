@@ -251,6 +251,30 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
           if (xrowptr[(size_t)c * nang + j + 1] > xrowptr[(size_t)c * nang + j]) rows.push_back(make_int2(c, j));
       fam_row0[r + 1] = (int)rows.size();
     }
+    // x1 tiles: rows of a channel grouped by angular group (same m => same coupling partners), CHX_T rows each
+    ang_group = S.ang_group.size() == (size_t)nang ? S.ang_group : std::vector<int>(nang, 0);
+    std::vector<int> tiles1;
+    fam_t1.assign(nr + 1, 0);
+    for (int r = 0; r < nr; r++) {
+      for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++) {
+        std::vector<int> js;
+        for (int j = 0; j < nang; j++)
+          if (xrowptr[(size_t)c * nang + j + 1] > xrowptr[(size_t)c * nang + j]) js.push_back(j);
+        std::stable_sort(js.begin(), js.end(), [&](int a, int b) { return ang_group[a] < ang_group[b]; });
+        for (size_t q = 0; q < js.size();) {
+          size_t e = q;
+          while (e < js.size() && e - q < (size_t)CHX_T && ang_group[js[e]] == ang_group[js[q]]) e++;
+          tiles1.push_back(c);
+          tiles1.push_back((int)(e - q));
+          for (int t = 0; t < CHX_T; t++) tiles1.push_back(q + t < e ? js[q + t] : js[q]);
+          q = e;
+        }
+      }
+      fam_t1[r + 1] = (int)(tiles1.size() / (2 + CHX_T));
+    }
+    const int* dt1 = nullptr;
+    if ((rc = up(this, &dt1, tiles1))) return rc;
+    dTiles1 = const_cast<int*>(dt1);
     const int2* drows = nullptr;
     if ((rc = up(this, &xprm.rowptr, xrowptr)) || (rc = up(this, &xprm.row_i, xrow_i)) || (rc = up(this, &xprm.row_coef, coef)) ||
         (rc = up(this, &drows, rows)))
@@ -262,29 +286,52 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang));
     owned.push_back(p);
     dNzP = p;
-    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nch_max * nang * nang));
-    owned.push_back(p);
-    dWmask = p;
     if (hNzP) cudaFreeHost(hNzP);
     HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang));
   }
+  if ((rc = up(this, &dFamFac, fam_fac))) return rc;
+  // x3 tile: NI output blocks per CTA, as many as the shared-memory tile allows
+  x3_ni = 32;
+  while (x3_ni > 8 && (size_t)x3_ni * xprm.LDK * sizeof(double) > 200 * 1024) x3_ni >>= 1;
   mask_cached.clear();
   have_k = true;
   return 0;
 }
 
-// Output blocks of every family for one sparsity pattern of P: (j,k) is an item of family r when some channel
-// c of r has rows (c,j), (c,k) and a non-zero block P[i,l] with i in row (c,j), l in row (c,k).
+namespace {
+template <class T>
+int up_list(ChanEngine::DevList& L, const std::vector<T>& v) {
+  const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+  if (bytes > L.cap) {
+    if (L.p) cudaFree(L.p);
+    L.p = nullptr;
+    L.cap = 0;
+    HFB_CUDA_OK(cudaMalloc(&L.p, bytes));
+    L.cap = bytes;
+  }
+  if (!v.empty()) HFB_CUDA_OK(cudaMemcpy(L.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+}  // namespace
+
+// Everything that depends on the sparsity pattern of P (one block mask), built once per pattern:
+//  * L(c,j) = { l : some partner i of the coupling row (c,j) has P[i,l] != 0 } -> compact layout of W
+//  * items of family r: (j,k) such that some channel c of r has rows (c,j), (c,k) and L(c,j) meets row (c,k)
+//  * x2 tiles, x3 groups, the CSR of distinct output blocks for x4
+//  * batches of consecutive families whose W and R workspaces fit the budget
 int ChanEngine::build_items(const unsigned char* nz) {
-  const int nang = xprm.nang, nr = prm.nr, nw = (nang + 63) / 64;
+  const int nang = xprm.nang, nr = prm.nr, nw = (nang + 63) / 64, st = prm.stack, nel = prm.nel, np2 = prm.np2;
+  const size_t nrad2 = (size_t)nrad * nrad;
   std::vector<uint64_t> nzrow((size_t)nang * nw, 0);  // nzrow[i] = { l : P[i,l] != 0 }
   for (int i = 0; i < nang; i++)
     for (int l = 0; l < nang; l++)
       if (nz[(size_t)i * nang + l]) nzrow[(size_t)i * nw + (l >> 6)] |= (uint64_t)1 << (l & 63);
+  std::vector<unsigned long long> wbits((size_t)nchan * nang * nw, 0);
+  std::vector<int> wcount((size_t)nchan * nang, 0);
   std::vector<std::vector<int2>> fam_items(nr);
 #pragma omp parallel
   {
-    std::vector<uint64_t> lset((size_t)nang * nw), rowset((size_t)nang * nw);
+    std::vector<uint64_t> rowset((size_t)nang * nw);
     std::vector<unsigned char> hit((size_t)nang * nang);
     std::vector<int> js;
 #pragma omp for schedule(dynamic)
@@ -297,52 +344,117 @@ int ChanEngine::build_items(const unsigned char* nz) {
           const int e0 = xrowptr[(size_t)c * nang + j], e1 = xrowptr[(size_t)c * nang + j + 1];
           if (e0 == e1) continue;
           js.push_back(j);
-          uint64_t* ls = &lset[(size_t)j * nw];
+          unsigned long long* ls = &wbits[((size_t)c * nang + j) * nw];
           uint64_t* rs = &rowset[(size_t)j * nw];
-          for (int w = 0; w < nw; w++) { ls[w] = 0; rs[w] = 0; }
+          for (int w = 0; w < nw; w++) rs[w] = 0;
           for (int e = e0; e < e1; e++) {
             const int i = xrow_i[e];
             rs[i >> 6] |= (uint64_t)1 << (i & 63);
             for (int w = 0; w < nw; w++) ls[w] |= nzrow[(size_t)i * nw + w];
           }
+          int n = 0;
+          for (int w = 0; w < nw; w++) n += __builtin_popcountll(ls[w]);
+          wcount[(size_t)c * nang + j] = n;
         }
-        for (int j : js)
+        for (int j : js) {
+          const unsigned long long* ls = &wbits[((size_t)c * nang + j) * nw];
           for (int k : js) {
             if (hit[(size_t)j * nang + k]) continue;
             uint64_t any = 0;
-            for (int w = 0; w < nw; w++) any |= lset[(size_t)j * nw + w] & rowset[(size_t)k * nw + w];
+            for (int w = 0; w < nw; w++) any |= ls[w] & rowset[(size_t)k * nw + w];
             if (any) hit[(size_t)j * nang + k] = 1;
           }
+        }
       }
-      for (int j = 0; j < nang; j++)
+      for (int j = 0; j < nang; j++) {
+        const size_t b0 = fam_items[r].size();
         for (int k = 0; k < nang; k++)
           if (hit[(size_t)j * nang + k]) fam_items[r].push_back(make_int2(j, k));
+        // within one j: order by angular group so that the x2 tiles (consecutive items) share their partners
+        std::stable_sort(fam_items[r].begin() + b0, fam_items[r].end(),
+                         [&](const int2& a, const int2& b) { return ang_group[a.y] < ang_group[b.y]; });
+      }
     }
   }
-  fam_item0.assign(nr + 1, 0);
-  max_items = 0;
+  // global lists + batches
+  const long long wcap = (long long)((16ull << 30) / ((size_t)st * nrad2 * sizeof(double)));
+  const long long icap = (long long)((12ull << 30) / ((size_t)st * st * nel * nel * np2 * sizeof(double)));
+  std::vector<int2> items, tiles2, groups;
+  std::vector<int> item_fam, out_ptr, out_item;
+  std::vector<long long> wbase((size_t)nchan * nang, -1);
+  batches.clear();
+  max_wblocks = 0;
+  max_batch_items = 0;
+  XBatch cur{fam_t1[0], fam_t1[0], 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  auto close_batch = [&]() {
+    cur.item1 = (int)items.size();
+    cur.t2_1 = (int)tiles2.size();
+    cur.g1 = (int)groups.size();
+    // distinct output blocks of the batch, items of one block in family order
+    std::vector<int> idx(cur.item1 - cur.item0);
+    for (size_t q = 0; q < idx.size(); q++) idx[q] = cur.item0 + (int)q;
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) {
+      return (long long)items[a].x * nang + items[a].y < (long long)items[b].x * nang + items[b].y;
+    });
+    cur.out0 = (int)out_ptr.size();
+    cur.nout = 0;
+    for (size_t q = 0; q < idx.size(); q++) {
+      if (q == 0 || items[idx[q]].x != items[idx[q - 1]].x || items[idx[q]].y != items[idx[q - 1]].y) {
+        out_ptr.push_back((int)out_item.size());
+        cur.nout++;
+      }
+      out_item.push_back(idx[q]);
+    }
+    out_ptr.push_back((int)out_item.size());
+    if (cur.item1 > cur.item0 || cur.wblocks > 0) batches.push_back(cur);
+    max_wblocks = std::max(max_wblocks, cur.wblocks);
+    max_batch_items = std::max(max_batch_items, cur.item1 - cur.item0);
+  };
   for (int r = 0; r < nr; r++) {
-    fam_item0[r + 1] = fam_item0[r] + (int)fam_items[r].size();
-    max_items = std::max(max_items, (int)fam_items[r].size());
+    long long wr = 0;
+    for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
+      for (int j = 0; j < nang; j++) wr += wcount[(size_t)c * nang + j];
+    const long long ir = (long long)fam_items[r].size();
+    const bool nonempty = cur.wblocks > 0 || (int)items.size() > cur.item0;
+    if (nonempty && (cur.wblocks + wr > wcap || (long long)items.size() - cur.item0 + ir > icap)) {
+      cur.t1_1 = fam_t1[r];
+      close_batch();
+      cur = XBatch{fam_t1[r], fam_t1[r], (int)tiles2.size(), 0, (int)groups.size(), 0, (int)items.size(), 0, 0, 0, 0};
+    }
+    for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
+      for (int j = 0; j < nang; j++)
+        if (wcount[(size_t)c * nang + j]) {
+          wbase[(size_t)c * nang + j] = cur.wblocks;
+          cur.wblocks += wcount[(size_t)c * nang + j];
+        }
+    const std::vector<int2>& it = fam_items[r];
+    const int g0 = (int)items.size();
+    for (size_t q = 0; q < it.size();) {  // x2 tiles: <= CHX_T consecutive items with one j and one angular group of k
+      size_t e = q;
+      while (e < it.size() && e - q < (size_t)CHX_T && it[e].x == it[q].x && ang_group[it[e].y] == ang_group[it[q].y]) e++;
+      tiles2.push_back(make_int2(g0 + (int)q, (int)(e - q)));
+      q = e;
+    }
+    for (size_t q = 0; q < it.size(); q += x3_ni) groups.push_back(make_int2(g0 + (int)q, (int)std::min<size_t>(x3_ni, it.size() - q)));
+    items.insert(items.end(), it.begin(), it.end());
+    item_fam.insert(item_fam.end(), it.size(), r);
+    cur.t1_1 = fam_t1[r + 1];
   }
-  std::vector<int2> all;
-  all.reserve(fam_item0[nr]);
-  for (int r = 0; r < nr; r++) all.insert(all.end(), fam_items[r].begin(), fam_items[r].end());
-  if (all.size() > items_cap) {
-    if (dItems) cudaFree(dItems);
-    dItems = nullptr;
-    items_cap = 0;
-    HFB_CUDA_OK(cudaMalloc(&dItems, std::max<size_t>(all.size(), 1) * sizeof(int2)));
-    items_cap = std::max<size_t>(all.size(), 1);
-  }
-  if (!all.empty()) HFB_CUDA_OK(cudaMemcpy(dItems, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
+  cur.t1_1 = fam_t1[nr];
+  close_batch();
+  total_items = (long long)items.size();
+  int rc;
+  if ((rc = up_list(dItems, items)) || (rc = up_list(dItemFam, item_fam)) || (rc = up_list(dTiles2, tiles2)) ||
+      (rc = up_list(dGroups, groups)) || (rc = up_list(dWbase, wbase)) || (rc = up_list(dWbits, wbits)) ||
+      (rc = up_list(dOutPtr, out_ptr)) || (rc = up_list(dOutItem, out_item)))
+    return rc;
   return 0;
 }
 
 // J = coulomb(P) with dense host matrices ((nang*nrad)^2, column-major, block (iang,jang) at rows
 // iang*nrad, cols jang*nrad: atomic/TwoDBasis.cpp:290-300).  Only the element-diagonal radial blocks of
 // each angular pair enter or leave the operator, so that is all that crosses PCIe.
-int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st) {
+int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map, int nout) {
   const int nel = prm.nel, np = prm.np, np2 = prm.np2, nang = (int)std::lround(std::sqrt((double)npair));
   const size_t nband = (size_t)npair * nel * np2;
   const int KP = 4 * prm.KS, MP = 8 * prm.MT;
@@ -360,14 +472,24 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
         const int f = first[e], npe = last[e] - f + 1;
         double* blk = dst + (size_t)e * np2;
         if (npe < np) memset(blk, 0, sizeof(double) * np2);
-        for (int j = 0; j < npe; j++)
-          memcpy(blk + (size_t)j * np, P + (size_t)(k * nrad + f) + (size_t)(l * nrad + f + j) * ldp, sizeof(double) * npe);
+        if (!map) {
+          for (int j = 0; j < npe; j++)
+            memcpy(blk + (size_t)j * np, P + (size_t)(k * nrad + f) + (size_t)(l * nrad + f + j) * ldp, sizeof(double) * npe);
+        } else {
+          for (int j = 0; j < npe; j++) {
+            const int pc = map[l * nrad + f + j];
+            for (int i = 0; i < npe; i++) {
+              const int pr = map[k * nrad + f + i];
+              blk[(size_t)j * np + i] = (pr < 0 || pc < 0) ? 0.0 : P[(size_t)pr + (size_t)pc * ldp];
+            }
+          }
+        }
       }
     }
   HFB_CUDA_OK(cudaMemcpyAsync(dP.p, hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, st));
   if ((rc = coulomb_kernels(nang, st))) return rc;
   HFB_CUDA_OK(cudaMemcpyAsync(hOut.p, dJ.p, nband * sizeof(double), cudaMemcpyDeviceToHost, st));
-  const int ntot = nang * nrad;
+  const int ntot = map ? nout : nang * nrad;
 #pragma omp parallel for schedule(static)
   for (int c = 0; c < ntot; c++) memset(J + (size_t)c * ldj, 0, sizeof(double) * ntot);
   HFB_CUDA_OK(cudaStreamSynchronize(st));
@@ -377,9 +499,20 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
       const double* src = hOut.p + ((size_t)(i * nang + j) * nel) * np2;
       for (int e = 0; e < nel; e++) {
         const int f = first[e], npe = last[e] - f + 1;
-        for (int b = 0; b < npe; b++)
-          for (int a = 0; a < npe; a++)
-            J[(size_t)(i * nrad + f + a) + (size_t)(j * nrad + f + b) * ldj] += src[(size_t)e * np2 + a + (size_t)b * np];
+        if (!map) {
+          for (int b = 0; b < npe; b++)
+            for (int a = 0; a < npe; a++)
+              J[(size_t)(i * nrad + f + a) + (size_t)(j * nrad + f + b) * ldj] += src[(size_t)e * np2 + a + (size_t)b * np];
+        } else {
+          for (int b = 0; b < npe; b++) {
+            const int pc = map[j * nrad + f + b];
+            if (pc < 0) continue;
+            for (int a = 0; a < npe; a++) {
+              const int pr = map[i * nrad + f + a];
+              if (pr >= 0) J[(size_t)pr + (size_t)pc * ldj] += src[(size_t)e * np2 + a + (size_t)b * np];
+            }
+          }
+        }
       }
     }
   return 0;
@@ -387,8 +520,8 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
 
 namespace {
 template <int NI>
-int launch_x3(const ChanXParams& q, int r, int nitems, size_t smem, cudaStream_t st) {
-  const dim3 grid((nitems + NI - 1) / NI, q.nel * q.nel);
+int launch_x3(const ChanXParams& q, const int2* groups, int ngroups, size_t smem, cudaStream_t st) {
+  const dim3 grid(ngroups, q.nel * q.nel);
   const int ntl = (q.np + 7) / 8;
 #define HFB_X3(NTL)                                                                                                   \
   {                                                                                                                   \
@@ -397,7 +530,7 @@ int launch_x3(const ChanXParams& q, int r, int nitems, size_t smem, cudaStream_t
       HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
       attr_set = true;                                                                                                \
     }                                                                                                                 \
-    chan_x3_kernel<NI, NTL><<<grid, 256, smem, st>>>(q, r, nitems);                                                   \
+    chan_x3_kernel<NI, NTL><<<grid, 256, smem, st>>>(q, groups);                                                      \
   }
   switch (ntl) {
     case 1: HFB_X3(1) break;
@@ -452,20 +585,61 @@ int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj,
   return 0;
 }
 
-// -K = exchange(P), dense host matrices.
-int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st) {
+// -K = exchange(P), dense host matrices.  map (optional): operator index -> row/column of the caller's matrices, -1 for
+// rows that are identically zero (the diatomic boundary functions); the caller's matrices are nout x nout.
+// The matrix is staged through one pinned buffer in column chunks so that packing, H2D, D2H and unpacking overlap.
+int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map, int nout) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
-  const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
+  const int nang = xprm.nang, ntot = nang * nrad;
+  (void)nout;
   int rc;
-  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot))) return rc;
-  HFB_CUDA_OK(cudaMemcpy2DAsync(dPdense.p, ntot * sizeof(double), P, ldp * sizeof(double), ntot * sizeof(double), ntot,
+  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) || (rc = hX.reserve((size_t)ntot * ntot)))
+    return rc;
+  const int nchunk = ntot >= 4096 ? 16 : 1;
+  std::vector<cudaEvent_t> ev(nchunk);
+  for (auto& e : ev) HFB_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (int ch = 0; ch < nchunk; ch++) {
+    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
+#pragma omp parallel for schedule(static)
+    for (int c = c0; c < c1; c++) {
+      double* dst = hX.p + (size_t)c * ntot;
+      if (!map) {
+        memcpy(dst, P + (size_t)c * ldp, sizeof(double) * ntot);
+      } else {
+        const int pc = map[c];
+        if (pc < 0) { memset(dst, 0, sizeof(double) * ntot); continue; }
+        const double* src = P + (size_t)pc * ldp;
+        for (int r = 0; r < ntot; r++) dst[r] = map[r] < 0 ? 0.0 : src[map[r]];
+      }
+    }
+    HFB_CUDA_OK(cudaMemcpyAsync(dPdense.p + (size_t)c0 * ntot, hX.p + (size_t)c0 * ntot, (size_t)(c1 - c0) * ntot * sizeof(double),
                                 cudaMemcpyHostToDevice, st));
+  }
   if ((rc = exchange_device(dPdense.p, ntot, dKdense.p, ntot, st))) return rc;
-  HFB_CUDA_OK(cudaMemcpy2DAsync(K, ldk * sizeof(double), dKdense.p, ntot * sizeof(double), ntot * sizeof(double), ntot,
+  for (int ch = 0; ch < nchunk; ch++) {
+    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
+    HFB_CUDA_OK(cudaMemcpyAsync(hX.p + (size_t)c0 * ntot, dKdense.p + (size_t)c0 * ntot, (size_t)(c1 - c0) * ntot * sizeof(double),
                                 cudaMemcpyDeviceToHost, st));
-  HFB_CUDA_OK(cudaStreamSynchronize(st));
-  (void)nel; (void)np2; (void)st2; (void)nang2; (void)nrad2;
+    HFB_CUDA_OK(cudaEventRecord(ev[ch], st));
+  }
+  for (int ch = 0; ch < nchunk; ch++) {
+    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
+    HFB_CUDA_OK(cudaEventSynchronize(ev[ch]));
+#pragma omp parallel for schedule(static)
+    for (int c = c0; c < c1; c++) {
+      const double* src = hX.p + (size_t)c * ntot;
+      if (!map) {
+        memcpy(K + (size_t)c * ldk, src, sizeof(double) * ntot);
+      } else {
+        const int pc = map[c];
+        if (pc < 0) continue;
+        double* dst = K + (size_t)pc * ldk;
+        for (int r = 0; r < ntot; r++)
+          if (map[r] >= 0) dst[map[r]] = src[r];
+      }
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
   return 0;
 }
 
@@ -474,7 +648,6 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
   const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
   const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
   int rc;
-  if ((rc = dW.reserve((size_t)nch_max * stack * nang2 * nrad2))) return rc;
   HFB_CUDA_OK(cudaMemset2DAsync(dKm, (size_t)ldkm * sizeof(double), 0, (size_t)ntot * sizeof(double), ntot, st));
   size_t ev_used = 0;
   std::vector<std::pair<int, size_t>> ev_marks;  // (stage, index of the start event; the end event follows)
@@ -484,7 +657,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     if (begin) ev_marks.push_back({stage, ev_used});
     cudaEventRecord(ev_pool[ev_used++], st);
   };
-  // block mask of P; the item lists are rebuilt only when the sparsity pattern changes
+  // block mask of P; the per-pattern lists are rebuilt only when the sparsity pattern changes
   tick(0, true);
   chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP);
   tick(0, false);
@@ -495,50 +668,58 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     if ((rc = build_items(hNzP))) return rc;
     mask_cached.assign(hNzP, hNzP + nang2);
   }
-  if (max_items > 0) {
-    const size_t need_r = (size_t)max_items * st2 * nel * nel * np2;
+  last_items = total_items;
+  if (total_items > 0) {
+    const size_t need_r = (size_t)max_batch_items * st2 * nel * nel * np2;
     if (need_r > dRsub.cap) {
       if ((rc = dRsub.reserve(need_r))) return rc;
       HFB_CUDA_OK(cudaMemsetAsync(dRsub.p, 0, need_r * sizeof(double), st));  // padding positions stay zero for good
     }
-    if ((rc = dKblocks.reserve((size_t)max_items * nel * nel * np2))) return rc;
+    if ((rc = dKblocks.reserve((size_t)max_batch_items * nel * nel * np2)) ||
+        (rc = dW.reserve((size_t)std::max<long long>(max_wblocks, 1) * stack * nrad2)))
+      return rc;
     ChanXParams q = xprm;
-    q.P = dPm; q.ldp = ldpm; q.nzP = dNzP; q.W = dW.p; q.Wmask = dWmask; q.Rsub = dRsub.p; q.blocks = dKblocks.p;
-    q.K = dKm; q.ldk = ldkm;
-    // x3 tile: NI items per CTA, as many as the shared-memory tile allows
-    const int ntl = (prm.np + 7) / 8;
+    q.P = dPm; q.ldp = ldpm; q.nzP = dNzP; q.W = dW.p; q.Rsub = dRsub.p; q.blocks = dKblocks.p; q.K = dKm; q.ldk = ldkm;
+    q.fam_c0 = prm.fam_c0; q.fam_fac = dFamFac; q.items = (const int2*)dItems.p; q.item_fam = (const int*)dItemFam.p;
+    q.wbase = (const long long*)dWbase.p; q.wbits = (const unsigned long long*)dWbits.p; q.nw = (nang + 63) / 64;
+    const int ntl = (prm.np + 7) / 8, NI = x3_ni;
     const size_t ybytes = (size_t)8 * 8 * ntl * (8 * ntl + 1) * sizeof(double);
-    int NI = 32;
-    while (NI > 8 && (size_t)NI * q.LDK * sizeof(double) > 200 * 1024) NI >>= 1;
-    const size_t smem = std::max((size_t)NI * q.LDK * sizeof(double), ybytes);
-    if (smem > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
-    const int nchunk = (int)((nrad2 + 256 * CHX_EPT - 1) / (256 * CHX_EPT));
-    last_items = 0;
-    last_x3_flops = 0.0;
-    for (int r = 0; r < prm.nr; r++) {
-      const int nrows = fam_row0[r + 1] - fam_row0[r], nitems = fam_item0[r + 1] - fam_item0[r];
-      if (nrows == 0 || nitems == 0) continue;
-      last_items += nitems;
-      const int c0 = fam_c0_host[r], nch = fam_c0_host[r + 1] - c0;
-      const int2* items = dItems + fam_item0[r];
-      tick(1, true);
-      HFB_CUDA_OK(cudaMemsetAsync(dWmask, 0, (size_t)nch * nang2, st));
-      chan_x1_kernel<<<dim3(nrows, std::min(nang, 8)), 256, 0, st>>>(q, dRows + fam_row0[r], c0);
-      HFB_CUDA_OK(cudaGetLastError());
-      tick(1, false);
+    const size_t smem3 = std::max((size_t)NI * q.LDK * sizeof(double), ybytes);
+    if (smem3 > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
+    const int nchunk = (int)((nrad2 + 255) / 256);
+    const size_t smem1 = (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_T * sizeof(long long) +
+                         (size_t)(2 * nang + CHX_UMAX) * sizeof(int) + (size_t)nang;
+    const size_t smem2 = (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_UMAX * sizeof(size_t) + (size_t)2 * nch_max * nang * sizeof(int);
+    if (smem1 > 48 * 1024 || smem2 > 48 * 1024) {
+      if (smem1 > 227 * 1024 || smem2 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
+      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    }
+    for (const XBatch& B : batches) {
+      q.item0 = B.item0;
+      const int nt1 = B.t1_1 - B.t1_0, nt2 = B.t2_1 - B.t2_0, ng = B.g1 - B.g0;
+      if (nt1 > 0 && B.wblocks > 0) {
+        tick(1, true);
+        chan_x1_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
+        HFB_CUDA_OK(cudaGetLastError());
+        tick(1, false);
+      }
+      if (nt2 == 0) continue;
       tick(2, true);
-      chan_x2_kernel<<<dim3(nitems, nchunk), 256, 0, st>>>(q, items, c0, nch, fam_fac[r]);
+      const int ny2 = std::max(1, std::min(nchunk, 2368 / std::max(nt2, 1)));
+      chan_x2_kernel<<<dim3(nt2, ny2), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
       HFB_CUDA_OK(cudaGetLastError());
       tick(2, false);
       tick(3, true);
-      if (NI == 32) rc = launch_x3<32>(q, r, nitems, smem, st);
-      else if (NI == 16) rc = launch_x3<16>(q, r, nitems, smem, st);
-      else rc = launch_x3<8>(q, r, nitems, smem, st);
+      if (NI == 32) rc = launch_x3<32>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
+      else if (NI == 16) rc = launch_x3<16>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
+      else rc = launch_x3<8>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
       if (rc) return rc;
       tick(3, false);
       tick(4, true);
-      const size_t work = (size_t)nitems * nrad2;
-      chan_x4_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(q, items, nitems);
+      const size_t work = (size_t)B.nout * nrad2;
+      chan_x4_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(q, (const int*)dOutPtr.p + B.out0,
+                                                                                              (const int*)dOutItem.p, B.nout);
       HFB_CUDA_OK(cudaGetLastError());
       tick(4, false);
     }
@@ -570,15 +751,18 @@ void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
   for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRsub}) b->release();
-  if (dItems) cudaFree(dItems);
-  dItems = nullptr;
-  items_cap = 0;
+  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroups, &dWbase, &dWbits, &dOutPtr, &dOutItem}) {
+    if (L->p) cudaFree(L->p);
+    L->p = nullptr;
+    L->cap = 0;
+  }
   if (hNzP) cudaFreeHost(hNzP);
   hNzP = nullptr;
   for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
   ev_pool.clear();
   hIn.release();
   hOut.release();
+  hX.release();
 }
 
 }  // namespace hfb

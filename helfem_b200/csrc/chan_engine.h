@@ -22,6 +22,8 @@ struct ChanSpec {
   std::vector<double> fac;                 // [nr]  4 pi/(2L+1)  resp.  LMfac
   std::vector<int> chan_r;                 // [nchan] family of each channel, sorted by family
   std::vector<std::vector<ChanCoupling>> pair_coupl;  // [nang*nang], index k*nang + l
+  std::vector<int> ang_group;              // [nang] optional: angular functions with equal value (m) share their coupling
+                                           // partners; only used to tile the exchange contractions efficiently
   // in-element integrals of family r, element e, block (hout, hin) of the stacked matrix:
   // returns the (np_e^2 x np_e^2) column-major block and its sign, nullptr if the block is absent
   std::function<const double*(int r, int e, int hout, int hin, double* sign)> tei;
@@ -47,20 +49,29 @@ struct ChanEngine {
   std::vector<int> xrowptr, xrow_i;                 // host copy of the coupling rows (item lists are derived from them)
   std::vector<int> fam_row0;                        // [nr+1] range of each family in dRows
   int2* dRows = nullptr;                            // (channel, j) of every non-empty coupling row, grouped by family
-  // per sparsity pattern of P: the output blocks ("items") of every family
+  // per sparsity pattern of P (build_items): output blocks of every family, compact W layout, tiles, batches
   std::vector<unsigned char> mask_cached;
-  std::vector<int> fam_item0;                       // [nr+1]
-  int2* dItems = nullptr;
-  size_t items_cap = 0;
-  int max_items = 0;
-  unsigned char *dNzP = nullptr, *dWmask = nullptr, *hNzP = nullptr;
+  struct XBatch { int t1_0, t1_1, t2_0, t2_1, g0, g1, item0, item1, out0, nout; long long wblocks; };
+  std::vector<XBatch> batches;
+  long long total_items = 0, max_wblocks = 0;
+  int max_batch_items = 0;
+  struct DevList { void* p = nullptr; size_t cap = 0; };
+  DevList dItems, dItemFam, dTiles2, dGroups, dWbase, dWbits, dOutPtr, dOutItem;
+  const double* dFamFac = nullptr;
+  std::vector<int> fam_t1;                          // [nr+1] x1 tiles of each family in dTiles1 ([c, nj, j x CHX_T] each)
+  int* dTiles1 = nullptr;
+  std::vector<int> ang_group;                       // [nang]
+  unsigned char *dNzP = nullptr, *hNzP = nullptr;
   DevBuf dPdense, dKdense, dKblocks, dW, dRsub;
 
   int build_items(const unsigned char* nz);
   int build_exchange(const ChanSpec& spec);
   int build(const ChanSpec& spec, bool with_exchange);
-  int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st);
-  int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st);
+  // dense HOST matrices; map (optional, length nang*nrad): operator index -> row/column of the caller's nout x nout
+  // matrices, -1 = identically zero row (diatomic boundary functions, diatomic/basis.cpp:1735-1773)
+  int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map = nullptr, int nout = 0);
+  int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map = nullptr, int nout = 0);
+  PinBuf hX;
   // device-resident variants: dense (nang*nrad)^2 matrices already in HBM; every kernel of the operator, no PCIe
   int coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st);
   int exchange_device(const double* dPm, int ldp, double* dKm, int ldk, cudaStream_t st);

@@ -12,7 +12,8 @@
 // The reference's quadruple angular loop costs O(#(j,k) #(i,l) #L) block AXPYs.  The coupling
 // coefficient of a channel c = (L,M) FACTORISES, c_c(j,i) c_c(k,l), and the radial operator of a
 // family commutes with the angular contraction, so the operator is evaluated family by family as
-//   x1  W^a_c[j,l]  = sum_i c^a_c(j,i) P[i,l]                        (left angular contraction, sparse rows)
+//   x1  W^a_c[j,l]  = sum_i c^a_c(j,i) P[i,l]                        (left angular contraction, sparse rows; tiled:
+//                     rows that share their partners stream every P block once)
 //   x2  R^{ab}[j,k] = fac_r (+-) sum_{c in r} sum_l c^b_c(k,l) W^a_c[j,l]   (right angular contraction), written
 //                     per element pair as zero-padded (np x np) sub-blocks
 //   x3  Ksub(ie,je) = sum_ab T^{ab}_r(ie,je)[Rsub^{ab}(ie,je)]       FP64 tensor pipe (DMMA.8x8x4):
@@ -21,8 +22,10 @@
 //         ie != je:  iint . Rsub . jint^T  as two chained (np x np) DMMA products per item
 //   x4  K[j,k] -= the (at most four) sub-blocks that overlap each radial index pair   (fixed order)
 // Zero blocks of P are skipped like the reference does (Frobenius norm < 10 eps, atomic/TwoDBasis.cpp:1036):
-// x1 consults a block mask, x2 the mask of W blocks x1 produced, and the list of output blocks
-// ("items") of every family is derived from the mask on the host once per sparsity pattern.
+// the block mask of P fixes, once per sparsity pattern and on the host, the set L(c,j) of W blocks every coupling
+// row produces (W is stored compactly, one block per member), the output blocks ("items") of every family, and a
+// partition of the families into BATCHES whose W / R workspaces fit a fixed budget.  One launch of each stage
+// covers a whole batch of families, so that the grid fills the 148 SMs even when a single family is small.
 #pragma once
 #include <cuda_runtime.h>
 #include "sadatom_grid_mma.cuh"  // dmma()
@@ -46,10 +49,19 @@ struct ChanXParams {
   const double* P;        // dense, ld = ldp
   int ldp;
   const unsigned char* nzP;  // [nang*nang] block (i,l) at i*nang + l
-  double* W;              // [nch_max][stack][nang*nang][nrad*nrad]
-  unsigned char* Wmask;   // [nch_max][nang*nang]
-  double* Rsub;           // [items][stack*stack][nel*nel][np2]
-  double* blocks;         // [items][nel*nel][np2]
+  // family tables and the per-sparsity-pattern lists (all families; a launch covers a BATCH of families)
+  const int* fam_c0;      // [nr+1] channel range of a family
+  const double* fam_fac;  // [nr]
+  const int2* items;      // [nitems] output blocks (j,k), grouped by family
+  const int* item_fam;    // [nitems]
+  // compact storage of W: row (c,j) holds one block per l of its set L(c,j) = { l : some i of the row has P[i,l] != 0 }
+  const long long* wbase; // [nchan*nang] first block of the row inside the batch's W buffer
+  const unsigned long long* wbits;  // [nchan*nang][nw] bitset of L(c,j)
+  int nw;
+  double* W;              // [blocks of the batch][stack][nrad*nrad]
+  int item0;              // first item of the batch (Rsub / blocks are indexed relative to it)
+  double* Rsub;           // [items of the batch][stack*stack][nel*nel][np2]
+  double* blocks;         // [items of the batch][nel*nel][np2]
   double* K;              // dense, ld = ldk
   int ldk;
 };
@@ -74,104 +86,240 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
   }
 }
 
-// x1.  grid (rows of the family, l chunks), 256 threads.  rows: (channel, j) with a non-empty coupling row.
-static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, const int2* rows, int c0) {
-  const int c = rows[blockIdx.x].x, j = rows[blockIdx.x].y, cl = c - c0;
-  const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack;
-  const int e0 = prm.rowptr[c * nang + j], e1 = prm.rowptr[c * nang + j + 1];
-  const size_t nang2 = (size_t)nang * nang;
-  for (int l = blockIdx.y; l < nang; l += gridDim.y) {
-    bool any = false;
-    for (int e = e0; e < e1; e++) any = any || prm.nzP[prm.row_i[e] * nang + l];
-    if (!any) continue;  // block-uniform
-    double* W0 = prm.W + (((size_t)cl * st) * nang2 + (size_t)j * nang + l) * nrad2;
-    double* W1 = W0 + nang2 * nrad2;
-    for (int k = threadIdx.x; k < nrad2; k += blockDim.x) {
-      const int A = k % nrad, B = k / nrad;
-      const double* src = prm.P + A + (size_t)(l * nrad + B) * prm.ldp;
-      double w0 = 0.0, w1 = 0.0;
-      for (int e = e0; e < e1; e++) {
-        const int i = prm.row_i[e];
-        if (!prm.nzP[i * nang + l]) continue;
-        const double p = src[(size_t)i * nrad];
-        w0 = fma(prm.row_coef[2 * e], p, w0);
-        w1 = fma(prm.row_coef[2 * e + 1], p, w1);
-      }
-      W0[k] = w0;
-      if (st == 2) W1[k] = w1;
+// Tiling of the two angular contractions: a CTA owns up to CHX_T rows that share their coupled partners (same m),
+// builds the UNION of the partners in shared memory (flags -> ballot scan -> slots) with a dense (slot x row)
+// coefficient table, and streams every input block ONCE for all its rows instead of once per row.
+constexpr int CHX_T = 8;      // rows (x1: j, x2: k) per tile
+constexpr int CHX_UMAX = 64;  // union slots per pass
+
+// slots for the flagged entries of dom[0..n): -1 = absent, 0 = present on entry; slot number on exit.  Warp 0 only.
+__device__ __forceinline__ int chx_scan_slots(int* dom, int* ulist, int n, int lane) {
+  int base = 0;
+  for (int q0 = 0; q0 < n; q0 += 32) {
+    const int q = q0 + lane;
+    const bool f = q < n && dom[q] == 0;
+    const unsigned m = __ballot_sync(0xffffffffu, f);
+    if (f) {
+      const int sl = base + __popc(m & ((1u << lane) - 1u));
+      dom[q] = sl;
+      ulist[sl] = q;
     }
-    if (threadIdx.x == 0) prm.Wmask[(size_t)cl * nang2 + (size_t)j * nang + l] = 1;
+    base += __popc(m);
   }
+  return base;
 }
 
-// x2.  grid (items of the family, element chunks of 256*EPT), 256 threads.
-constexpr int CHX_EPT = 8;
-static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, const int2* items, int c0, int nch, double fac) {
-  const int j = items[blockIdx.x].x, k = items[blockIdx.x].y;
+// Block of W for (row, l), or -1 when l is not in the row's set.
+__device__ __forceinline__ long long chx_wblock(const ChanXParams& prm, int row, int l) {
+  const unsigned long long* bits = prm.wbits + (size_t)row * prm.nw;
+  const int w = l >> 6;
+  const unsigned long long m = bits[w];
+  if (!((m >> (l & 63)) & 1ull)) return -1;
+  long long idx = prm.wbase[row] + __popcll(m & ((1ull << (l & 63)) - 1ull));
+  for (int q = 0; q < w; q++) idx += __popcll(bits[q]);
+  return idx;
+}
+
+// x1.  grid (tiles of the batch, l chunks), 256 threads.  tiles: [c, nj, j_0 .. j_{T-1}] per tile.
+// dynamic smem: coef[UMAX][T][2] doubles | wblk[T] long long | ulist[nang] | dom[nang] | act[UMAX] ints | done[nang] bytes
+static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, const int* tiles) {
+  extern __shared__ double sm[];
+  __shared__ int s_cnt;
+  const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack;
+  double* coef = sm;
+  long long* wblk = reinterpret_cast<long long*>(coef + CHX_UMAX * CHX_T * 2);
+  int* ulist = reinterpret_cast<int*>(wblk + CHX_T);
+  int* dom = ulist + nang;
+  int* act = dom + nang;
+  unsigned char* done = reinterpret_cast<unsigned char*>(act + CHX_UMAX);
+  const int* T = tiles + (size_t)blockIdx.x * (2 + CHX_T);
+  const int c = T[0], nj = T[1];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int q = tid; q < nang; q += 256) { dom[q] = -1; done[q] = 0; }
+  __syncthreads();
+  for (int jj = 0; jj < nj; jj++) {
+    const int row = c * nang + T[2 + jj];
+    for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) dom[prm.row_i[e]] = 0;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int n = chx_scan_slots(dom, ulist, nang, lane);
+    if (lane == 0) s_cnt = n;
+  }
+  __syncthreads();
+  const int cnt = s_cnt;
+  for (int ubase = 0; ubase < cnt; ubase += CHX_UMAX) {
+    const int nu = min(CHX_UMAX, cnt - ubase);
+    for (int q = tid; q < nu * CHX_T * 2; q += 256) coef[q] = 0.0;
+    __syncthreads();
+    for (int jj = 0; jj < nj; jj++) {
+      const int row = c * nang + T[2 + jj];
+      for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
+        const int sl = dom[prm.row_i[e]] - ubase;
+        if (sl >= 0 && sl < nu) {
+          coef[(sl * CHX_T + jj) * 2] = prm.row_coef[2 * e];
+          coef[(sl * CHX_T + jj) * 2 + 1] = prm.row_coef[2 * e + 1];
+        }
+      }
+    }
+    for (int l = blockIdx.y; l < nang; l += gridDim.y) {
+      __syncthreads();  // coef complete / previous l done with act and wblk
+      int mine = 0;
+      if (tid < nu) {
+        mine = prm.nzP[(size_t)ulist[ubase + tid] * nang + l];
+        act[tid] = mine;
+      }
+      if (tid < CHX_T) wblk[tid] = tid < nj ? chx_wblock(prm, c * nang + T[2 + tid], l) : -1;
+      if (!__syncthreads_or(mine)) continue;  // block-uniform
+      const bool prev = done[l] != 0;  // an earlier pass already wrote the blocks of this l
+      for (int k = tid; k < nrad2; k += 256) {
+        const int A = k % nrad, B = k / nrad;
+        const double* src = prm.P + A + (size_t)(l * nrad + B) * prm.ldp;
+        double acc[CHX_T][2];
+#pragma unroll
+        for (int jj = 0; jj < CHX_T; jj++) { acc[jj][0] = 0.0; acc[jj][1] = 0.0; }
+        for (int u = 0; u < nu; u++) {
+          if (!act[u]) continue;
+          const double p = src[(size_t)ulist[ubase + u] * nrad];
+          const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);
+#pragma unroll
+          for (int jj = 0; jj < CHX_T; jj++) {
+            const double2 cc = cf[jj];
+            acc[jj][0] = fma(cc.x, p, acc[jj][0]);
+            acc[jj][1] = fma(cc.y, p, acc[jj][1]);
+          }
+        }
+#pragma unroll
+        for (int jj = 0; jj < CHX_T; jj++) {
+          const long long wb = wblk[jj];
+          if (wb < 0) continue;  // l is not in the set of this row (its partners' blocks are all zero): nothing stored
+          double* W0 = prm.W + (size_t)wb * st * nrad2 + k;
+          if (prev) { acc[jj][0] += W0[0]; if (st == 2) acc[jj][1] += W0[nrad2]; }
+          W0[0] = acc[jj][0];
+          if (st == 2) W0[nrad2] = acc[jj][1];
+        }
+      }
+      if (tid == 0) done[l] = 1;
+    }
+    __syncthreads();
+  }
+  // blocks of the rows' sets that no pass reached cannot exist: l in L(c,j) means an active partner in some pass
+}
+
+// x2.  grid (tiles of the batch, element chunks), 256 threads.  A tile = <= CHX_T consecutive items (j, k_0..) of one family, one j.
+// dynamic smem: coef[UMAX][T][2] doubles | woff[UMAX] (size_t) | ulist[D] | dom[D] ints, D = nch_max*nang
+static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
+  extern __shared__ double sm[];
+  __shared__ int s_cnt;
   const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack, st2 = st * st;
-  const size_t nang2 = (size_t)nang * nang;
-  const int base = blockIdx.y * (256 * CHX_EPT) + threadIdx.x;
-  double acc[CHX_EPT][4];
+  double* coef = sm;
+  size_t* woff = reinterpret_cast<size_t*>(coef + CHX_UMAX * CHX_T * 2);
+  int* ulist = reinterpret_cast<int*>(woff + CHX_UMAX);
+  int* dom = ulist + nch_max * nang;
+  const int it0 = tiles[blockIdx.x].x, nk = tiles[blockIdx.x].y;
+  const int j = prm.items[it0].x, r = prm.item_fam[it0];
+  const int c0 = prm.fam_c0[r], nch = prm.fam_c0[r + 1] - c0, D = nch * nang;
+  const double fac = prm.fam_fac[r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int q = tid; q < D; q += 256) dom[q] = -1;
+  __syncthreads();
+  for (int kk = 0; kk < nk; kk++) {
+    const int k = prm.items[it0 + kk].y;
+    for (int cl = 0; cl < nch; cl++) {
+      const int row = (c0 + cl) * nang + k, jrow = (c0 + cl) * nang + j;
+      const unsigned long long* bits = prm.wbits + (size_t)jrow * prm.nw;
+      for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
+        const int l = prm.row_i[e];
+        if ((bits[l >> 6] >> (l & 63)) & 1ull) dom[cl * nang + l] = 0;
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int n = chx_scan_slots(dom, ulist, D, lane);
+    if (lane == 0) s_cnt = n;
+  }
+  __syncthreads();
+  const int cnt = s_cnt;
+  const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2;
+  const size_t istride = (size_t)st2 * nel2 * np2;
+  for (int ubase = 0; ubase < max(cnt, 1); ubase += CHX_UMAX) {  // cnt == 0: one pass that writes zeros
+    const int nu = max(0, min(CHX_UMAX, cnt - ubase));
+    __syncthreads();
+    for (int q = tid; q < nu * CHX_T * 2; q += 256) coef[q] = 0.0;
+    if (tid < nu) {
+      const int q = ulist[ubase + tid], cl = q / nang, l = q - cl * nang;
+      woff[tid] = (size_t)chx_wblock(prm, (c0 + cl) * nang + j, l) * st * nrad2;
+    }
+    __syncthreads();
+    for (int kk = 0; kk < nk; kk++) {
+      const int k = prm.items[it0 + kk].y;
+      for (int cl = 0; cl < nch; cl++) {
+        const int row = (c0 + cl) * nang + k;
+        for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
+          const int d = dom[cl * nang + prm.row_i[e]];
+          const int sl = d - ubase;
+          if (d >= 0 && sl >= 0 && sl < nu) {
+            coef[(sl * CHX_T + kk) * 2] = prm.row_coef[2 * e];
+            coef[(sl * CHX_T + kk) * 2 + 1] = prm.row_coef[2 * e + 1];
+          }
+        }
+      }
+    }
+    __syncthreads();
+    for (int el = blockIdx.y * 256 + tid; el < nrad2; el += gridDim.y * 256) {
+      double acc[CHX_T][4];
 #pragma unroll
-  for (int q = 0; q < CHX_EPT; q++) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = 0.0; }
-  for (int cl = 0; cl < nch; cl++) {
-    const int c = c0 + cl;
-    const int e0 = prm.rowptr[c * nang + k], e1 = prm.rowptr[c * nang + k + 1];
-    if (prm.rowptr[c * nang + j] == prm.rowptr[c * nang + j + 1]) continue;  // j has no row in this channel: no W
-    for (int e = e0; e < e1; e++) {
-      const int l = prm.row_i[e];
-      if (!prm.Wmask[(size_t)cl * nang2 + (size_t)j * nang + l]) continue;
-      const double cb0 = prm.row_coef[2 * e], cb1 = prm.row_coef[2 * e + 1];
-      const double* W0 = prm.W + (((size_t)cl * st) * nang2 + (size_t)j * nang + l) * nrad2;
-      const double* W1 = W0 + nang2 * nrad2;
+      for (int kk = 0; kk < CHX_T; kk++) { acc[kk][0] = acc[kk][1] = acc[kk][2] = acc[kk][3] = 0.0; }
+      for (int u = 0; u < nu; u++) {
+        const double* Wp = prm.W + woff[u] + el;
+        const double w0 = Wp[0];
+        const double w1 = st == 2 ? Wp[nrad2] : 0.0;
+        const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);
 #pragma unroll
-      for (int q = 0; q < CHX_EPT; q++) {
-        const int el = base + 256 * q;
-        if (el < nrad2) {
-          const double w0 = W0[el];
-          acc[q][0] = fma(cb0, w0, acc[q][0]);
-          if (st == 2) {
-            const double w1 = W1[el];
-            acc[q][1] = fma(cb1, w0, acc[q][1]);  // (a,b) = (0,1)
-            acc[q][2] = fma(cb0, w1, acc[q][2]);  // (1,0)
-            acc[q][3] = fma(cb1, w1, acc[q][3]);  // (1,1)
+        for (int kk = 0; kk < CHX_T; kk++) {
+          const double2 cc = cf[kk];
+          acc[kk][0] = fma(cc.x, w0, acc[kk][0]);  // (a,b) = (0,0)
+          acc[kk][1] = fma(cc.y, w0, acc[kk][1]);  // (0,1)
+          acc[kk][2] = fma(cc.x, w1, acc[kk][2]);  // (1,0)
+          acc[kk][3] = fma(cc.y, w1, acc[kk][3]);  // (1,1)
+        }
+      }
+      // scatter into the element-pair sub-blocks (a radial function belongs to one or two elements)
+      const int A = el % nrad, B = el / nrad;
+      for (int x = 0; x < 2; x++) {
+        const int ie = prm.elem_of[2 * A + x];
+        if (ie < 0) continue;
+        for (int y = 0; y < 2; y++) {
+          const int je = prm.elem_of[2 * B + y];
+          if (je < 0) continue;
+          const size_t off = (size_t)(ie * nel + je) * np2 + (A - prm.first[ie]) + (B - prm.first[je]) * np;
+#pragma unroll
+          for (int kk = 0; kk < CHX_T; kk++) {
+            if (kk >= nk) break;
+            double* out = prm.Rsub + (size_t)(it0 - prm.item0 + kk) * istride + off;
+            for (int ab = 0; ab < st2; ab++) {
+              const int a = ab / st, b = ab % st;
+              const double v = (a != b ? -fac : fac) * acc[kk][st == 2 ? ab : 0];
+              if (ubase == 0) out[(size_t)ab * nel2 * np2] = v;
+              else out[(size_t)ab * nel2 * np2] += v;
+            }
           }
         }
       }
     }
   }
-  // scatter into the element-pair sub-blocks (a radial function belongs to one or two elements)
-  const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2;
-  double* out = prm.Rsub + (size_t)blockIdx.x * st2 * nel2 * np2;
-#pragma unroll
-  for (int q = 0; q < CHX_EPT; q++) {
-    const int el = base + 256 * q;
-    if (el >= nrad2) continue;
-    const int A = el % nrad, B = el / nrad;
-    for (int x = 0; x < 2; x++) {
-      const int ie = prm.elem_of[2 * A + x];
-      if (ie < 0) continue;
-      for (int y = 0; y < 2; y++) {
-        const int je = prm.elem_of[2 * B + y];
-        if (je < 0) continue;
-        const size_t off = (size_t)(ie * nel + je) * np2 + (A - prm.first[ie]) + (B - prm.first[je]) * np;
-        for (int ab = 0; ab < st2; ab++) {
-          const int a = ab / st, b = ab % st;
-          out[(size_t)ab * nel2 * np2 + off] = (a != b ? -fac : fac) * acc[q][st == 2 ? ab : 0];
-        }
-      }
-    }
-  }
 }
 
-// x3.  grid (item groups of NI, nel*nel), 256 threads; dynamic smem NI*LDK doubles.
-// NTL = 8-row tiles of an (np x np) block (np <= 8 NTL).
+// x3.  grid (item groups of the batch, nel*nel), 256 threads; dynamic smem NI*LDK doubles.  groups: (first item, count <= NI)
+// of ONE family.  NTL = 8-row tiles of an (np x np) block (np <= 8 NTL).
 template <int NI, int NTL>
-__global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, int r, int nitems) {
+__global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, const int2* groups) {
   extern __shared__ double sm[];
   const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2, st = prm.stack, st2 = st * st;
   const int ie = blockIdx.y / nel, je = blockIdx.y % nel;
-  const int n0 = blockIdx.x * NI, nn = min(NI, nitems - n0);
+  const int r = prm.item_fam[groups[blockIdx.x].x];
+  const int n0 = groups[blockIdx.x].x - prm.item0, nn = groups[blockIdx.x].y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
   const size_t istride = (size_t)st2 * nel2 * np2;  // Rsub stride between items
   const double* Rbase = prm.Rsub + (size_t)n0 * istride + (size_t)(ie * nel + je) * np2;
@@ -298,14 +446,16 @@ __global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, int r, in
   }
 }
 
-// x4.  K[j,k] -= overlapping sub-blocks, fixed order.  grid-stride over items x nrad^2.
-static __global__ void chan_x4_kernel(ChanXParams prm, const int2* items, int nitems) {
+// x4.  K[j,k] -= sum over the batch's items with that (j,k) (several families) of the (at most four) sub-blocks that
+// overlap each radial index pair; fixed order.  out_ptr/out_item: CSR over the distinct output blocks of the batch.
+static __global__ void chan_x4_kernel(ChanXParams prm, const int* out_ptr, const int* out_item, int nout) {
   const int np = prm.np, np2 = prm.np2, nel = prm.nel, nel2 = nel * nel, nrad = prm.nrad;
-  const size_t per = (size_t)nrad * nrad, total = per * nitems;
+  const size_t per = (size_t)nrad * nrad, total = per * nout;
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int o = (int)(idx / per);
     const int a = (int)(idx % nrad), b = (int)((idx / nrad) % nrad);
-    const int2 jk = items[o];
+    const int q0 = out_ptr[o], q1 = out_ptr[o + 1];
+    const int2 jk = prm.items[out_item[q0]];
     double s = 0.0;
     for (int x = 0; x < 2; x++) {
       const int ie = prm.elem_of[2 * a + x];
@@ -313,7 +463,8 @@ static __global__ void chan_x4_kernel(ChanXParams prm, const int2* items, int ni
       for (int y = 0; y < 2; y++) {
         const int je = prm.elem_of[2 * b + y];
         if (je < 0) continue;
-        s += prm.blocks[((size_t)o * nel2 + ie * nel + je) * np2 + (a - prm.first[ie]) + (b - prm.first[je]) * np];
+        const size_t off = (size_t)(ie * nel + je) * np2 + (a - prm.first[ie]) + (b - prm.first[je]) * np;
+        for (int q = q0; q < q1; q++) s += prm.blocks[(size_t)(out_item[q] - prm.item0) * nel2 * np2 + off];
       }
     }
     prm.K[(size_t)(jk.x * nrad + a) + (size_t)(jk.y * nrad + b) * prm.ldk] -= s;

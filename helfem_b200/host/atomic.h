@@ -41,6 +41,8 @@ class TwoDBasis {
   Mat coulomb(const Mat& P) const;
   /// -K = exchange(P), atomic/TwoDBasis.cpp:957-1140
   Mat exchange(const Mat& P) const;
+  void coulomb(const double* P, double* J) const;   // raw n x n column-major buffers, n = Nbf()
+  void exchange(const double* P, double* K) const;
 
   const std::vector<Mat>& get_disjoint_L() const { return disjoint_L; }
   const std::vector<Mat>& get_disjoint_m1L() const { return disjoint_m1L; }

@@ -278,5 +278,17 @@ Mat TwoDBasis::exchange(const Mat& P) const {
   return K;
 }
 
+
+// Raw-pointer forms of the two operators (n x n column-major, n = Nbf()): what the flat C entry points of
+// hostapi.cpp call, so that a caller's buffers go straight to the C ABI without an intermediate Mat copy.
+void TwoDBasis::coulomb(const double* P, double* J) const {
+  if (prim_tei.empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+  throw_status(hfb200_diatomic_coulomb(context(), P, (int)Nbf(), J, (int)Nbf()));
+}
+void TwoDBasis::exchange(const double* P, double* K) const {
+  if (prim_ktei.empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+  throw_status(hfb200_diatomic_exchange(context(), P, (int)Nbf(), K, (int)Nbf()));
+}
+
 }  // namespace diatomic
 }  // namespace hfb

@@ -84,6 +84,8 @@ class TwoDBasis {
   Mat coulomb(const Mat& P) const;
   /// -K = exchange(P), diatomic/basis.cpp:1532-1733
   Mat exchange(const Mat& P) const;
+  void coulomb(const double* P, double* J) const;   // raw n x n column-major buffers, n = Nbf()
+  void exchange(const double* P, double* K) const;
 
   // stored integrals, index [ilm*Nel + iel]; two-electron blocks [4*(ilm*Nel+iel) + 2a+b]
   const std::vector<Mat>& get_disjoint(int which) const { return disjoint[which]; }  // 0 P0, 1 P2, 2 Q0, 3 Q2

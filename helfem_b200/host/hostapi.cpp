@@ -304,22 +304,12 @@ int hfh_atomic_get_tei(void* h, int L, int iel, double* disL, double* dism1L, do
 }
 int hfh_atomic_coulomb(void* h, const double* P, double* J) {
   HFH_TRY
-  auto* b = (atomic::TwoDBasis*)h;
-  const size_t n = b->Nbf();
-  Mat Pm(n, n);
-  memcpy(Pm.ptr(), P, n * n * sizeof(double));
-  Mat Jm = b->coulomb(Pm);
-  memcpy(J, Jm.ptr(), n * n * sizeof(double));
+  ((atomic::TwoDBasis*)h)->coulomb(P, J);
   HFH_CATCH
 }
 int hfh_atomic_exchange(void* h, const double* P, double* K) {
   HFH_TRY
-  auto* b = (atomic::TwoDBasis*)h;
-  const size_t n = b->Nbf();
-  Mat Pm(n, n);
-  memcpy(Pm.ptr(), P, n * n * sizeof(double));
-  Mat Km = b->exchange(Pm);
-  memcpy(K, Km.ptr(), n * n * sizeof(double));
+  ((atomic::TwoDBasis*)h)->exchange(P, K);
   HFH_CATCH
 }
 
@@ -391,22 +381,12 @@ int hfh_diatomic_get_tei(void* h, int which, int ilm, int iel, double* out) {
 }
 int hfh_diatomic_coulomb(void* h, const double* P, double* J) {
   HFH_TRY
-  auto* b = (diatomic::TwoDBasis*)h;
-  const size_t n = b->Nbf();
-  Mat Pm(n, n);
-  memcpy(Pm.ptr(), P, n * n * sizeof(double));
-  Mat Jm = b->coulomb(Pm);
-  memcpy(J, Jm.ptr(), n * n * sizeof(double));
+  ((diatomic::TwoDBasis*)h)->coulomb(P, J);
   HFH_CATCH
 }
 int hfh_diatomic_exchange(void* h, const double* P, double* K) {
   HFH_TRY
-  auto* b = (diatomic::TwoDBasis*)h;
-  const size_t n = b->Nbf();
-  Mat Pm(n, n);
-  memcpy(Pm.ptr(), P, n * n * sizeof(double));
-  Mat Km = b->exchange(Pm);
-  memcpy(K, Km.ptr(), n * n * sizeof(double));
+  ((diatomic::TwoDBasis*)h)->exchange(P, K);
   HFH_CATCH
 }
 
