@@ -271,6 +271,7 @@ static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, co
       double acc[CHX_T][4];
 #pragma unroll
       for (int kk = 0; kk < CHX_T; kk++) { acc[kk][0] = acc[kk][1] = acc[kk][2] = acc[kk][3] = 0.0; }
+#pragma unroll 4
       for (int u = 0; u < nu; u++) {
         const double* Wp = prm.W + woff[u] + el;
         const double w0 = Wp[0];
@@ -344,7 +345,7 @@ __global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, const int
         __syncthreads();
         const double* A = prm.teiK + ((((size_t)r * nel + ie) * st2 + ab) * MT) * KS * 32 + lane;
         const double* bs = sm + gid * LDK + t4;
-#pragma unroll 2
+#pragma unroll 4
         for (int ks = 0; ks < KS; ks++) {
           double b[NTN], a[4];
 #pragma unroll
