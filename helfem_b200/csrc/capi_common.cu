@@ -71,6 +71,8 @@ void hfb200_destroy(hfb200_ctx* c) {
   if (c->chan) { c->chan->release(); delete c->chan; }
   if (c->g2d) { c->g2d->release(); delete c->g2d; }
   if (c->stream) cudaStreamDestroy(c->stream);
+  for (cudaStream_t q : c->xs)
+    if (q) cudaStreamDestroy(q);
   delete c;
 }
 

@@ -247,6 +247,27 @@ int hfb200_sadatom_unpack_band_add(hfb200_ctx* c, const double* band, double* M,
   return HFB200_OK;
 }
 
+}  // extern "C"
+
+// Kernels of `nbatch` builds whose per-build scratch (folded densities, traces, partial scalars) starts at build
+// index `sb` of the context's scratch buffers, which the caller has reserved for `sb + nbatch` builds at least:
+// chunks of one host batch run concurrently on different streams with disjoint scratch.
+static int fock_batch_at(hfb200_ctx* c, size_t sb, int nbatch, int x_func, int c_func, int nspin, int nslices, double dens_thr,
+                         const double* dP_band, double* dJ_band, double* dH_band, double* dScalars, cudaStream_t st);
+
+static int fock_reserve(hfb200_ctx* c, size_t nbuilds, bool withJ, bool withH) {
+  int rc;
+  if (withJ) {
+    if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+    if ((rc = c->dPtot.reserve(nbuilds * c->nel * 4 * c->jKS))) return rc;
+    if ((rc = c->dTraces.reserve(nbuilds * c->nel * 2))) return rc;
+  }
+  if (withH && (rc = c->dPartial.reserve(nbuilds * c->nel * 4))) return rc;
+  return 0;
+}
+
+extern "C" {
+
 int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func, int nspin, int nslices,
                               double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
                               double* dScalars, void* stream) {
@@ -255,13 +276,19 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
     return HFB200_EINVAL;
   }
   HFB_CUDA_OK(cudaSetDevice(c->device));
-  cudaStream_t st = (cudaStream_t)stream;
   int rc;
-  if (dJ_band) {
-    if (!c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-    if ((rc = c->dPtot.reserve((size_t)nbatch * c->nel * 4 * c->jKS))) return rc;
-    if ((rc = c->dTraces.reserve((size_t)nbatch * c->nel * 2))) return rc;
-  }
+  if ((rc = fock_reserve(c, (size_t)nbatch, dJ_band != nullptr, dH_band != nullptr))) return rc;
+  return fock_batch_at(c, 0, nbatch, x_func, c_func, nspin, nslices, dens_thr, dP_band, dJ_band, dH_band, dScalars, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+
+static int fock_batch_at(hfb200_ctx* c, size_t sb, int nbatch, int x_func, int c_func, int nspin, int nslices, double dens_thr,
+                         const double* dP_band, double* dJ_band, double* dH_band, double* dScalars, cudaStream_t st) {
+  int rc;
+  double* sPtot = dJ_band ? c->dPtot.p + sb * c->nel * 4 * c->jKS : nullptr;
+  double* sTraces = dJ_band ? c->dTraces.p + sb * c->nel * 2 : nullptr;
+  double* sPartial = dH_band ? c->dPartial.p + sb * c->nel * 4 : nullptr;
   // J and Vxc in one build: the grid kernel emits the folded density + traces of the Coulomb kernel, P is read once
   const bool fused_pack = dJ_band && dH_band;
   if (dH_band) {
@@ -270,19 +297,18 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
       set_error("functional pair (%d,%d) has no device implementation (no CPU fallback)", x_func, c_func);
       return HFB200_EFUNC;
     }
-    if ((rc = c->dPartial.reserve((size_t)nbatch * c->nel * 4))) return rc;
     SadGridParams g;
     g.Bt = c->dBt; g.dBt = c->ddBt; g.r = c->dR; g.wrad = c->dW;
     g.nel = c->nel; g.nq = c->nq; g.nq8 = c->nq8; g.ldq = c->ldq; g.np_max = c->np_max; g.np_pad = c->np_pad;
     g.nslices = nslices; g.nb = nbatch;
     g.x_func = x_func; g.c_func = c_func; g.dens_thr = dens_thr;
-    g.P = dP_band; g.H = dH_band; g.partial = c->dPartial.p;
-    g.pc = fused_pack ? c->dPtot.p : nullptr;
-    g.traces = c->dTraces.p; g.dLc = c->dLc; g.dm1Lc = c->dm1Lc; g.tri = c->dTri;
+    g.P = dP_band; g.H = dH_band; g.partial = sPartial;
+    g.pc = fused_pack ? sPtot : nullptr;
+    g.traces = sTraces; g.dLc = c->dLc; g.dm1Lc = c->dm1Lc; g.tri = c->dTri;
     g.ntri = c->ntri; g.jKP = fused_pack ? 4 * c->jKS : 0; g.jMP = 8 * c->jMT;
     if ((rc = launch_grid(fam, nspin, g, st))) return rc;
     if (dScalars) {
-      sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(c->dPartial.p, c->nel, dScalars);
+      sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(sPartial, c->nel, dScalars);
       HFB_CUDA_OK(cudaGetLastError());
     }
   }
@@ -291,11 +317,13 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* c, int nbatch, int x_func, int c_func,
     q.teiF = c->dTeiF; q.dLc = c->dLc; q.dm1Lc = c->dm1Lc; q.tri = c->dTri;
     q.nel = c->nel; q.np_max = c->np_max; q.ntri = c->ntri; q.MT = c->jMT; q.KS = c->jKS;
     q.nslices = nslices; q.nspin = nspin; q.nb = nbatch;
-    q.P = dP_band; q.pc = c->dPtot.p; q.traces = c->dTraces.p; q.J = dJ_band;
+    q.P = dP_band; q.pc = sPtot; q.traces = sTraces; q.J = dJ_band;
     if ((rc = launch_coulomb(q, !fused_pack, st))) return rc;
   }
   return HFB200_OK;
 }
+
+extern "C" {
 
 int hfb200_sadatom_coulomb(hfb200_ctx* c, const double* P, int ldp, double* J, int ldj) {
   if (!c || c->kind != CTX_SADATOM || !P || !J || ldp < c->nrad || ldj < c->nrad) {
@@ -364,7 +392,8 @@ int hfb200_sadatom_eval_fxc(hfb200_ctx* c, int x_func, int c_func, int nspin, co
 }
 
 /* Batched Fock builds with HOST element-band buffers (pinned or pageable): densities down, J / H bands and
- * scalars back, all on the context's stream; returns after the results are on the host. */
+ * scalars back, pipelined in chunks over three streams (H2D, kernels and D2H of different chunks overlap);
+ * returns after the results are on the host. */
 int hfb200_sadatom_fock_host(hfb200_ctx* c, int nbatch, int x_func, int c_func, int nspin, int nslices,
                              double dens_thr, const double* hP_band, double* hJ_band, double* hH_band,
                              double* hScalars) {
@@ -379,15 +408,38 @@ int hfb200_sadatom_fock_host(hfb200_ctx* c, int nbatch, int x_func, int c_func, 
   if ((rc = c->dP.reserve(nP)) || (hH_band && (rc = c->dH.reserve(nP))) || (hJ_band && (rc = c->dJ.reserve(nJ))) ||
       (rc = c->dScalars.reserve((size_t)4 * nbatch)))
     return rc;
-  HFB_CUDA_OK(cudaMemcpyAsync(c->dP.p, hP_band, nP * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  if ((rc = hfb200_sadatom_fock_batch(c, nbatch, x_func, c_func, nspin, nslices, dens_thr, c->dP.p, hJ_band ? c->dJ.p : nullptr,
-                                      hH_band ? c->dH.p : nullptr, (hH_band && hScalars) ? c->dScalars.p : nullptr, c->stream)))
-    return rc;
-  if (hJ_band) HFB_CUDA_OK(cudaMemcpyAsync(hJ_band, c->dJ.p, nJ * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-  if (hH_band) HFB_CUDA_OK(cudaMemcpyAsync(hH_band, c->dH.p, nP * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-  if (hH_band && hScalars)
-    HFB_CUDA_OK(cudaMemcpyAsync(hScalars, c->dScalars.p, (size_t)4 * nbatch * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-  HFB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  if ((rc = fock_reserve(c, (size_t)nbatch, hJ_band != nullptr, hH_band != nullptr))) return rc;
+  if (hH_band) {
+    int fam = 0;
+    if (!valid_pair(x_func, c_func, &fam)) {
+      set_error("functional pair (%d,%d) has no device implementation (no CPU fallback)", x_func, c_func);
+      return HFB200_EFUNC;
+    }
+  }
+  // Chunks of builds round-robin over three streams: the H2D of one chunk, the kernels of another and the D2H of a
+  // third overlap, so the batch costs max(H2D, D2H) instead of their sum (PCIe is full duplex).
+  for (int q = 0; q < 3; q++)
+    if (!c->xs[q]) HFB_CUDA_OK(cudaStreamCreateWithFlags(&c->xs[q], cudaStreamNonBlocking));
+  // (chunks stay above 16 builds: the Coulomb kernel picks a split-K variant below that, and results must not
+  // depend on how a batch is chunked -- the host path reproduces the device-resident path bit for bit)
+  const int chunk = std::max(32, (nbatch + 11) / 12);
+  const size_t perP = nblk * nslices * nspin;
+  int ci = 0;
+  for (int b0 = 0, nb = 0; b0 < nbatch; b0 += nb, ci++) {
+    nb = std::min(chunk, nbatch - b0);
+    if (nbatch - b0 - nb > 0 && nbatch - b0 - nb <= 16) nb = nbatch - b0;
+    cudaStream_t st = c->xs[ci % 3];
+    HFB_CUDA_OK(cudaMemcpyAsync(c->dP.p + b0 * perP, hP_band + b0 * perP, nb * perP * sizeof(double), cudaMemcpyHostToDevice, st));
+    if ((rc = fock_batch_at(c, (size_t)b0, nb, x_func, c_func, nspin, nslices, dens_thr, c->dP.p + b0 * perP,
+                            hJ_band ? c->dJ.p + b0 * nblk : nullptr, hH_band ? c->dH.p + b0 * perP : nullptr,
+                            (hH_band && hScalars) ? c->dScalars.p + (size_t)4 * b0 : nullptr, st)))
+      return rc;
+    if (hJ_band) HFB_CUDA_OK(cudaMemcpyAsync(hJ_band + b0 * nblk, c->dJ.p + b0 * nblk, nb * nblk * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (hH_band) HFB_CUDA_OK(cudaMemcpyAsync(hH_band + b0 * perP, c->dH.p + b0 * perP, nb * perP * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (hH_band && hScalars)
+      HFB_CUDA_OK(cudaMemcpyAsync(hScalars + (size_t)4 * b0, c->dScalars.p + (size_t)4 * b0, (size_t)4 * nb * sizeof(double), cudaMemcpyDeviceToHost, st));
+  }
+  for (int q = 0; q < 3; q++) HFB_CUDA_OK(cudaStreamSynchronize(c->xs[q]));
   return HFB200_OK;
 }
 

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include "../../include/helfem_b200.h"
@@ -377,8 +378,12 @@ int ChanEngine::build_items(const unsigned char* nz) {
     }
   }
   // global lists + batches
-  const long long wcap = (long long)((16ull << 30) / ((size_t)st * nrad2 * sizeof(double)));
-  const long long icap = (long long)((12ull << 30) / ((size_t)st * st * nel * nel * np2 * sizeof(double)));
+  // workspace budgets of a batch (HFB200_X_WCAP_MB / HFB200_X_RCAP_MB override them: the tests force many small batches)
+  size_t wcap_bytes = 16ull << 30, rcap_bytes = 12ull << 30;
+  if (const char* e = getenv("HFB200_X_WCAP_MB")) wcap_bytes = std::max<size_t>(1, (size_t)atoll(e)) << 20;
+  if (const char* e = getenv("HFB200_X_RCAP_MB")) rcap_bytes = std::max<size_t>(1, (size_t)atoll(e)) << 20;
+  const long long wcap = (long long)(wcap_bytes / ((size_t)st * nrad2 * sizeof(double)));
+  const long long icap = (long long)(rcap_bytes / ((size_t)st * st * nel * nel * np2 * sizeof(double)));
   std::vector<int2> items, tiles2, groups;
   std::vector<int> item_fam, out_ptr, out_item;
   std::vector<long long> wbase((size_t)nchan * nang, -1);
@@ -519,28 +524,30 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
 }
 
 namespace {
-template <int NI>
-int launch_x3(const ChanXParams& q, const int2* groups, int ngroups, size_t smem, cudaStream_t st) {
-  const dim3 grid(ngroups, q.nel * q.nel);
-  const int ntl = (q.np + 7) / 8;
-#define HFB_X3(NTL)                                                                                                   \
-  {                                                                                                                   \
-    static bool attr_set = false;                                                                                     \
-    if (!attr_set) {                                                                                                  \
-      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
-      attr_set = true;                                                                                                \
-    }                                                                                                                 \
-    chan_x3_kernel<NI, NTL><<<grid, 256, smem, st>>>(q, groups);                                                      \
+template <int NI, int NTL, bool OFFD>
+int launch_x3_one(const ChanXParams& q, const int2* groups, int ngroups, size_t smem, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
   }
-  switch (ntl) {
-    case 1: HFB_X3(1) break;
-    case 2: HFB_X3(2) break;
-    case 3: HFB_X3(3) break;
-    default: HFB_X3(4) break;
-  }
-#undef HFB_X3
+  const int ny = OFFD ? q.nel * (q.nel - 1) : q.nel;
+  if (ny == 0) return 0;
+  chan_x3_kernel<NI, NTL, OFFD><<<dim3(ngroups, ny), 256, smem, st>>>(q, groups);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
+}
+template <int NI>
+int launch_x3(const ChanXParams& q, const int2* groups, int ngroups, size_t smem_d, size_t smem_o, cudaStream_t st) {
+  const int ntl = (q.np + 7) / 8;
+  int rc;
+  if ((rc = launch_x3_one<NI, 1, false>(q, groups, ngroups, smem_d, st))) return rc;  // the same-element path does not depend on NTL
+  switch (ntl) {
+    case 1: return launch_x3_one<NI, 1, true>(q, groups, ngroups, smem_o, st);
+    case 2: return launch_x3_one<NI, 2, true>(q, groups, ngroups, smem_o, st);
+    case 3: return launch_x3_one<NI, 3, true>(q, groups, ngroups, smem_o, st);
+    default: return launch_x3_one<NI, 4, true>(q, groups, ngroups, smem_o, st);
+  }
 }
 }  // namespace
 
@@ -684,8 +691,8 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     q.wbase = (const long long*)dWbase.p; q.wbits = (const unsigned long long*)dWbits.p; q.nw = (nang + 63) / 64;
     const int ntl = (prm.np + 7) / 8, NI = x3_ni;
     const size_t ybytes = (size_t)8 * 8 * ntl * (8 * ntl + 1) * sizeof(double);
-    const size_t smem3 = std::max((size_t)NI * q.LDK * sizeof(double), ybytes);
-    if (smem3 > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
+    const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
+    if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 255) / 256);
     const size_t smem1 = (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_T * sizeof(long long) +
                          (size_t)(2 * nang + CHX_UMAX) * sizeof(int) + (size_t)nang;
@@ -711,9 +718,9 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       HFB_CUDA_OK(cudaGetLastError());
       tick(2, false);
       tick(3, true);
-      if (NI == 32) rc = launch_x3<32>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
-      else if (NI == 16) rc = launch_x3<16>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
-      else rc = launch_x3<8>(q, (const int2*)dGroups.p + B.g0, ng, smem3, st);
+      if (NI == 32) rc = launch_x3<32>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
+      else if (NI == 16) rc = launch_x3<16>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
+      else rc = launch_x3<8>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
       if (rc) return rc;
       tick(3, false);
       tick(4, true);

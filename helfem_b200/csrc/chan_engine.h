@@ -79,6 +79,7 @@ struct ChanEngine {
   const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;
   // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
   long long last_items = 0;
+  int nbatches() const { return (int)batches.size(); }
   double last_x3_flops = 0.0;
   // optional per-stage device timing of exchange_device (x0 mask, x1, x2, x3, x4), summed over families
   bool profile_stages = false;

@@ -312,13 +312,22 @@ static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, co
   }
 }
 
-// x3.  grid (item groups of the batch, nel*nel), 256 threads; dynamic smem NI*LDK doubles.  groups: (first item, count <= NI)
-// of ONE family.  NTL = 8-row tiles of an (np x np) block (np <= 8 NTL).
-template <int NI, int NTL>
-__global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, const int2* groups) {
+// x3.  Two kernels, 256 threads, over (item groups of the batch) x (element pairs); groups: (first item, count <= NI) of
+// ONE family.  OFFD = false: same element, grid.y = nel, dynamic smem NI*LDK doubles.  OFFD = true: ordered pairs of
+// different elements, grid.y = nel*(nel-1), dynamic smem 8 warps x (8 NTL)(8 NTL + 1) doubles.
+// NTL = 8-row tiles of an (np x np) block (np <= 8 NTL).
+template <int NI, int NTL, bool OFFD>
+__global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const int2* groups) {
   extern __shared__ double sm[];
   const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2, st = prm.stack, st2 = st * st;
-  const int ie = blockIdx.y / nel, je = blockIdx.y % nel;
+  int ie, je;
+  if (OFFD) {
+    ie = blockIdx.y / (nel - 1);
+    const int jj = blockIdx.y % (nel - 1);
+    je = jj + (jj >= ie ? 1 : 0);
+  } else {
+    ie = je = blockIdx.y;
+  }
   const int r = prm.item_fam[groups[blockIdx.x].x];
   const int n0 = groups[blockIdx.x].x - prm.item0, nn = groups[blockIdx.x].y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
@@ -326,7 +335,7 @@ __global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, const int
   const double* Rbase = prm.Rsub + (size_t)n0 * istride + (size_t)(ie * nel + je) * np2;
   double* Obase = prm.blocks + ((size_t)n0 * nel2 + ie * nel + je) * np2;
 
-  if (ie == je) {
+  if constexpr (!OFFD) {
     // ---------------- same element: C[np2 x NI] = sum_ab teiK^{ab} [np2 x np2] . Rsub^{ab} [np2 x NI] ----------------
     constexpr int NTN = NI / 8;
     const int MT = prm.MT, KS = prm.KS, LDK = prm.LDK;
@@ -375,74 +384,98 @@ __global__ void __launch_bounds__(256) chan_x3_kernel(ChanXParams prm, const int
       }
     }
   } else {
-    // ---------------- different elements: Ksub = sum_ab iint^a . Rsub^{ab} . (jint^b)^T, one item per warp pass ----------------
+    // ---------------- different elements: Ksub = sum_ab iint^a . Rsub^{ab} . (jint^b)^T ----------------
+    // A warp owns the items n = warp, warp + 8, ...; the fragments of iint / jint are loaded once per (a,b) and the
+    // accumulators of all its items stay in registers (small element blocks), or one item at a time (large ones).
     constexpr int LDY = 8 * NTL + 1;
+    constexpr int NIT = (NTL <= 2 && NI >= 16) ? 2 : 1;  // items a warp carries through the ab loop together
     double* Y = sm + warp * (8 * NTL * LDY);
     const bool lower = ie > je;
-    for (int n = warp; n < nn; n += 8) {
-      double kacc[NTL][NTL][2];
+    for (int nbase = warp; nbase < nn; nbase += 8 * NIT) {
+      double kacc[NIT][NTL][NTL][2];
 #pragma unroll
-      for (int mt = 0; mt < NTL; mt++)
+      for (int it = 0; it < NIT; it++)
 #pragma unroll
-        for (int qt = 0; qt < NTL; qt++) { kacc[mt][qt][0] = 0.0; kacc[mt][qt][1] = 0.0; }
+        for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+          for (int qt = 0; qt < NTL; qt++) { kacc[it][mt][qt][0] = 0.0; kacc[it][mt][qt][1] = 0.0; }
       for (int ab = 0; ab < st2; ab++) {
         const int a = ab / st, b = ab % st;
         const double* iint = (lower ? prm.big_f : prm.small_f) + (((size_t)r * nel + ie) * st + a) * np2;
         const double* jint = (lower ? prm.small_f : prm.big_f) + (((size_t)r * nel + je) * st + b) * np2;
-        const double* Rn = Rbase + (size_t)n * istride + (size_t)ab * nel2 * np2;
-        // step 1: Y = iint . Rsub
-        double y[NTL][NTL][2];
-#pragma unroll
-        for (int mt = 0; mt < NTL; mt++)
-#pragma unroll
-          for (int nt = 0; nt < NTL; nt++) { y[mt][nt][0] = 0.0; y[mt][nt][1] = 0.0; }
+        double af[2 * NTL][NTL], jf[2 * NTL][NTL];
 #pragma unroll
         for (int ks = 0; ks < 2 * NTL; ks++) {
           const int kk = 4 * ks + t4;
-          double af[NTL], bf[NTL];
 #pragma unroll
-          for (int mt = 0; mt < NTL; mt++) af[mt] = (kk < np && 8 * mt + gid < np) ? __ldg(iint + (8 * mt + gid) + kk * np) : 0.0;
-#pragma unroll
-          for (int nt = 0; nt < NTL; nt++) bf[nt] = (kk < np && 8 * nt + gid < np) ? Rn[kk + (8 * nt + gid) * np] : 0.0;
-#pragma unroll
-          for (int mt = 0; mt < NTL; mt++)
-#pragma unroll
-            for (int nt = 0; nt < NTL; nt++) dmma(y[mt][nt][0], y[mt][nt][1], af[mt], bf[nt]);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int mt = 0; mt < NTL; mt++)
-#pragma unroll
-          for (int nt = 0; nt < NTL; nt++) {
-            Y[(8 * mt + gid) * LDY + 8 * nt + 2 * t4] = y[mt][nt][0];
-            Y[(8 * mt + gid) * LDY + 8 * nt + 2 * t4 + 1] = y[mt][nt][1];
+          for (int mt = 0; mt < NTL; mt++) {
+            const bool ok = kk < np && 8 * mt + gid < np;
+            af[ks][mt] = ok ? __ldg(iint + (8 * mt + gid) + kk * np) : 0.0;
+            jf[ks][mt] = ok ? __ldg(jint + (8 * mt + gid) + kk * np) : 0.0;
           }
-        __syncwarp();
-        // step 2: Ksub += Y . jint^T   (A = Y from shared memory, B[k][q] = jint[q][k])
+        }
 #pragma unroll
-        for (int ks = 0; ks < 2 * NTL; ks++) {
-          const int kk = 4 * ks + t4;
-          double af[NTL], bf[NTL];
+        for (int it = 0; it < NIT; it++) {
+          const int n = nbase + 8 * it;
+          if (n >= nn) break;  // warp-uniform
+          const double* Rn = Rbase + (size_t)n * istride + (size_t)ab * nel2 * np2;
+          // step 1: Y = iint . Rsub
+          double rf[2 * NTL][NTL];
 #pragma unroll
-          for (int mt = 0; mt < NTL; mt++) af[mt] = Y[(8 * mt + gid) * LDY + kk];
+          for (int ks = 0; ks < 2 * NTL; ks++) {
+            const int kk = 4 * ks + t4;
 #pragma unroll
-          for (int qt = 0; qt < NTL; qt++) bf[qt] = (kk < np && 8 * qt + gid < np) ? __ldg(jint + (8 * qt + gid) + kk * np) : 0.0;
+            for (int nt = 0; nt < NTL; nt++) rf[ks][nt] = (kk < np && 8 * nt + gid < np) ? Rn[kk + (8 * nt + gid) * np] : 0.0;
+          }
+          double y[NTL][NTL][2];
 #pragma unroll
           for (int mt = 0; mt < NTL; mt++)
 #pragma unroll
-            for (int qt = 0; qt < NTL; qt++) dmma(kacc[mt][qt][0], kacc[mt][qt][1], af[mt], bf[qt]);
+            for (int nt = 0; nt < NTL; nt++) { y[mt][nt][0] = 0.0; y[mt][nt][1] = 0.0; }
+#pragma unroll
+          for (int ks = 0; ks < 2 * NTL; ks++)
+#pragma unroll
+            for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+              for (int nt = 0; nt < NTL; nt++) dmma(y[mt][nt][0], y[mt][nt][1], af[ks][mt], rf[ks][nt]);
+          __syncwarp();
+#pragma unroll
+          for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+            for (int nt = 0; nt < NTL; nt++) {
+              Y[(8 * mt + gid) * LDY + 8 * nt + 2 * t4] = y[mt][nt][0];
+              Y[(8 * mt + gid) * LDY + 8 * nt + 2 * t4 + 1] = y[mt][nt][1];
+            }
+          __syncwarp();
+          // step 2: Ksub += Y . jint^T   (A = Y from shared memory, B[k][q] = jint[q][k])
+#pragma unroll
+          for (int ks = 0; ks < 2 * NTL; ks++) {
+            const int kk = 4 * ks + t4;
+            double yf[NTL];
+#pragma unroll
+            for (int mt = 0; mt < NTL; mt++) yf[mt] = Y[(8 * mt + gid) * LDY + kk];
+#pragma unroll
+            for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+              for (int qt = 0; qt < NTL; qt++) dmma(kacc[it][mt][qt][0], kacc[it][mt][qt][1], yf[mt], jf[ks][qt]);
+          }
         }
       }
-      double* On = Obase + (size_t)n * nel2 * np2;
 #pragma unroll
-      for (int mt = 0; mt < NTL; mt++)
+      for (int it = 0; it < NIT; it++) {
+        const int n = nbase + 8 * it;
+        if (n >= nn) break;
+        double* On = Obase + (size_t)n * nel2 * np2;
 #pragma unroll
-        for (int qt = 0; qt < NTL; qt++)
+        for (int mt = 0; mt < NTL; mt++)
 #pragma unroll
-          for (int cc = 0; cc < 2; cc++) {
-            const int row = 8 * mt + gid, col = 8 * qt + 2 * t4 + cc;
-            if (row < np && col < np) On[row + col * np] = kacc[mt][qt][cc];
-          }
+          for (int qt = 0; qt < NTL; qt++)
+#pragma unroll
+            for (int cc = 0; cc < 2; cc++) {
+              const int row = 8 * mt + gid, col = 8 * qt + 2 * t4 + cc;
+              if (row < np && col < np) On[row + col * np] = kacc[it][mt][qt][cc];
+            }
+      }
     }
   }
 }

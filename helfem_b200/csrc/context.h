@@ -64,6 +64,7 @@ struct hfb200_ctx {
   int kind = 0;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t xs[3] = {nullptr, nullptr, nullptr};  // chunk pipeline of the host-buffer batch calls
   // ---- radial tables ----
   int lmax = 0, nel = 0, nq = 0, nq8 = 0, ldq = 0, np_max = 0, np_pad = 0, nrad = 0;
   std::vector<int> first, last;

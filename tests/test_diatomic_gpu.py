@@ -16,6 +16,7 @@ CASES = {
     "n2_l2m1": (7, 7, 2.068, 4, 6, 2, 2, 1),
     "co_l3m2": (6, 8, 2.132, 4, 5, 3, [3, 3, 2], 2),
     "n2_hip_l1m1": (7, 7, 2.068, 5, 4, 2, 1, 1),
+    "n2_l5m2": (7, 7, 2.068, 4, 6, 3, 5, 2),
 }
 _cache = {}
 
@@ -102,3 +103,19 @@ def test_diatomic_exchange_block_sparse_density(native, case):
     assert np.max(np.abs(K - Ko)) <= tol(Ko)
     Z = b.exchange(np.zeros_like(P))
     assert np.max(np.abs(Z)) == 0.0
+
+
+def test_diatomic_exchange_many_batches(native, monkeypatch):
+    """The families are processed in batches whose workspaces fit a budget; with a 1 MB budget every family (or two)
+    is its own batch; only the association of the per-family sums changes (rounding level)."""
+    import helfem_b200 as hb
+    Z1, Z2, Rb, primbas, nnodes, nelem, lmax, mmax = CASES["co_l3m2"]
+    b, o, P = setup_case("co_l3m2")
+    K1 = b.exchange(P)
+    monkeypatch.setenv("HFB200_X_WCAP_MB", "1")
+    monkeypatch.setenv("HFB200_X_RCAP_MB", "1")
+    b2 = hb.DiatomicBasis(Z1, Z2, Rb, nelem=nelem, nnodes=nnodes, primbas=primbas, lmax=lmax, mmax=mmax)
+    b2.compute_tei(True)
+    K2 = b2.exchange(P)
+    assert np.max(np.abs(K1 - K2)) <= 1e-12 * np.max(np.abs(K1))
+    assert np.max(np.abs(K2 - o.exchange(P))) <= tol(K1)
