@@ -26,8 +26,8 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
+if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+    os.environ["NCCL_DEBUG"] = "NONE"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
@@ -459,7 +459,11 @@ def run_chan(args, w, rank, world, local_rank):
                              lmax=w["lmax"], mmax=w["mmax"], device=local_rank)
     sharded = bool(args.shard) and world > 1
     if sharded:
-        b.set_shard(rank, world)  # integral families r % world == rank; partial operators are all-reduced (NCCL)
+        # integral families r % world == rank; partial operators are all-reduced (NCCL)
+        if kind == "diatomic":
+            b.set_shard(rank, world, owned_only=True)
+        else:
+            b.set_shard(rank, world)
     b.compute_tei(True)
     t_tei = time.perf_counter() - t0
     t0 = time.perf_counter()
@@ -541,13 +545,38 @@ def run_chan(args, w, rank, world, local_rank):
     else:
         Ph = np.asfortranarray(Ph)
     ne2e = 1 if n > 8000 else 3
-    b.coulomb(Ph); b.exchange(Ph)
+
+    if sharded:
+        # sharded end to end: every rank uploads P from pinned host memory, contracts its families through the
+        # device-resident entry points, J and K are summed over NCCL on the device, rank 0 downloads the result
+        hP = torch.empty((n, n), dtype=torch.float64).pin_memory()
+        hP.copy_(dP.cpu())
+        hJ = torch.empty((n, n), dtype=torch.float64).pin_memory()
+        hK = torch.empty((n, n), dtype=torch.float64).pin_memory()
+
+        def host_build():
+            dP.copy_(hP, non_blocking=True)
+            step()
+            if rank == 0:
+                hJ.copy_(dJ, non_blocking=True)
+                hK.copy_(dK, non_blocking=True)
+            torch.cuda.synchronize()
+            return hJ, hK
+    else:
+        def host_build():
+            return b.coulomb(Ph), b.exchange(Ph)
+
+    host_build()
     barrier()
     t0 = time.perf_counter()
     for _ in range(ne2e):
-        Jh = b.coulomb(Ph)
-        Kh = b.exchange(Ph)
+        Jh, Kh = host_build()
+    torch.cuda.synchronize()
     t_e2e = (time.perf_counter() - t0) / ne2e
+    if dist is not None:
+        t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -566,7 +595,7 @@ def run_chan(args, w, rank, world, local_rank):
         tc = time.perf_counter() - t0
         cpu = {"value": 1.0 / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
                "sample": "1 Fock build (coulomb + exchange) of the same workload",
-               "max_dJ": float(np.max(np.abs(Jh - Jo))), "max_dK": float(np.max(np.abs(Kh - Ko)))}
+               "max_dJ": float(np.max(np.abs(np.asarray(Jh) - Jo))), "max_dK": float(np.max(np.abs(np.asarray(Kh) - Ko)))}
     tf = x3_flops / (stage[3] * 1e-3) / 1e12 if stage[3] > 0 else None
     roofline = {"kernel": "chan_x3_kernel", "bound": "tensor", "achieved": tf, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s",
                 "frac": (tf / FP64_TFLOPS_MEASURED) if tf else None, "traffic": ncu_traffic(args.workload, "chan_x3_kernel"),
@@ -584,8 +613,11 @@ def run_chan(args, w, rank, world, local_rank):
                                      else "independent builds per rank, no data-path collective"),
                        "setup_s": {"compute_tei_host": t_tei, "upload": t_upload, "first_build": t_first}},
             "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": {"value": units / t_e2e, "unit": "builds/s", "h2d_bytes_per_step": 2 * nb * nb * 8, "d2h_bytes_per_step": 2 * nb * nb * 8,
-                    "api": "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis)"},
+            "e2e": {"value": units / t_e2e, "unit": "builds/s",
+                    "h2d_bytes_per_step": (n * n * 8 * world) if sharded else 2 * nb * nb * 8,
+                    "d2h_bytes_per_step": (2 * n * n * 8) if sharded else 2 * nb * nb * 8,
+                    "api": ("pinned host P -> hfb200_chan_coulomb_device + hfb200_chan_exchange_device on every rank -> NCCL all-reduce -> "
+                            "host J, K on rank 0" if sharded else "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis)")},
             "gpu_launches": int(args.steps * (5 + 1 + 4 * (b.nlm if kind == "diatomic" else b.nL))), "clocks": clocks}
     print(json.dumps(line), flush=True)
     if dist is not None:

@@ -91,6 +91,10 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
 // coefficient table, and streams every input block ONCE for all its rows instead of once per row.
 constexpr int CHX_T = 8;      // rows (x1: j, x2: k) per tile
 constexpr int CHX_UMAX = 64;  // union slots per pass
+#ifndef HFB_CHX_PF
+#define HFB_CHX_PF 6
+#endif
+constexpr int CHX_PF = HFB_CHX_PF;  // prefetch distance (partners ahead) of the x2 stream
 
 // slots for the flagged entries of dom[0..n): -1 = absent, 0 = present on entry; slot number on exit.  Warp 0 only.
 __device__ __forceinline__ int chx_scan_slots(int* dom, int* ulist, int n, int lane) {
@@ -274,6 +278,11 @@ static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, co
 #pragma unroll 4
       for (int u = 0; u < nu; u++) {
         const double* Wp = prm.W + woff[u] + el;
+        if (u + CHX_PF < nu) {  // pull the blocks CHX_PF partners ahead towards L2 (no registers held, unlike a deeper unroll)
+          const double* Wn = prm.W + woff[u + CHX_PF] + el;
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(Wn));
+          if (st == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(Wn + nrad2));
+        }
         const double w0 = Wp[0];
         const double w1 = st == 2 ? Wp[nrad2] : 0.0;
         const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);

@@ -89,9 +89,11 @@ class DiatomicBasis:
     def set_profile(self, on=True):
         check(lib().hfb200_chan_set_profile(self.context(), int(bool(on))))
 
-    def set_shard(self, rank, nranks):
-        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""
+    def set_shard(self, rank, nranks, owned_only=False):
+        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call).
+        owned_only: compute_tei builds the stored integrals of the owned families only."""
         check_host(lib().hfh_diatomic_set_shard(self._h, int(rank), int(nranks)))
+        check_host(lib().hfh_diatomic_set_owned_only(self._h, int(bool(owned_only))))
 
     def coulomb(self, P):
         P = np.asfortranarray(P, dtype=np.float64)

@@ -216,6 +216,7 @@ void TwoDBasis::compute_tei(bool exchange) {
 #endif
   for (size_t ilm = 0; ilm < nlm; ilm++)
     for (size_t iel = 0; iel < Nel; iel++) {
+      if (owned_only && (int)(ilm % (size_t)shard_n) != shard_rank) continue;  // family held by another rank
       const int L = lm_map[ilm].first, M = lm_map[ilm].second;
       const size_t idx = ilm * Nel + iel;
       disjoint[0][idx] = radial.Plm_integral(0, iel, L, M);

@@ -93,6 +93,9 @@ class TwoDBasis {
   const std::vector<Mat>& get_prim_ktei() const { return prim_ktei; }
   /// multi-GPU: this object contracts only the integral families r % nranks == rank (see hfb200_set_shard)
   void set_shard(int rank, int nranks) { shard_rank = rank; shard_n = nranks; }
+  /// with a shard set: compute_tei only builds the stored integrals of the owned families (1/nranks of the setup
+  /// time and host memory); the others stay empty and are never read
+  void set_owned_only(bool on) { owned_only = on; }
   hfb200_ctx* context() const;
 
  private:
@@ -104,6 +107,7 @@ class TwoDBasis {
   std::vector<Mat> disjoint[4];
   std::vector<Mat> prim_tei, prim_ktei;
   int shard_rank = 0, shard_n = 1;
+  bool owned_only = false;
   mutable hfb200_ctx* ctx = nullptr;
   mutable bool tei_uploaded = false;
 };

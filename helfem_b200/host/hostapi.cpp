@@ -183,6 +183,11 @@ int hfh_atomic_context(void* h, hfb200_ctx** ctx) {
   *ctx = ((atomic::TwoDBasis*)h)->context();
   HFH_CATCH
 }
+int hfh_diatomic_set_owned_only(void* h, int on) {
+  HFH_TRY
+  ((diatomic::TwoDBasis*)h)->set_owned_only(on != 0);
+  HFH_CATCH
+}
 int hfh_diatomic_context(void* h, hfb200_ctx** ctx) {
   HFH_TRY
   *ctx = ((diatomic::TwoDBasis*)h)->context();
