@@ -480,16 +480,18 @@ def run_chan(args, w, rank, world, local_rank):
     sh = stream.cuda_stream
     assert sh != 0
 
+    from helfem_b200 import shard as shard_mod
+
     def step(J=True, K=True):
         if J:
             b.coulomb_device(dP.data_ptr(), dJ.data_ptr(), n, sh)
         if K:
             b.exchange_device(dP.data_ptr(), dK.data_ptr(), n, sh)
-        if sharded:
+        if sharded:  # NCCL moves the non-zero angular blocks only
             if J:
-                dist.all_reduce(dJ)
+                shard_mod.allreduce_blocksparse_(dJ, b.nang, b.nrad)
             if K:
-                dist.all_reduce(dK)
+                shard_mod.allreduce_blocksparse_(dK, b.nang, b.nrad)
 
     def barrier():
         if dist is not None:

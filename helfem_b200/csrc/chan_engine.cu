@@ -714,7 +714,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       if (nt2 == 0) continue;
       tick(2, true);
       const int ny2 = std::max(1, std::min(nchunk, 2368 / std::max(nt2, 1)));
-      chan_x2_kernel<<<dim3(nt2, ny2), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
+      chan_x2_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
       HFB_CUDA_OK(cudaGetLastError());
       tick(2, false);
       tick(3, true);

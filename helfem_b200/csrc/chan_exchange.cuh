@@ -91,10 +91,6 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
 // coefficient table, and streams every input block ONCE for all its rows instead of once per row.
 constexpr int CHX_T = 8;      // rows (x1: j, x2: k) per tile
 constexpr int CHX_UMAX = 64;  // union slots per pass
-#ifndef HFB_CHX_PF
-#define HFB_CHX_PF 6
-#endif
-constexpr int CHX_PF = HFB_CHX_PF;  // prefetch distance (partners ahead) of the x2 stream
 
 // slots for the flagged entries of dom[0..n): -1 = absent, 0 = present on entry; slot number on exit.  Warp 0 only.
 __device__ __forceinline__ int chx_scan_slots(int* dom, int* ulist, int n, int lane) {
@@ -128,7 +124,7 @@ __device__ __forceinline__ long long chx_wblock(const ChanXParams& prm, int row,
 // dynamic smem: coef[UMAX][T][2] doubles | wblk[T] long long | ulist[nang] | dom[nang] | act[UMAX] ints | done[nang] bytes
 static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, const int* tiles) {
   extern __shared__ double sm[];
-  __shared__ int s_cnt;
+  __shared__ int s_cnt, s_na;
   const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack;
   double* coef = sm;
   long long* wblk = reinterpret_cast<long long*>(coef + CHX_UMAX * CHX_T * 2);
@@ -168,13 +164,22 @@ static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, co
     }
     for (int l = blockIdx.y; l < nang; l += gridDim.y) {
       __syncthreads();  // coef complete / previous l done with act and wblk
-      int mine = 0;
-      if (tid < nu) {
-        mine = prm.nzP[(size_t)ulist[ubase + tid] * nang + l];
-        act[tid] = mine;
+      // compact list of the partners whose P block is non-zero (warp 0: ballot scan), so that the stream loop is branch free
+      if (warp == 0) {
+        int base = 0;
+        for (int q0 = 0; q0 < nu; q0 += 32) {
+          const int q = q0 + lane;
+          const bool f = q < nu && prm.nzP[(size_t)ulist[ubase + q] * nang + l];
+          const unsigned mk = __ballot_sync(0xffffffffu, f);
+          if (f) act[base + __popc(mk & ((1u << lane) - 1u))] = q;
+          base += __popc(mk);
+        }
+        if (lane == 0) s_na = base;
       }
       if (tid < CHX_T) wblk[tid] = tid < nj ? chx_wblock(prm, c * nang + T[2 + tid], l) : -1;
-      if (!__syncthreads_or(mine)) continue;  // block-uniform
+      __syncthreads();
+      const int na = s_na;
+      if (na == 0) continue;  // block-uniform
       const bool prev = done[l] != 0;  // an earlier pass already wrote the blocks of this l
       for (int k = tid; k < nrad2; k += 256) {
         const int A = k % nrad, B = k / nrad;
@@ -182,8 +187,9 @@ static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, co
         double acc[CHX_T][2];
 #pragma unroll
         for (int jj = 0; jj < CHX_T; jj++) { acc[jj][0] = 0.0; acc[jj][1] = 0.0; }
-        for (int u = 0; u < nu; u++) {
-          if (!act[u]) continue;
+#pragma unroll 4
+        for (int v = 0; v < na; v++) {
+          const int u = act[v];
           const double p = src[(size_t)ulist[ubase + u] * nrad];
           const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);
 #pragma unroll
@@ -210,9 +216,9 @@ static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, co
   // blocks of the rows' sets that no pass reached cannot exist: l in L(c,j) means an active partner in some pass
 }
 
-// x2.  grid (tiles of the batch, element chunks), 256 threads.  A tile = <= CHX_T consecutive items (j, k_0..) of one family, one j.
+// x2.  grid (tiles of the batch, element chunks, stack half a), 256 threads.  A tile = <= CHX_T consecutive items (j, k_0..) of one family, one j.
 // dynamic smem: coef[UMAX][T][2] doubles | woff[UMAX] (size_t) | ulist[D] | dom[D] ints, D = nch_max*nang
-static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
+static __global__ void __launch_bounds__(256, 3) chan_x2_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
   extern __shared__ double sm[];
   __shared__ int s_cnt;
   const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack, st2 = st * st;
@@ -271,28 +277,23 @@ static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, co
       }
     }
     __syncthreads();
+    // one stack half a = blockIdx.z per CTA: 2 T accumulators per thread keep the register count low enough for
+    // three resident CTAs, and the u loop unrolled by 8 keeps eight independent loads in flight per thread
+    const int a = blockIdx.z;
     for (int el = blockIdx.y * 256 + tid; el < nrad2; el += gridDim.y * 256) {
-      double acc[CHX_T][4];
+      double acc[CHX_T][2];
 #pragma unroll
-      for (int kk = 0; kk < CHX_T; kk++) { acc[kk][0] = acc[kk][1] = acc[kk][2] = acc[kk][3] = 0.0; }
-#pragma unroll 4
+      for (int kk = 0; kk < CHX_T; kk++) { acc[kk][0] = 0.0; acc[kk][1] = 0.0; }
+      const double* Wa = prm.W + (size_t)a * nrad2 + el;
+#pragma unroll 8
       for (int u = 0; u < nu; u++) {
-        const double* Wp = prm.W + woff[u] + el;
-        if (u + CHX_PF < nu) {  // pull the blocks CHX_PF partners ahead towards L2 (no registers held, unlike a deeper unroll)
-          const double* Wn = prm.W + woff[u + CHX_PF] + el;
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(Wn));
-          if (st == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(Wn + nrad2));
-        }
-        const double w0 = Wp[0];
-        const double w1 = st == 2 ? Wp[nrad2] : 0.0;
+        const double w = Wa[woff[u]];
         const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);
 #pragma unroll
         for (int kk = 0; kk < CHX_T; kk++) {
           const double2 cc = cf[kk];
-          acc[kk][0] = fma(cc.x, w0, acc[kk][0]);  // (a,b) = (0,0)
-          acc[kk][1] = fma(cc.y, w0, acc[kk][1]);  // (0,1)
-          acc[kk][2] = fma(cc.x, w1, acc[kk][2]);  // (1,0)
-          acc[kk][3] = fma(cc.y, w1, acc[kk][3]);  // (1,1)
+          acc[kk][0] = fma(cc.x, w, acc[kk][0]);  // b = 0
+          acc[kk][1] = fma(cc.y, w, acc[kk][1]);  // b = 1
         }
       }
       // scatter into the element-pair sub-blocks (a radial function belongs to one or two elements)
@@ -308,11 +309,13 @@ static __global__ void __launch_bounds__(256) chan_x2_kernel(ChanXParams prm, co
           for (int kk = 0; kk < CHX_T; kk++) {
             if (kk >= nk) break;
             double* out = prm.Rsub + (size_t)(it0 - prm.item0 + kk) * istride + off;
-            for (int ab = 0; ab < st2; ab++) {
-              const int a = ab / st, b = ab % st;
-              const double v = (a != b ? -fac : fac) * acc[kk][st == 2 ? ab : 0];
-              if (ubase == 0) out[(size_t)ab * nel2 * np2] = v;
-              else out[(size_t)ab * nel2 * np2] += v;
+#pragma unroll
+            for (int b = 0; b < 2; b++) {
+              if (b < st) {
+                const double v = (a != b ? -fac : fac) * acc[kk][b];
+                if (ubase == 0) out[(size_t)(a * st + b) * nel2 * np2] = v;
+                else out[(size_t)(a * st + b) * nel2 * np2] += v;
+              }
             }
           }
         }

@@ -57,6 +57,33 @@ def allreduce_operator(M, group=None, device=None):
     return np.asfortranarray(out.T) if fortran else out
 
 
+def allreduce_blocksparse_(dM, nang, nrad, group=None):
+    """In-place sum over the ranks of a DEVICE-resident dense operator (torch tensor, (nang*nrad)^2) whose angular
+    blocks are mostly zero (a linear molecule / an atom only populates the m-diagonal blocks: 1/13 of the matrix at
+    lmax 24, mmax 6).  The ranks agree on the union of their non-zero blocks (one all-reduce of a nang^2 byte mask),
+    pack those blocks contiguously, all-reduce the packed buffer and scatter it back: NCCL moves the non-zero
+    blocks only.  Exact: blocks outside the union are zero on every rank."""
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return dM
+    M4 = dM.view(nang, nrad, nang, nrad)
+    mask = (M4.abs().amax(dim=(1, 3)) > 0).to(torch.uint8)
+    dist.all_reduce(mask, op=dist.ReduceOp.MAX, group=group)
+    idx = mask.nonzero(as_tuple=True)
+    if idx[0].numel() == 0:
+        return dM
+    if idx[0].numel() * 2 > nang * nang:  # dense enough: one plain all-reduce
+        dist.all_reduce(dM, op=dist.ReduceOp.SUM, group=group)
+        return dM
+    Mb = M4.permute(0, 2, 1, 3)           # (nang, nang, nrad, nrad) view
+    packed = Mb[idx[0], idx[1]].contiguous()
+    dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+    Mb[idx[0], idx[1]] = packed
+    return dM
+
+
 class ShardedOperator:
     """J / K of an AtomicBasis or DiatomicBasis distributed over the ranks of a process group.
 

@@ -79,6 +79,18 @@ def _worker(rank, world, port, q):
         J = shard.allreduce_operator(Jp)
         K = shard.allreduce_operator(Kp)
         assert J.flags.f_contiguous and J.shape == Jp.shape
+        # block-sparse in-place all-reduce of a device-style tensor (here on the CPU): only the union of non-zero
+        # angular blocks travels; the result equals the plain sum exactly
+        import torch
+        nang_t, nrad_t = 6, 4
+        gen = torch.Generator().manual_seed(7)
+        parts = [torch.zeros(nang_t * nrad_t, nang_t * nrad_t, dtype=torch.float64) for _ in range(world)]
+        for r, blocks in enumerate(([(0, 0), (1, 1), (2, 3)], [(1, 1), (5, 5)])):
+            v = parts[r].view(nang_t, nrad_t, nang_t, nrad_t)
+            for (bi, bj) in blocks:
+                v[bi, :, bj, :] = torch.rand(nrad_t, nrad_t, generator=gen, dtype=torch.float64)
+        bs = shard.allreduce_blocksparse_(parts[rank].clone(), nang_t, nrad_t)
+        assert torch.equal(bs, parts[0] + parts[1])
         # independent units: every rank takes its slice, results are gathered by rank 0 only for reporting
         b, e = shard.partition_units(7, rank, world)
         counts = [None] * world
