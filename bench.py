@@ -51,6 +51,9 @@ WORKLOADS = {
 }
 
 
+FP64_TFLOPS_MEASURED = 35.5  # cuBLAS DGEMM 8192^3 on this pool's B200, profiles/r01_fp64_peak.json (MEASURED_PEAKS.json has no FP64 entry)
+
+
 def ncu_traffic(workload, kernel):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same
     workload (profiles/ncu_traffic.json, written from the .ncu-rep by tools/ncu_summary.py); None if not captured."""
@@ -378,11 +381,19 @@ def run_gpu(args, w, rank, world, local_rank):
         kname, kms, kbytes = "sad_coulomb_kernel", ms_j, alg["j_bytes_batched"] * nb
         kflops = alg["j_flops"] * nb
     achieved = kbytes / (kms * 1e-3) / 1e9
-    roofline = {"kernel": kname, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": ncu_traffic(args.workload, kname), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": kbytes, "ms_per_launch": kms,
-                "fp64_tflops_algorithmic": kflops / (kms * 1e-3) / 1e12,
-                "ms_grid_kernel": ms_grid, "ms_coulomb_kernels": ms_j}
+    tflops = kflops / (kms * 1e-3) / 1e12
+    hbm_frac, fp64_frac = achieved / hbm_peak, tflops / FP64_TFLOPS_MEASURED
+    # the kernel's algorithmic intensity sits at or above the FP64 ridge, so both fractions are reported
+    # and the larger one names the binding roof ("tensor" = the FP64 DMMA/DFMA pipe; tcgen05 has no FP64 kind)
+    common = {"kernel": kname, "traffic": ncu_traffic(args.workload, kname), "algorithmic_bytes_per_launch": kbytes,
+              "algorithmic_flops_per_launch": kflops, "ms_per_launch": kms, "ms_grid_kernel": ms_grid, "ms_coulomb_kernels": ms_j,
+              "hbm": {"achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_frac, "peak_source": peak_src},
+              "fp64": {"achieved": tflops, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s", "frac": fp64_frac,
+                       "peak_source": "measured cuBLAS DGEMM FP64 (profiles/r01_fp64_peak.json)"}}
+    if fp64_frac >= hbm_frac:
+        roofline = dict({"bound": "tensor", "achieved": tflops, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s", "frac": fp64_frac}, **common)
+    else:
+        roofline = dict({"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_frac}, **common)
     # CPU baseline: the oracle port on this box's host cores, bounded sample
     cpu = None
     if world == 1:  # reported at N = 1 only
@@ -416,9 +427,6 @@ def run_gpu(args, w, rank, world, local_rank):
 # ------------------------------------------------------------------------------------------------
 # atomic / diatomic Hartree-Fock builds: J + K through the Gaunt-coupled channel engine
 # ------------------------------------------------------------------------------------------------
-FP64_TFLOPS_MEASURED = 35.5  # cuBLAS DGEMM 8192^3 on this pool's B200, profiles/r01_fp64_peak.json (MEASURED_PEAKS.json has no FP64 entry)
-
-
 def chan_orbitals(b, kind, rank):
     """Synthetic occupied orbitals, each pure in m (what an SCF of an atom / linear molecule produces): smooth seeded
     coefficients decaying with l and with the radial index.  Returns C (ndim x norb) in the operator's index space."""
@@ -604,7 +612,7 @@ def run_chan(args, w, rank, world, local_rank):
                 "peak_source": "measured cuBLAS DGEMM FP64 (profiles/r01_fp64_peak.json); tcgen05 has no FP64 kind, DMMA.8x8x4 is the FP64 tensor path",
                 "algorithmic_flops_per_build": x3_flops, "ms_per_build": stage[3],
                 "exchange_stage_ms": dict(zip(["mask", "x1_left_angular", "x2_right_angular", "x3_radial_dmma", "x4_assemble"], stage)),
-                "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items}
+                "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items, "family_batches": b.exchange_batches()}
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -620,7 +628,8 @@ def run_chan(args, w, rank, world, local_rank):
                     "d2h_bytes_per_step": (2 * n * n * 8) if sharded else 2 * nb * nb * 8,
                     "api": ("pinned host P -> hfb200_chan_coulomb_device + hfb200_chan_exchange_device on every rank -> NCCL all-reduce -> "
                             "host J, K on rank 0" if sharded else "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis)")},
-            "gpu_launches": int(args.steps * (5 + 1 + 4 * (b.nlm if kind == "diatomic" else b.nL))), "clocks": clocks}
+            # coulomb: pack, pre, DMMA, post, unpack; exchange: mask + (x1, x2, x3 same-element, x3 pairs, x4) per family batch
+            "gpu_launches": int(args.steps * (5 + 1 + 5 * b.exchange_batches())), "clocks": clocks}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

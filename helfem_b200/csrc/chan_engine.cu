@@ -242,15 +242,13 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
             coef[2 * (size_t)pos] = cp.coef[0];
             coef[2 * (size_t)pos + 1] = st == 2 ? cp.coef[1] : 0.0;
           }
-    std::vector<int2> rows;
-    fam_row0.assign(nr + 1, 0);
+    fam_rows.assign(nr, 0);  // non-empty coupling rows of a family (0: family not coupled / held by another rank)
     nch_max = 1;
     for (int r = 0; r < nr; r++) {
       nch_max = std::max(nch_max, fam_c0_host[r + 1] - fam_c0_host[r]);
       for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
         for (int j = 0; j < nang; j++)
-          if (xrowptr[(size_t)c * nang + j + 1] > xrowptr[(size_t)c * nang + j]) rows.push_back(make_int2(c, j));
-      fam_row0[r + 1] = (int)rows.size();
+          if (xrowptr[(size_t)c * nang + j + 1] > xrowptr[(size_t)c * nang + j]) fam_rows[r]++;
     }
     // x1 tiles: rows of a channel grouped by angular group (same m => same coupling partners), CHX_T rows each
     ang_group = S.ang_group.size() == (size_t)nang ? S.ang_group : std::vector<int>(nang, 0);
@@ -276,11 +274,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     const int* dt1 = nullptr;
     if ((rc = up(this, &dt1, tiles1))) return rc;
     dTiles1 = const_cast<int*>(dt1);
-    const int2* drows = nullptr;
-    if ((rc = up(this, &xprm.rowptr, xrowptr)) || (rc = up(this, &xprm.row_i, xrow_i)) || (rc = up(this, &xprm.row_coef, coef)) ||
-        (rc = up(this, &drows, rows)))
-      return rc;
-    dRows = const_cast<int2*>(drows);
+    if ((rc = up(this, &xprm.rowptr, xrowptr)) || (rc = up(this, &xprm.row_i, xrow_i)) || (rc = up(this, &xprm.row_coef, coef))) return rc;
   }
   {
     unsigned char* p = nullptr;
@@ -337,7 +331,7 @@ int ChanEngine::build_items(const unsigned char* nz) {
     std::vector<int> js;
 #pragma omp for schedule(dynamic)
     for (int r = 0; r < nr; r++) {
-      if (fam_row0[r + 1] == fam_row0[r]) continue;
+      if (fam_rows[r] == 0) continue;
       std::fill(hit.begin(), hit.end(), 0);
       for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++) {
         js.clear();
@@ -797,6 +791,11 @@ int hfb200_chan_exchange_stats(hfb200_ctx* c, long long* items, double* x3_flops
   if (x3_flops) *x3_flops = c->chan->last_x3_flops;
   if (stage_ms)
     for (int q = 0; q < 5; q++) stage_ms[q] = c->chan->stage_ms[q];
+  return HFB200_OK;
+}
+int hfb200_chan_exchange_batches(hfb200_ctx* c, int* nbatches) {
+  if (!c || !c->chan || !nbatches) { hfb::set_error("hfb200_chan_exchange_batches: invalid argument"); return HFB200_EINVAL; }
+  *nbatches = c->chan->nbatches();
   return HFB200_OK;
 }
 int hfb200_chan_set_profile(hfb200_ctx* c, int on) {

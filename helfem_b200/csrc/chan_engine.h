@@ -40,15 +40,14 @@ struct ChanEngine {
   std::vector<void*> owned;         // device allocations to free
   DevBuf dP, dPc, dTr, dJc, dJ;
   PinBuf hIn, hOut;
-  std::vector<int> fam_c0_host, out_pairs_host;
+  std::vector<int> fam_c0_host;
   // exchange tables (chan_exchange.cuh)
   bool have_k = false;
   ChanXParams xprm{};
   int nch_max = 0, x3_ni = 32;
   std::vector<double> fam_fac;                      // [nr]
   std::vector<int> xrowptr, xrow_i;                 // host copy of the coupling rows (item lists are derived from them)
-  std::vector<int> fam_row0;                        // [nr+1] range of each family in dRows
-  int2* dRows = nullptr;                            // (channel, j) of every non-empty coupling row, grouped by family
+  std::vector<int> fam_rows;                        // [nr] non-empty coupling rows of each family
   // per sparsity pattern of P (build_items): output blocks of every family, compact W layout, tiles, batches
   std::vector<unsigned char> mask_cached;
   struct XBatch { int t1_0, t1_1, t2_0, t2_1, g0, g1, item0, item1, out0, nout; long long wblocks; };

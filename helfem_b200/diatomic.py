@@ -86,6 +86,11 @@ class DiatomicBasis:
         check(lib().hfb200_chan_exchange_stats(self.context(), ctypes.byref(items), ctypes.byref(fl), ms))
         return items.value, fl.value, list(ms)
 
+    def exchange_batches(self):
+        n = ctypes.c_int()
+        check(lib().hfb200_chan_exchange_batches(self.context(), ctypes.byref(n)))
+        return n.value
+
     def set_profile(self, on=True):
         check(lib().hfb200_chan_set_profile(self.context(), int(bool(on))))
 

@@ -158,6 +158,7 @@ int hfb200_chan_dim(hfb200_ctx* ctx, int* ndim);
 int hfb200_chan_coulomb_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dJ, int ldj, void* stream);
 int hfb200_chan_exchange_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dK, int ldk, void* stream);
 int hfb200_chan_exchange_stats(hfb200_ctx* ctx, long long* items, double* x3_flops, double* stage_ms /* [5] or NULL */);
+int hfb200_chan_exchange_batches(hfb200_ctx* ctx, int* nbatches); /* family batches of the last exchange call (5 launches each) */
 int hfb200_chan_set_profile(hfb200_ctx* ctx, int on); /* per-stage CUDA-event timing of exchange (mask, x1..x4) */
 
 /* ------------------------------------------------------------------------------------------
