@@ -46,6 +46,11 @@ WORKLOADS = {
                         desc="diatomic N2, lmax 12, mmax 3, 5 elements (half-size version of configs[3])"),
     "n2_hf_l4m1": dict(kind="diatomic", Z1=7, Z2=7, Rbond=2.068, lmax=4, mmax=1, nelem=3, nnodes=10, primbas=4,
                        desc="diatomic N2, lmax 4, mmax 1, 3 elements (small case the CPU oracle finishes in seconds)"),
+    # product-grid DFT of the diatomic program (configs[3]b in SURVEY 8: the 2-D prolate grid), first correct version
+    "n2_pbe_grid_l6m2": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=6, mmax=2, nelem=3, nnodes=10, primbas=4, x=101, c=130,
+                             desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 6, mmax 2, 3 elements, ldft 4 lmax+12, mdft 4 mmax+5"),
+    "n2_pbe_grid_l2m1": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=2, mmax=1, nelem=2, nnodes=5, primbas=4, x=101, c=130,
+                             desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 2, mmax 1 (oracle-sized)"),
     "ne_pbe_small": dict(Z=10, primbas=4, nnodes=15, nelem=5, taylor=-1, lmax=2, x=101, c=130, nspin=1,
                          desc="small smoke case"),
 }
@@ -635,6 +640,59 @@ def run_chan(args, w, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_grid2d(args, w, rank, world, local_rank):
+    """DFTGrid::eval_Fxc of the diatomic program through the host mirror class (dense host matrices in and out)."""
+    import torch
+    import helfem_b200 as hb
+    if not torch.cuda.is_available() or hb.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: helfem_b200 has no CPU fallback")
+    from grid2d_cases import diatomic_density
+    b = hb.DiatomicBasis(w["Z1"], w["Z2"], w["Rbond"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"],
+                         lmax=w["lmax"], mmax=w["mmax"], device=local_rank)
+    lang, mang = 4 * w["lmax"] + 12, 4 * w["mmax"] + 5  # diatomic/main.cpp:417,425
+    g = hb.DiatomicDFTGrid(b, lang, mang)
+    n = b.nbf
+    C = chan_orbitals(b, "diatomic", rank)
+    pure = b.pure_indices()
+    P = np.asfortranarray(2.0 * C[pure] @ C[pure].T)
+    for _ in range(max(args.warmup, 3)):
+        H, exc, nel, ekin = g.eval_Fxc(w["x"], w["c"], P)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        H, exc, nel, ekin = g.eval_Fxc(w["x"], w["c"], P)
+    t = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop()
+    if args.kernels_only:
+        print(json.dumps({"kernels_only": True, "ms_per_step": 1e3 * t}), flush=True)
+        return
+    cpu = None
+    if n <= 400:
+        import oracle
+        oracle.lib().oracle_set_num_threads(host_threads())
+        tabs = [b.radial(e) for e in range(b.nel)]
+        o = oracle.Grid2DOracle(1, b.lval, b.mval, b.first, b.last, [q[0] for q in tabs], [q[1] for q in tabs],
+                                [q[2] for q in tabs], [q[3] for q in tabs], lang, mang, Rhalf=b.Rhalf, pure=pure)
+        t0 = time.perf_counter()
+        Ho, exco, nelo, ekino = o.eval_fxc(w["x"], w["c"], P)
+        tc = time.perf_counter() - t0
+        cpu = {"value": 1.0 / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
+               "sample": "1 eval_Fxc of the same workload", "max_dH": float(np.max(np.abs(H - Ho))), "dExc": float(abs(exc - exco))}
+    line = {"metric": "fock_builds_per_sec", "value": 1.0 / t, "unit": "builds/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "operators": "eval_Fxc (PBE) restricted, dense host matrices",
+                       "nbf": n, "nang": int(b.nang), "nrad": int(b.nrad), "angular_points": lang * mang},
+            "roofline": None, "roofline_note": "first correct version of the product-grid kernels (DESIGN.md section 7): no per-kernel "
+                                               "roofline claimed yet; kernel shares in the committed launch list",
+            "cpu_baseline": cpu,
+            "e2e": {"value": 1.0 / t, "unit": "builds/s", "h2d_bytes_per_step": n * n * 8, "d2h_bytes_per_step": n * n * 8,
+                    "api": "diatomic::DFTGrid::eval_Fxc mirror on dense host matrices"},
+            "gpu_launches": None, "clocks": clocks, "Exc": exc, "Nel": nel}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -652,6 +710,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     w = WORKLOADS[args.workload]
+    if w.get("kind") == "grid2d":
+        if rank == 0 and args.impl != "reference":
+            run_grid2d(args, w, rank, world, local_rank)
+        return
     if w.get("kind") in ("atomic", "diatomic"):
         if args.impl == "reference":
             if rank == 0:
