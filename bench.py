@@ -502,9 +502,9 @@ def run_chan(args, w, rank, world, local_rank):
             b.exchange_device(dP.data_ptr(), dK.data_ptr(), n, sh)
         if sharded:  # NCCL moves the non-zero angular blocks only
             if J:
-                shard_mod.allreduce_blocksparse_(dJ, b.nang, b.nrad)
+                shard_mod.allreduce_blocksparse_(dJ, b.nang, b.nrad, pattern_key="J of the bench density")
             if K:
-                shard_mod.allreduce_blocksparse_(dK, b.nang, b.nrad)
+                shard_mod.allreduce_blocksparse_(dK, b.nang, b.nrad, pattern_key="K of the bench density")
 
     def barrier():
         if dist is not None:

@@ -57,21 +57,33 @@ def allreduce_operator(M, group=None, device=None):
     return np.asfortranarray(out.T) if fortran else out
 
 
-def allreduce_blocksparse_(dM, nang, nrad, group=None):
+_block_cache = {}
+
+
+def allreduce_blocksparse_(dM, nang, nrad, group=None, pattern_key=None):
     """In-place sum over the ranks of a DEVICE-resident dense operator (torch tensor, (nang*nrad)^2) whose angular
     blocks are mostly zero (a linear molecule / an atom only populates the m-diagonal blocks: 1/13 of the matrix at
     lmax 24, mmax 6).  The ranks agree on the union of their non-zero blocks (one all-reduce of a nang^2 byte mask),
     pack those blocks contiguously, all-reduce the packed buffer and scatter it back: NCCL moves the non-zero
-    blocks only.  Exact: blocks outside the union are zero on every rank."""
+    blocks only.  Exact: blocks outside the union are zero on every rank.
+    pattern_key: the block pattern of an operator depends only on the block pattern of the density it was built from;
+    a caller that knows the density pattern is unchanged (an SCF after its first iteration) passes the same hashable
+    key again and the union computed for it is reused instead of scanning the matrix."""
     import torch
     import torch.distributed as dist
 
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return dM
     M4 = dM.view(nang, nrad, nang, nrad)
-    mask = (M4.abs().amax(dim=(1, 3)) > 0).to(torch.uint8)
-    dist.all_reduce(mask, op=dist.ReduceOp.MAX, group=group)
-    idx = mask.nonzero(as_tuple=True)
+    ck = (pattern_key, nang, nrad, dM.device) if pattern_key is not None else None
+    if ck is not None and ck in _block_cache:
+        idx = _block_cache[ck]
+    else:
+        mask = ((M4.amax(dim=(1, 3)) != 0) | (M4.amin(dim=(1, 3)) != 0)).to(torch.uint8)
+        dist.all_reduce(mask, op=dist.ReduceOp.MAX, group=group)
+        idx = mask.nonzero(as_tuple=True)
+        if ck is not None:
+            _block_cache[ck] = idx
     if idx[0].numel() == 0:
         return dM
     if idx[0].numel() * 2 > nang * nang:  # dense enough: one plain all-reduce
