@@ -377,9 +377,12 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
             a[mi] = (mt < MT) ? __ldg(A + ((size_t)mt * KS + ks) * 32) : 0.0;
           }
 #pragma unroll
-          for (int mi = 0; mi < 4; mi++)
+          for (int mi = 0; mi < 4; mi++) {
+            if (mt0 + warp + 8 * mi < MT) {  // warp-uniform: a missing m-tile (np2 = 225: 29 tiles on 32 slots) costs no DMMA
 #pragma unroll
-            for (int nt = 0; nt < NTN; nt++) dmma(acc[mi][nt][0], acc[mi][nt][1], a[mi], b[nt]);
+              for (int nt = 0; nt < NTN; nt++) dmma(acc[mi][nt][0], acc[mi][nt][1], a[mi], b[nt]);
+            }
+          }
         }
       }
 #pragma unroll

@@ -96,3 +96,14 @@ def test_atomic_missing_tei_is_logic_error(native):
     b = hb.AtomicBasis(Z=2, nelem=2, nnodes=6, lmax=0, mmax=0)
     with pytest.raises(ValueError):
         b.coulomb(np.zeros((b.nbf, b.nbf)))
+
+
+def test_atomic_nonsymmetric_density(native):
+    """coulomb / exchange are linear in an arbitrary (not necessarily symmetric) matrix, as in the reference."""
+    b, o, P = setup_case("ne_l2m2")
+    n = b.nbf
+    A = np.asfortranarray(P + 0.2 * np.max(np.abs(P)) * np.triu(splitmix64(n * n, seed=78).reshape(n, n), 1))
+    J, Jo = b.coulomb(A), o.coulomb(A)
+    K, Ko = b.exchange(A), o.exchange(A)
+    assert np.max(np.abs(J - Jo)) <= tol(Jo), np.max(np.abs(J - Jo))
+    assert np.max(np.abs(K - Ko)) <= tol(Ko), np.max(np.abs(K - Ko))

@@ -164,3 +164,23 @@ def test_diatomic_midsize_properties(native):
     assert np.max(np.abs(Jd - J2)) <= 1e-12 * max(1.0, np.max(np.abs(J2)))
     items, flops, _ = b.exchange_stats()
     assert items > 0 and flops > 0
+
+
+def test_diatomic_nonsymmetric_density_and_size_errors(native):
+    """The operators are linear maps of ANY matrix (the reference never symmetrises P): parity for a non-symmetric
+    input; a matrix of the wrong size raises like the reference's size check (diatomic/basis.cpp:1735-1741)."""
+    b, o, P = setup_case("n2_l2m1")
+    n = b.nbf
+    A = np.asfortranarray(P + 0.3 * np.triu(splitmix64(n * n, seed=77).reshape(n, n), 1))
+    assert np.max(np.abs(A - A.T)) > 1e-3
+    J, Jo = b.coulomb(A), o.coulomb(A)
+    K, Ko = b.exchange(A), o.exchange(A)
+    assert np.max(np.abs(J - Jo)) <= tol(Jo) and np.max(np.abs(K - Ko)) <= tol(Ko)
+    import ctypes
+    import helfem_b200 as hb
+    bad = np.zeros((n - 1, n - 1), order="F")
+    out = np.zeros((n - 1, n - 1), order="F")
+    # the flat harness entry point takes bare pointers, so drive the C ABI's own leading-dimension check
+    rc = hb.lib().hfb200_diatomic_coulomb(b.context(), bad.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), n - 1,
+                                           out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), n - 1)
+    assert rc != 0 and b"expected size" in hb.lib().hfb200_last_error()
