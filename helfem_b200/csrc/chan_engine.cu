@@ -684,7 +684,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     q.fam_c0 = prm.fam_c0; q.fam_fac = dFamFac; q.items = (const int2*)dItems.p; q.item_fam = (const int*)dItemFam.p;
     q.wbase = (const long long*)dWbase.p; q.wbits = (const unsigned long long*)dWbits.p; q.nw = (nang + 63) / 64;
     const int ntl = (prm.np + 7) / 8, NI = x3_ni;
-    const size_t ybytes = (size_t)8 * 8 * ntl * (8 * ntl + 1) * sizeof(double);
+    const size_t ybytes = (size_t)8 * 8 * ntl * ((8 * ntl + 15) / 16 * 16 + 4) * sizeof(double);  // per-warp Y tiles of x3 (pairs)
     const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
     if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 255) / 256);

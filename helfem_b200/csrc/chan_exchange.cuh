@@ -402,7 +402,8 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
     // ---------------- different elements: Ksub = sum_ab iint^a . Rsub^{ab} . (jint^b)^T ----------------
     // A warp owns the items n = warp, warp + 8, ...; the fragments of iint / jint are loaded once per (a,b) and the
     // accumulators of all its items stay in registers (small element blocks), or one item at a time (large ones).
-    constexpr int LDY = 8 * NTL + 1;
+    // row stride = 4 (mod 16) doubles: the A-fragment reads of step 2 (row gid, column 4 ks + t4) are bank-conflict free
+    constexpr int LDY = (8 * NTL + 15) / 16 * 16 + 4;
     constexpr int NIT = (NTL <= 2 && NI >= 16) ? 2 : 1;  // items a warp carries through the ab loop together
     double* Y = sm + warp * (8 * NTL * LDY);
     const bool lower = ie > je;
