@@ -1,5 +1,6 @@
 set -x
-timeout 900 python -m pytest tests/test_diatomic_gpu.py tests/test_atomic_gpu.py -m gpu -x -q > gpurun_out/v_tests.log 2>&1; tail -5 gpurun_out/v_tests.log
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3
-timeout 600 python bench.py --workload n2_hf_l12m3 --steps 3 --kernels-only > gpurun_out/v_l12m3.json 2> gpurun_out/v_l12m3.err; cat gpurun_out/v_l12m3.json
-timeout 900 python bench.py --workload n2_hf_cfg4 --steps 2 --kernels-only > gpurun_out/v_cfg4.json 2> gpurun_out/v_cfg4.err; cat gpurun_out/v_cfg4.json
+python -m pytest tests -m gpu -x -q > gpurun_out/final_gpu_tests.log 2>&1; tail -3 gpurun_out/final_gpu_tests.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/final_smoke.log 2>&1; tail -3 gpurun_out/final_smoke.log
+python bench.py > gpurun_out/final_bench_cfg2.json 2> gpurun_out/final_bench_cfg2.err; tail -c 300 gpurun_out/final_bench_cfg2.err; cut -c1-400 gpurun_out/final_bench_cfg2.json
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/final_bench_ref.json 2> gpurun_out/final_bench_ref.err; cut -c1-300 gpurun_out/final_bench_ref.json
+python bench.py --workload n2_hf_cfg4 --steps 3 > gpurun_out/final_bench_cfg4.json 2> gpurun_out/final_bench_cfg4.err; tail -c 300 gpurun_out/final_bench_cfg4.err; cut -c1-300 gpurun_out/final_bench_cfg4.json
