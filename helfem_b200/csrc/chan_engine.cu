@@ -156,6 +156,21 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     }
   }
   if ((rc = up(this, &xprm.first, first)) || (rc = up(this, &xprm.npe, npe)) || (rc = up(this, &xprm.elem_of, elem_of))) return rc;
+  {
+    // where the radial pair (A,B) lives inside the element-pair sub-blocks of Rsub (x2 scatter)
+    std::vector<int4> eltab((size_t)nrad * nrad);
+    for (int B = 0; B < nrad; B++)
+      for (int A = 0; A < nrad; A++) {
+        int o[4];
+        for (int x = 0; x < 2; x++)
+          for (int y = 0; y < 2; y++) {
+            const int ie = elem_of[2 * A + x], je = elem_of[2 * B + y];
+            o[2 * x + y] = (ie < 0 || je < 0) ? -1 : (ie * nel + je) * np2 + (A - first[ie]) + (B - first[je]) * np;
+          }
+        eltab[A + (size_t)B * nrad] = make_int4(o[0], o[1], o[2], o[3]);
+      }
+    if ((rc = up(this, &xprm.eltab, eltab))) return rc;
+  }
   fam_fac = S.fac;
   // disjoint factors, zero padded squares
   {
@@ -647,6 +662,7 @@ int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cud
 int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ldkm, cudaStream_t st) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
   const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
+  if ((size_t)ldpm * (size_t)ntot >= ((size_t)1 << 32)) { set_error("exchange: density matrix too large for 32-bit block offsets"); return HFB200_EINVAL; }
   const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
   int rc;
   HFB_CUDA_OK(cudaMemset2DAsync(dKm, (size_t)ldkm * sizeof(double), 0, (size_t)ntot * sizeof(double), ntot, st));
@@ -688,27 +704,36 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
     if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 255) / 256);
-    const size_t smem1 = (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_T * sizeof(long long) +
-                         (size_t)(2 * nang + CHX_UMAX) * sizeof(int) + (size_t)nang;
-    const size_t smem2 = (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_UMAX * sizeof(size_t) + (size_t)2 * nch_max * nang * sizeof(int);
+    static const bool x1_scalar = getenv("HFB200_X1_SCALAR") != nullptr;  // A/B switch: the scalar (DFMA) variant of x1
+    const size_t smem1 = x1_scalar ? (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_T * sizeof(long long) +
+                                         (size_t)(2 * nang + CHX_UMAX) * sizeof(int) + (size_t)nang
+                                   : (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + CHX_T * sizeof(long long) +
+                                         (size_t)(2 * nang + 2 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)nang;
+    static const bool x2_scalar = getenv("HFB200_X2_SCALAR") != nullptr;  // A/B switch: the scalar (DFMA) variant of x2
+    const size_t smem2 = (size_t)(x2_scalar ? CHX_UMAX * CHX_T * 2 : 2 * CHX_UMAX * CHX_LDC) * sizeof(double) + CHX_UMAX * sizeof(size_t) +
+                         (size_t)2 * nch_max * nang * sizeof(int) + (x2_scalar ? 0 : 8 + (size_t)8 * CHX_X2_STAGES * 128 * sizeof(double));
     if (smem1 > 48 * 1024 || smem2 > 48 * 1024) {
       if (smem1 > 227 * 1024 || smem2 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
       HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
       HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     }
     for (const XBatch& B : batches) {
       q.item0 = B.item0;
       const int nt1 = B.t1_1 - B.t1_0, nt2 = B.t2_1 - B.t2_0, ng = B.g1 - B.g0;
       if (nt1 > 0 && B.wblocks > 0) {
         tick(1, true);
-        chan_x1_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
+        if (x1_scalar) chan_x1_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
+        else chan_x1_mma_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
         HFB_CUDA_OK(cudaGetLastError());
         tick(1, false);
       }
       if (nt2 == 0) continue;
       tick(2, true);
       const int ny2 = std::max(1, std::min(nchunk, 2368 / std::max(nt2, 1)));
-      chan_x2_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
+      if (x2_scalar) chan_x2_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
+      else chan_x2_mma_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
       HFB_CUDA_OK(cudaGetLastError());
       tick(2, false);
       tick(3, true);

@@ -1,6 +1,8 @@
 set -x
-python -m pytest tests -m gpu -x -q > gpurun_out/final_gpu_tests.log 2>&1; tail -3 gpurun_out/final_gpu_tests.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/final_smoke.log 2>&1; tail -3 gpurun_out/final_smoke.log
-python bench.py > gpurun_out/final_bench_cfg2.json 2> gpurun_out/final_bench_cfg2.err; tail -c 300 gpurun_out/final_bench_cfg2.err; cut -c1-400 gpurun_out/final_bench_cfg2.json
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/final_bench_ref.json 2> gpurun_out/final_bench_ref.err; cut -c1-300 gpurun_out/final_bench_ref.json
-python bench.py --workload n2_hf_cfg4 --steps 3 > gpurun_out/final_bench_cfg4.json 2> gpurun_out/final_bench_cfg4.err; tail -c 300 gpurun_out/final_bench_cfg4.err; cut -c1-300 gpurun_out/final_bench_cfg4.json
+python -m pytest tests/test_diatomic_gpu.py tests/test_atomic_gpu.py -m gpu -x -q > gpurun_out/x_tests.log 2>&1; tail -3 gpurun_out/x_tests.log
+run() { python bench.py --workload n2_hf_l12m3 --steps 5 > gpurun_out/x_l12m3_$1.json 2> gpurun_out/x_l12m3_$1.err; tail -c 300 gpurun_out/x_l12m3_$1.err; python -c "
+import json;d=json.load(open('gpurun_out/x_l12m3_$1.json'));print('$1', d['ms_per_step'], d['roofline'].get('exchange_stage_ms'))"; }
+run mma
+python bench.py --workload n2_hf_cfg4 --steps 3 > gpurun_out/x_cfg4.json 2> gpurun_out/x_cfg4.err; tail -c 300 gpurun_out/x_cfg4.err; python -c "
+import json;d=json.load(open('gpurun_out/x_cfg4.json'));print(d['ms_per_step'], d['roofline'].get('exchange_stage_ms'))"
+ncu --set full --clock-control none --import-source on -k "regex:chan_x2_mma" -c 1 -s 3 -o gpurun_out/x_chan_x2_mma -f python bench.py --kernels-only --workload n2_hf_l12m3 --steps 1 --warmup 1 > gpurun_out/ncu_x2.log 2>&1; tail -1 gpurun_out/ncu_x2.log
