@@ -161,11 +161,11 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     std::vector<int4> eltab((size_t)nrad * nrad);
     for (int B = 0; B < nrad; B++)
       for (int A = 0; A < nrad; A++) {
-        int o[4];
+        int o[4] = {-1, -1, -1, -1}, no = 0;  // valid offsets first
         for (int x = 0; x < 2; x++)
           for (int y = 0; y < 2; y++) {
             const int ie = elem_of[2 * A + x], je = elem_of[2 * B + y];
-            o[2 * x + y] = (ie < 0 || je < 0) ? -1 : (ie * nel + je) * np2 + (A - first[ie]) + (B - first[je]) * np;
+            if (ie >= 0 && je >= 0) o[no++] = (ie * nel + je) * np2 + (A - first[ie]) + (B - first[je]) * np;
           }
         eltab[A + (size_t)B * nrad] = make_int4(o[0], o[1], o[2], o[3]);
       }
@@ -390,7 +390,7 @@ int ChanEngine::build_items(const unsigned char* nz) {
   // workspace budgets of a batch (HFB200_X_WCAP_MB / HFB200_X_RCAP_MB override them: the tests force many small batches)
   size_t wcap_bytes = 16ull << 30, rcap_bytes = 12ull << 30;
   if (const char* e = getenv("HFB200_X_WCAP_MB")) wcap_bytes = std::max<size_t>(1, (size_t)atoll(e)) << 20;
-  if (const char* e = getenv("HFB200_X_RCAP_MB")) rcap_bytes = std::max<size_t>(1, (size_t)atoll(e)) << 20;
+  if (const char* e = getenv("HFB200_X_RCAP_MB")) rcap_bytes = std::min<size_t>(std::max<size_t>(1, (size_t)atoll(e)) << 20, 30ull << 30);
   const long long wcap = (long long)(wcap_bytes / ((size_t)st * nrad2 * sizeof(double)));
   const long long icap = (long long)(rcap_bytes / ((size_t)st * st * nel * nel * np2 * sizeof(double)));
   std::vector<int2> items, tiles2, groups;
@@ -688,6 +688,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
   last_items = total_items;
   if (total_items > 0) {
     const size_t need_r = (size_t)max_batch_items * st2 * nel * nel * np2;
+    if (need_r >= ((size_t)1 << 32)) { set_error("exchange: a family batch of %d output blocks exceeds the 32-bit offsets of its workspace", max_batch_items); return HFB200_EINVAL; }
     if (need_r > dRsub.cap) {
       if ((rc = dRsub.reserve(need_r))) return rc;
       HFB_CUDA_OK(cudaMemsetAsync(dRsub.p, 0, need_r * sizeof(double), st));  // padding positions stay zero for good
@@ -704,19 +705,13 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
     if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 255) / 256);
-    static const bool x1_scalar = getenv("HFB200_X1_SCALAR") != nullptr;  // A/B switch: the scalar (DFMA) variant of x1
-    const size_t smem1 = x1_scalar ? (size_t)CHX_UMAX * CHX_T * 2 * sizeof(double) + CHX_T * sizeof(long long) +
-                                         (size_t)(2 * nang + CHX_UMAX) * sizeof(int) + (size_t)nang
-                                   : (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + CHX_T * sizeof(long long) +
-                                         (size_t)(2 * nang + 2 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)nang;
-    static const bool x2_scalar = getenv("HFB200_X2_SCALAR") != nullptr;  // A/B switch: the scalar (DFMA) variant of x2
-    const size_t smem2 = (size_t)(x2_scalar ? CHX_UMAX * CHX_T * 2 : 2 * CHX_UMAX * CHX_LDC) * sizeof(double) + CHX_UMAX * sizeof(size_t) +
-                         (size_t)2 * nch_max * nang * sizeof(int) + (x2_scalar ? 0 : 8 + (size_t)8 * CHX_X2_STAGES * 128 * sizeof(double));
+    const size_t smem1 = (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + CHX_T * sizeof(long long) +
+                         (size_t)(2 * nang + 2 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)nang;
+    const size_t smem2 = (size_t)2 * CHX_UMAX * CHX_LDC * sizeof(double) + CHX_UMAX * sizeof(size_t) + (size_t)2 * nch_max * nang * sizeof(int) +
+                         (size_t)8 * CHX_X2_STAGES * 128 * sizeof(double);
     if (smem1 > 48 * 1024 || smem2 > 48 * 1024) {
       if (smem1 > 227 * 1024 || smem2 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
-      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
       HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
       HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     }
     for (const XBatch& B : batches) {
@@ -724,16 +719,14 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       const int nt1 = B.t1_1 - B.t1_0, nt2 = B.t2_1 - B.t2_0, ng = B.g1 - B.g0;
       if (nt1 > 0 && B.wblocks > 0) {
         tick(1, true);
-        if (x1_scalar) chan_x1_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
-        else chan_x1_mma_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
+        chan_x1_mma_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
         HFB_CUDA_OK(cudaGetLastError());
         tick(1, false);
       }
       if (nt2 == 0) continue;
       tick(2, true);
       const int ny2 = std::max(1, std::min(nchunk, 2368 / std::max(nt2, 1)));
-      if (x2_scalar) chan_x2_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
-      else chan_x2_mma_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
+      chan_x2_mma_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
       HFB_CUDA_OK(cudaGetLastError());
       tick(2, false);
       tick(3, true);

@@ -92,7 +92,13 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
 // coefficient table, and streams every input block ONCE for all its rows instead of once per row.
 constexpr int CHX_T = 8;      // rows (x1: j, x2: k) per tile
 constexpr int CHX_UMAX = 64;  // union slots per pass
-constexpr int CHX_X2_STAGES = 4;  // k-steps in flight per warp in the x2 stream (cp.async ring)
+#ifndef HFB_X2_STAGES
+#define HFB_X2_STAGES 6
+#endif
+#ifndef HFB_X2_MINB
+#define HFB_X2_MINB 2
+#endif
+constexpr int CHX_X2_STAGES = HFB_X2_STAGES;  // k-steps in flight per warp in the x2 stream (cp.async ring)
 constexpr int CHX_LDC = 12;   // row stride of the DMMA coefficient tables: the 4 x 8 fragment read of a half-warp hits 32 distinct banks
 
 // slots for the flagged entries of dom[0..n): -1 = absent, 0 = present on entry; slot number on exit.  Warp 0 only.
@@ -124,104 +130,8 @@ __device__ __forceinline__ long long chx_wblock(const ChanXParams& prm, int row,
 }
 
 // x1.  grid (tiles of the batch, l chunks), 256 threads.  tiles: [c, nj, j_0 .. j_{T-1}] per tile.
-// dynamic smem: coef[UMAX][T][2] doubles | wblk[T] long long | ulist[nang] | dom[nang] | act[UMAX] ints | done[nang] bytes
-static __global__ void __launch_bounds__(256) chan_x1_kernel(ChanXParams prm, const int* tiles) {
-  extern __shared__ double sm[];
-  __shared__ int s_cnt, s_na;
-  const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack;
-  double* coef = sm;
-  long long* wblk = reinterpret_cast<long long*>(coef + CHX_UMAX * CHX_T * 2);
-  int* ulist = reinterpret_cast<int*>(wblk + CHX_T);
-  int* dom = ulist + nang;
-  int* act = dom + nang;
-  unsigned char* done = reinterpret_cast<unsigned char*>(act + CHX_UMAX);
-  const int* T = tiles + (size_t)blockIdx.x * (2 + CHX_T);
-  const int c = T[0], nj = T[1];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int q = tid; q < nang; q += 256) { dom[q] = -1; done[q] = 0; }
-  __syncthreads();
-  for (int jj = 0; jj < nj; jj++) {
-    const int row = c * nang + T[2 + jj];
-    for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) dom[prm.row_i[e]] = 0;
-  }
-  __syncthreads();
-  if (warp == 0) {
-    const int n = chx_scan_slots(dom, ulist, nang, lane);
-    if (lane == 0) s_cnt = n;
-  }
-  __syncthreads();
-  const int cnt = s_cnt;
-  for (int ubase = 0; ubase < cnt; ubase += CHX_UMAX) {
-    const int nu = min(CHX_UMAX, cnt - ubase);
-    for (int q = tid; q < nu * CHX_T * 2; q += 256) coef[q] = 0.0;
-    __syncthreads();
-    for (int jj = 0; jj < nj; jj++) {
-      const int row = c * nang + T[2 + jj];
-      for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
-        const int sl = dom[prm.row_i[e]] - ubase;
-        if (sl >= 0 && sl < nu) {
-          coef[(sl * CHX_T + jj) * 2] = prm.row_coef[2 * e];
-          coef[(sl * CHX_T + jj) * 2 + 1] = prm.row_coef[2 * e + 1];
-        }
-      }
-    }
-    for (int l = blockIdx.y; l < nang; l += gridDim.y) {
-      __syncthreads();  // coef complete / previous l done with act and wblk
-      // compact list of the partners whose P block is non-zero (warp 0: ballot scan), so that the stream loop is branch free
-      if (warp == 0) {
-        int base = 0;
-        for (int q0 = 0; q0 < nu; q0 += 32) {
-          const int q = q0 + lane;
-          const bool f = q < nu && prm.nzP[(size_t)ulist[ubase + q] * nang + l];
-          const unsigned mk = __ballot_sync(0xffffffffu, f);
-          if (f) act[base + __popc(mk & ((1u << lane) - 1u))] = q;
-          base += __popc(mk);
-        }
-        if (lane == 0) s_na = base;
-      }
-      if (tid < CHX_T) wblk[tid] = tid < nj ? chx_wblock(prm, c * nang + T[2 + tid], l) : -1;
-      __syncthreads();
-      const int na = s_na;
-      if (na == 0) continue;  // block-uniform
-      const bool prev = done[l] != 0;  // an earlier pass already wrote the blocks of this l
-      for (int k = tid; k < nrad2; k += 256) {
-        const int A = k % nrad, B = k / nrad;
-        const double* src = prm.P + A + (size_t)(l * nrad + B) * prm.ldp;
-        double acc[CHX_T][2];
-#pragma unroll
-        for (int jj = 0; jj < CHX_T; jj++) { acc[jj][0] = 0.0; acc[jj][1] = 0.0; }
-#pragma unroll 4
-        for (int v = 0; v < na; v++) {
-          const int u = act[v];
-          const double p = src[(size_t)ulist[ubase + u] * nrad];
-          const double2* cf = reinterpret_cast<const double2*>(coef + u * CHX_T * 2);
-#pragma unroll
-          for (int jj = 0; jj < CHX_T; jj++) {
-            const double2 cc = cf[jj];
-            acc[jj][0] = fma(cc.x, p, acc[jj][0]);
-            acc[jj][1] = fma(cc.y, p, acc[jj][1]);
-          }
-        }
-#pragma unroll
-        for (int jj = 0; jj < CHX_T; jj++) {
-          const long long wb = wblk[jj];
-          if (wb < 0) continue;  // l is not in the set of this row (its partners' blocks are all zero): nothing stored
-          double* W0 = prm.W + (size_t)wb * st * nrad2 + k;
-          if (prev) { acc[jj][0] += W0[0]; if (st == 2) acc[jj][1] += W0[nrad2]; }
-          W0[0] = acc[jj][0];
-          if (st == 2) W0[nrad2] = acc[jj][1];
-        }
-      }
-      if (tid == 0) done[l] = 1;
-    }
-    __syncthreads();
-  }
-  // blocks of the rows' sets that no pass reached cannot exist: l in L(c,j) means an active partner in some pass
-}
-
-// x1 on the FP64 tensor pipe: W_{(c,j)}[l][k] = sum_v coef[u_v][j][b] P_{i_v l}[k] as a GEMM with M = the radial pairs k (A operand read from
+// On the FP64 tensor pipe: W_{(c,j)}[l][k] = sum_v coef[u_v][j][b] P_{i_v l}[k] as a GEMM with M = the radial pairs k (A operand read from
 // the dense P in fragment order), N = the tile's <= 8 rows j (one n-tile per stack half b), K = the active partners of this l.
-// Same grid, tile list and pass structure as chan_x1_kernel.
 // dynamic smem: coef[2][UMAX+1][CHX_LDC] doubles (slot UMAX stays zero: padding) | wblk[T] long long | ulist[nang] | dom[nang] |
 //               act[UMAX+4] | actl[UMAX+4] ints | done[nang] bytes
 static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams prm, const int* tiles) {
@@ -338,128 +248,15 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
   }
 }
 
-// x2.  grid (tiles of the batch, element chunks, stack half a), 256 threads.  A tile = <= CHX_T consecutive items (j, k_0..) of one family, one j.
-// dynamic smem: coef[UMAX][T][2] doubles | woff[UMAX] (size_t) | ulist[D] | dom[D] ints, D = nch_max*nang
-static __global__ void __launch_bounds__(256, 3) chan_x2_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
-  extern __shared__ double sm[];
-  __shared__ int s_cnt;
-  const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack, st2 = st * st;
-  double* coef = sm;
-  size_t* woff = reinterpret_cast<size_t*>(coef + CHX_UMAX * CHX_T * 2);
-  int* ulist = reinterpret_cast<int*>(woff + CHX_UMAX);
-  int* dom = ulist + nch_max * nang;
-  const int it0 = tiles[blockIdx.x].x, nk = tiles[blockIdx.x].y;
-  const int j = prm.items[it0].x, r = prm.item_fam[it0];
-  const int c0 = prm.fam_c0[r], nch = prm.fam_c0[r + 1] - c0, D = nch * nang;
-  const double fac = prm.fam_fac[r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int q = tid; q < D; q += 256) dom[q] = -1;
-  __syncthreads();
-  for (int kk = 0; kk < nk; kk++) {
-    const int k = prm.items[it0 + kk].y;
-    for (int cl = 0; cl < nch; cl++) {
-      const int row = (c0 + cl) * nang + k, jrow = (c0 + cl) * nang + j;
-      const unsigned long long* bits = prm.wbits + (size_t)jrow * prm.nw;
-      for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
-        const int l = prm.row_i[e];
-        if ((bits[l >> 6] >> (l & 63)) & 1ull) dom[cl * nang + l] = 0;
-      }
-    }
-  }
-  __syncthreads();
-  if (warp == 0) {
-    const int n = chx_scan_slots(dom, ulist, D, lane);
-    if (lane == 0) s_cnt = n;
-  }
-  __syncthreads();
-  const int cnt = s_cnt;
-  const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2;
-  const size_t istride = (size_t)st2 * nel2 * np2;
-  for (int ubase = 0; ubase < max(cnt, 1); ubase += CHX_UMAX) {  // cnt == 0: one pass that writes zeros
-    const int nu = max(0, min(CHX_UMAX, cnt - ubase));
-    const int nup = (nu + 3) & ~3;  // padded with zero coefficients: the stream loop has no serial remainder
-    __syncthreads();
-    for (int q = tid; q < nup * CHX_T * 2; q += 256) coef[q] = 0.0;
-    if (tid < nup) {
-      const int q = ulist[ubase + (tid < nu ? tid : 0)], cl = q / nang, l = q - cl * nang;
-      woff[tid] = (size_t)chx_wblock(prm, (c0 + cl) * nang + j, l) * st * nrad2;
-    }
-    __syncthreads();
-    for (int kk = 0; kk < nk; kk++) {
-      const int k = prm.items[it0 + kk].y;
-      for (int cl = 0; cl < nch; cl++) {
-        const int row = (c0 + cl) * nang + k;
-        for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
-          const int d = dom[cl * nang + prm.row_i[e]];
-          const int sl = d - ubase;
-          if (d >= 0 && sl >= 0 && sl < nu) {
-            coef[(sl * CHX_T + kk) * 2] = prm.row_coef[2 * e];
-            coef[(sl * CHX_T + kk) * 2 + 1] = prm.row_coef[2 * e + 1];
-          }
-        }
-      }
-    }
-    __syncthreads();
-    // one stack half a = blockIdx.z per CTA: 2 T accumulators per thread keep the register count low enough for
-    // three resident CTAs, and the u loop unrolled by 8 keeps eight independent loads in flight per thread
-    const int a = blockIdx.z;
-    for (int el = blockIdx.y * 256 + tid; el < nrad2; el += gridDim.y * 256) {
-      double acc[CHX_T][2];
-#pragma unroll
-      for (int kk = 0; kk < CHX_T; kk++) { acc[kk][0] = 0.0; acc[kk][1] = 0.0; }
-      const double* Wa = prm.W + (size_t)a * nrad2 + el;
-#pragma unroll 2
-      for (int u0 = 0; u0 < nup; u0 += 4) {
-        double w[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) w[i] = Wa[woff[u0 + i]];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const double2* cf = reinterpret_cast<const double2*>(coef + (u0 + i) * CHX_T * 2);
-#pragma unroll
-          for (int kk = 0; kk < CHX_T; kk++) {
-            const double2 cc = cf[kk];
-            acc[kk][0] = fma(cc.x, w[i], acc[kk][0]);  // b = 0
-            acc[kk][1] = fma(cc.y, w[i], acc[kk][1]);  // b = 1
-          }
-        }
-      }
-      // scatter into the element-pair sub-blocks (a radial function belongs to one or two elements)
-      const int A = el % nrad, B = el / nrad;
-      for (int x = 0; x < 2; x++) {
-        const int ie = prm.elem_of[2 * A + x];
-        if (ie < 0) continue;
-        for (int y = 0; y < 2; y++) {
-          const int je = prm.elem_of[2 * B + y];
-          if (je < 0) continue;
-          const size_t off = (size_t)(ie * nel + je) * np2 + (A - prm.first[ie]) + (B - prm.first[je]) * np;
-#pragma unroll
-          for (int kk = 0; kk < CHX_T; kk++) {
-            if (kk >= nk) break;
-            double* out = prm.Rsub + (size_t)(it0 - prm.item0 + kk) * istride + off;
-#pragma unroll
-            for (int b = 0; b < 2; b++) {
-              if (b < st) {
-                const double v = (a != b ? -fac : fac) * acc[kk][b];
-                if (ubase == 0) out[(size_t)(a * st + b) * nel2 * np2] = v;
-                else out[(size_t)(a * st + b) * nel2 * np2] += v;
-              }
-            }
-          }
-        }
-      }
-    }
-  }
-}
-
-// x2 on the FP64 tensor pipe.  R[el][(item, b)] = sum_u W_u[el] coef[u][item][b] is a GEMM with M = the radial pairs (A operand, streamed
+// x2.  grid (tiles of the batch, element chunks, stack half a), 256 threads.  A tile = <= CHX_T consecutive items (j, k_0..) of one family,
+// one j.  On the FP64 tensor pipe: R[el][(item, b)] = sum_u W_u[el] coef[u][item][b] is a GEMM with M = the radial pairs (A operand, streamed
 // from HBM directly in fragment order: lane (gid, t4) reads W_{u0+t4}[el0 + gid], 64-byte runs), N = the tile's <= 8 items (one n-tile per
-// stack half b; B operand = the coefficient table in shared memory), K = the union slots.  Against the scalar kernel above this removes
-// the 8 LDS.128 + 16 DFMA per streamed value: one DMMA pair per four values.  The accumulator layout (lane holds radial pair gid, items
+// stack half b; B operand = the coefficient table in shared memory), K = the union slots: one DMMA pair per four streamed values instead
+// of 8 LDS.128 + 16 DFMA per value.  The accumulator layout (lane holds radial pair gid, items
 // 2 t4, 2 t4 + 1) stores 64-byte runs per item, and the scatter offsets come from the precomputed eltab.
-// Same grid and tile list as chan_x2_kernel.  dynamic smem: coef[2][UMAX][CHX_LDC] doubles | woff[UMAX] (size_t) | ulist[D] | dom[D] ints |
+// dynamic smem: coef[2][UMAX][CHX_LDC] doubles | woff[UMAX] (size_t) | ulist[D] | dom[D] ints |
 //   stage[8 warps][CHX_X2_STAGES][4][32] doubles
-static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
+static __global__ void __launch_bounds__(256, HFB_X2_MINB) chan_x2_mma_kernel(ChanXParams prm, const int2* tiles, int nch_max) {
   extern __shared__ double sm[];
   __shared__ int s_cnt;
   const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack, st2 = st * st;
@@ -475,12 +272,12 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
   for (int q = tid; q < D; q += 256) dom[q] = -1;
   __syncthreads();
-  for (int kk = 0; kk < nk; kk++) {
+  for (int kk = warp; kk < nk; kk += 8) {  // one warp per item: the rows are short, the chains of dependent loads run side by side
     const int k = prm.items[it0 + kk].y;
     for (int cl = 0; cl < nch; cl++) {
       const int row = (c0 + cl) * nang + k, jrow = (c0 + cl) * nang + j;
       const unsigned long long* bits = prm.wbits + (size_t)jrow * prm.nw;
-      for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
+      for (int e = prm.rowptr[row] + lane; e < prm.rowptr[row + 1]; e += 32) {
         const int l = prm.row_i[e];
         if ((bits[l >> 6] >> (l & 63)) & 1ull) dom[cl * nang + l] = 0;
       }
@@ -495,7 +292,6 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
   const int cnt = s_cnt;
   const int nel = prm.nel, nel2 = nel * nel, np2 = prm.np2;
   const size_t istride = (size_t)st2 * nel2 * np2, bstride = (size_t)nel2 * np2;
-  const int a = blockIdx.z;
   for (int ubase = 0; ubase < max(cnt, 1); ubase += CHX_UMAX) {  // cnt == 0: one pass that writes zeros
     const int nu = max(0, min(CHX_UMAX, cnt - ubase));
     const int nup = (nu + 3) & ~3;  // k-steps of four slots; the padding slots keep zero coefficients
@@ -506,11 +302,11 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
       woff[tid] = (size_t)chx_wblock(prm, (c0 + cl) * nang + j, l) * st * nrad2;
     }
     __syncthreads();
-    for (int kk = 0; kk < nk; kk++) {
+    for (int kk = warp; kk < nk; kk += 8) {
       const int k = prm.items[it0 + kk].y;
       for (int cl = 0; cl < nch; cl++) {
         const int row = (c0 + cl) * nang + k;
-        for (int e = prm.rowptr[row] + tid; e < prm.rowptr[row + 1]; e += 256) {
+        for (int e = prm.rowptr[row] + lane; e < prm.rowptr[row + 1]; e += 32) {
           const int d = dom[cl * nang + prm.row_i[e]];
           const int sl = d - ubase;
           if (d >= 0 && sl >= 0 && sl < nu) {
@@ -521,10 +317,13 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
       }
     }
     __syncthreads();
-    const double* Wa = prm.W + (size_t)a * nrad2;
-    // output rows of this lane's two items, stack block (a, b = 0)
-    double* out0 = prm.Rsub + (size_t)(it0 - prm.item0 + 2 * t4) * istride + (size_t)(a * st) * bstride;
     const bool it_ok0 = 2 * t4 < nk, it_ok1 = 2 * t4 + 1 < nk;
+    for (int a = blockIdx.z; a < st; a += gridDim.z) {  // both stack halves reuse the tables built above
+    const double* Wa = prm.W + (size_t)a * nrad2;
+    // output rows of this lane's two items, stack block (a, b = 0), as 32-bit element offsets (the engine caps Rsub below 2^32 doubles)
+    const unsigned ob0 = (unsigned)((size_t)(it0 - prm.item0 + 2 * t4) * istride + (size_t)(a * st) * bstride);
+    const unsigned ist = (unsigned)istride, bst = (unsigned)bstride;
+    const double sg0 = (a != 0) ? -fac : fac, sg1 = (a != 1) ? -fac : fac;  // sign of the stack block (a, b)
     // The union of a tile is small (a few k-steps per radial tile), so the loop is a stream of short load -> DMMA -> store rounds.  The
     // fragments are therefore staged through a per-lane cp.async ring (CHX_X2_STAGES k-steps deep, each lane reads back exactly what it
     // copied: no barrier), with the producer running ahead ACROSS radial tiles, so that the loads of the next tiles are in flight during
@@ -536,14 +335,13 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
     int p_el = el_first, p_ks = 0, p_slot = 0;
     auto produce = [&]() {
       if (p_el < nrad2) {
+        // radial pairs past the end are clamped to the last one: their accumulator rows are never stored
         const int pg = p_el + gid;
-        const double* src = Wa + woff[4 * p_ks + t4] + pg;
+        const double* src = Wa + woff[4 * p_ks + t4];
 #pragma unroll
-        for (int mt = 0; mt < 4; mt++) {
-          const bool ok = pg + 8 * mt < nrad2;
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(stg_s + (unsigned)((p_slot * 4 + mt) * 256)),
-                       "l"(ok ? src + 8 * mt : Wa), "r"(ok ? 8 : 0) : "memory");
-        }
+        for (int mt = 0; mt < 4; mt++)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(stg_s + (unsigned)((p_slot * 4 + mt) * 256)),
+                       "l"(src + min(pg + 8 * mt, nrad2 - 1)) : "memory");
         if (++p_ks == ksn) { p_ks = 0; p_el += el_stride; }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -575,30 +373,27 @@ static __global__ void __launch_bounds__(256, 3) chan_x2_mma_kernel(ChanXParams 
         }
         c_slot = (c_slot + 1 == CHX_X2_STAGES) ? 0 : c_slot + 1;
       }
-      // scatter into the element-pair sub-blocks (a radial function belongs to one or two elements)
+      // scatter into the element-pair sub-blocks: a radial function belongs to one or two elements, so a pair has 1, 2 or 4 homes
+      // (eltab lists the valid offsets first); the loop is rolled, the common single-home case runs its body once
 #pragma unroll
       for (int mt = 0; mt < 4; mt++) {
-        const int offs[4] = {e4[mt].x, e4[mt].y, e4[mt].z, e4[mt].w};  // all -1 past the end
-#pragma unroll
-        for (int c = 0; c < 4; c++) {
-          if (offs[c] < 0) continue;
-#pragma unroll
-          for (int b = 0; b < 2; b++) {
-            if (b < st) {
-              const double sg = (a != b) ? -fac : fac;
-              double* o = out0 + (size_t)b * bstride + offs[c];
-              if (ubase == 0) {
-                if (it_ok0) o[0] = sg * acc[mt][b][0];
-                if (it_ok1) o[istride] = sg * acc[mt][b][1];
-              } else {
-                if (it_ok0) o[0] += sg * acc[mt][b][0];
-                if (it_ok1) o[istride] += sg * acc[mt][b][1];
-              }
-            }
+        int4 o4 = e4[mt];  // all -1 past the end
+        const double v00 = sg0 * acc[mt][0][0], v01 = sg0 * acc[mt][0][1], v10 = sg1 * acc[mt][1][0], v11 = sg1 * acc[mt][1][1];
+#pragma unroll 1
+        while (o4.x >= 0) {
+          const unsigned o = ob0 + (unsigned)o4.x;
+          if (ubase == 0) {
+            if (it_ok0) { prm.Rsub[o] = v00; if (st == 2) prm.Rsub[o + bst] = v10; }
+            if (it_ok1) { prm.Rsub[o + ist] = v01; if (st == 2) prm.Rsub[o + ist + bst] = v11; }
+          } else {
+            if (it_ok0) { prm.Rsub[o] += v00; if (st == 2) prm.Rsub[o + bst] += v10; }
+            if (it_ok1) { prm.Rsub[o + ist] += v01; if (st == 2) prm.Rsub[o + ist + bst] += v11; }
           }
+          o4 = make_int4(o4.y, o4.z, o4.w, -1);
         }
       }
     }
+    }  // a
   }
 }
 
