@@ -439,16 +439,24 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
         __syncthreads();
         const double* A = prm.teiK + ((((size_t)r * nel + ie) * st2 + ab) * MT) * KS * 32 + lane;
         const double* bs = sm + gid * LDK + t4;
-#pragma unroll 4
-        for (int ks = 0; ks < KS; ks++) {
-          double b[NTN], a[4];
+        // software pipeline: the A fragments of k-step ks + 1 are requested before the DMMAs of step ks are issued, so the L2
+        // latency of the integral stream hides behind a full step of tensor work instead of surfacing at every unroll boundary
+        double a[4], an[4];
 #pragma unroll
-          for (int nt = 0; nt < NTN; nt++) b[nt] = bs[8 * nt * LDK + 4 * ks];
+        for (int mi = 0; mi < 4; mi++) {
+          const int mt = mt0 + warp + 8 * mi;
+          a[mi] = (mt < MT) ? __ldg(A + (size_t)mt * KS * 32) : 0.0;
+        }
+#pragma unroll 2
+        for (int ks = 0; ks < KS; ks++) {
+          double b[NTN];
 #pragma unroll
           for (int mi = 0; mi < 4; mi++) {
             const int mt = mt0 + warp + 8 * mi;
-            a[mi] = (mt < MT) ? __ldg(A + ((size_t)mt * KS + ks) * 32) : 0.0;
+            an[mi] = (mt < MT && ks + 1 < KS) ? __ldg(A + ((size_t)mt * KS + ks + 1) * 32) : 0.0;
           }
+#pragma unroll
+          for (int nt = 0; nt < NTN; nt++) b[nt] = bs[8 * nt * LDK + 4 * ks];
 #pragma unroll
           for (int mi = 0; mi < 4; mi++) {
             if (mt0 + warp + 8 * mi < MT) {  // warp-uniform: a missing m-tile (np2 = 225: 29 tiles on 32 slots) costs no DMMA
@@ -456,6 +464,8 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
               for (int nt = 0; nt < NTN; nt++) dmma(acc[mi][nt][0], acc[mi][nt][1], a[mi], b[nt]);
             }
           }
+#pragma unroll
+          for (int mi = 0; mi < 4; mi++) a[mi] = an[mi];
         }
       }
 #pragma unroll
