@@ -432,9 +432,19 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
     for (int mt0 = 0; mt0 < MT; mt0 += 32) {  // 32 m-tiles per sweep (4 per warp); np2 <= 256 needs one sweep
       for (int ab = 0; ab < st2; ab++) {
         __syncthreads();
-        for (int idx = tid; idx < NI * LDK; idx += 256) {
-          const int n = idx / LDK, k = idx - n * LDK;
-          sm[idx] = (n < nn && k < np2) ? Rbase[(size_t)n * istride + (size_t)ab * nel2 * np2 + k] : 0.0;
+        // B tile: every element goes global -> shared by cp.async (zero fill for the padding), all copies of the CTA in flight
+        // together instead of one load -> store round trip per element
+        {
+          const unsigned sm_s = (unsigned)__cvta_generic_to_shared(sm);
+          const double* Rab = Rbase + (size_t)ab * nel2 * np2;
+          for (int idx = tid; idx < NI * LDK; idx += 256) {
+            const int n = idx / LDK, k = idx - n * LDK;
+            const bool ok = n < nn && k < np2;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sm_s + (unsigned)idx * 8u),
+                         "l"(ok ? Rab + (size_t)n * istride + k : Rbase), "r"(ok ? 8 : 0) : "memory");
+          }
+          asm volatile("cp.async.commit_group;" ::: "memory");
+          asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
         const double* A = prm.teiK + ((((size_t)r * nel + ie) * st2 + ab) * MT) * KS * 32 + lane;
