@@ -705,8 +705,8 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
     if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const int nchunk = (int)((nrad2 + 255) / 256);
-    const size_t smem1 = (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + CHX_T * sizeof(long long) +
-                         (size_t)(2 * nang + 2 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)nang;
+    const size_t smem1 = (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + 8 * CHX_T * sizeof(long long) +
+                         (size_t)(2 * nang + 16 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)2 * nang;
     const size_t smem2 = (size_t)2 * CHX_UMAX * CHX_LDC * sizeof(double) + CHX_UMAX * sizeof(size_t) + (size_t)2 * nch_max * nang * sizeof(int) +
                          (size_t)8 * CHX_X2_STAGES * 128 * sizeof(double);
     if (smem1 > 48 * 1024 || smem2 > 48 * 1024) {

@@ -132,24 +132,26 @@ __device__ __forceinline__ long long chx_wblock(const ChanXParams& prm, int row,
 // x1.  grid (tiles of the batch, l chunks), 256 threads.  tiles: [c, nj, j_0 .. j_{T-1}] per tile.
 // On the FP64 tensor pipe: W_{(c,j)}[l][k] = sum_v coef[u_v][j][b] P_{i_v l}[k] as a GEMM with M = the radial pairs k (A operand read from
 // the dense P in fragment order), N = the tile's <= 8 rows j (one n-tile per stack half b), K = the active partners of this l.
-// dynamic smem: coef[2][UMAX+1][CHX_LDC] doubles (slot UMAX stays zero: padding) | wblk[T] long long | ulist[nang] | dom[nang] |
-//               act[UMAX+4] | actl[UMAX+4] ints | done[nang] bytes
+// dynamic smem: coef[2][UMAX+1][CHX_LDC] doubles (slot UMAX stays zero: padding) | wblk[8][T] long long | ulist[nang] | dom[nang] |
+//               act[8][UMAX+4] | actl[8][UMAX+4] ints | done[nang] | cur[nang] bytes
 static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams prm, const int* tiles) {
   extern __shared__ double sm[];
-  __shared__ int s_cnt, s_na;
+  __shared__ int s_cnt, s_na[8];
   const int nang = prm.nang, nrad = prm.nrad, nrad2 = nrad * nrad, st = prm.stack;
   constexpr int CB = (CHX_UMAX + 1) * CHX_LDC;  // one stack half of the coefficient table
   double* coef = sm;
-  long long* wblk = reinterpret_cast<long long*>(coef + 2 * CB);
-  int* ulist = reinterpret_cast<int*>(wblk + CHX_T);
+  constexpr int NA = CHX_UMAX + 4;
+  long long* wblk_all = reinterpret_cast<long long*>(coef + 2 * CB);  // [8 l of a group][T]
+  int* ulist = reinterpret_cast<int*>(wblk_all + 8 * CHX_T);
   int* dom = ulist + nang;
-  int* act = dom + nang;           // coefficient slot of the v-th active partner
-  int* actl = act + CHX_UMAX + 4;  // its angular index times nrad (row offset of its P block)
-  unsigned char* done = reinterpret_cast<unsigned char*>(actl + CHX_UMAX + 4);
+  int* act_all = dom + nang;         // [8][NA] coefficient slot of the v-th active partner
+  int* actl_all = act_all + 8 * NA;  // [8][NA] its angular index times nrad (row offset of its P block)
+  unsigned char* done = reinterpret_cast<unsigned char*>(actl_all + 8 * NA);  // [nang] an EARLIER pass wrote the blocks of l
+  unsigned char* cur = done + nang;                                           // [nang] this pass writes them
   const int* T = tiles + (size_t)blockIdx.x * (2 + CHX_T);
   const int c = T[0], nj = T[1];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
-  for (int q = tid; q < nang; q += 256) { dom[q] = -1; done[q] = 0; }
+  for (int q = tid; q < nang; q += 256) { dom[q] = -1; done[q] = 0; cur[q] = 0; }
   __syncthreads();
   for (int jj = 0; jj < nj; jj++) {
     const int row = c * nang + T[2 + jj];
@@ -176,32 +178,46 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
         }
       }
     }
-    for (int l = blockIdx.y; l < nang; l += gridDim.y) {
-      __syncthreads();  // coef complete / previous l done with act and wblk
-      if (warp == 0) {  // compact list of the partners whose P block is non-zero, padded to k-steps of four with the zero slot
+    // groups of eight l: every warp compacts the partner list of one of them (no serial section, two block barriers per group
+    // instead of per l), then the CTA streams the eight l one after the other
+    for (int lg = blockIdx.y; lg < nang; lg += gridDim.y * 8) {
+      __syncthreads();  // coef complete / previous group done with its lists
+      {
+        const int l = lg + warp * gridDim.y;
+        int* act = act_all + warp * NA;
+        int* actl = actl_all + warp * NA;
         int base = 0;
-        for (int q0 = 0; q0 < nu; q0 += 32) {
-          const int q = q0 + lane;
-          const int lq = q < nu ? ulist[ubase + q] : 0;
-          const bool f = q < nu && prm.nzP[(size_t)lq * nang + l];
-          const unsigned mk = __ballot_sync(0xffffffffu, f);
-          if (f) {
-            const int v = base + __popc(mk & ((1u << lane) - 1u));
-            act[v] = q;
-            actl[v] = lq * nrad;
+        if (l < nang) {  // warp-uniform
+          for (int q0 = 0; q0 < nu; q0 += 32) {
+            const int q = q0 + lane;
+            const int lq = q < nu ? ulist[ubase + q] : 0;
+            const bool f = q < nu && prm.nzP[(size_t)lq * nang + l];
+            const unsigned mk = __ballot_sync(0xffffffffu, f);
+            if (f) {
+              const int v = base + __popc(mk & ((1u << lane) - 1u));
+              act[v] = q;
+              actl[v] = lq * nrad;
+            }
+            base += __popc(mk);
           }
-          base += __popc(mk);
+          __syncwarp();
+          // padded to k-steps of four with the zero slot
+          if (base > 0 && lane < ((4 - (base & 3)) & 3)) { act[base + lane] = CHX_UMAX; actl[base + lane] = actl[0]; }
+          if (lane < CHX_T) wblk_all[warp * CHX_T + lane] = lane < nj ? chx_wblock(prm, c * nang + T[2 + lane], l) : -1;
+          if (lane == 0 && base > 0) cur[l] = 1;
         }
-        __syncwarp();
-        if (base > 0 && lane < ((4 - (base & 3)) & 3)) { act[base + lane] = CHX_UMAX; actl[base + lane] = actl[0]; }
-        if (lane == 0) s_na = base;
+        if (lane == 0) s_na[warp] = base;
       }
-      if (tid < CHX_T) wblk[tid] = tid < nj ? chx_wblock(prm, c * nang + T[2 + tid], l) : -1;
       __syncthreads();
-      const int na = s_na;
+      for (int w = 0; w < 8; w++) {
+      const int l = lg + w * gridDim.y;
+      if (l >= nang) break;
+      const int na = s_na[w];
       if (na == 0) continue;  // block-uniform
-      const bool prev = done[l] != 0;  // an earlier pass already wrote the blocks of this l
-      const long long wb0 = wblk[2 * t4], wb1 = wblk[2 * t4 + 1];
+      const int* act = act_all + w * NA;
+      const int* actl = actl_all + w * NA;
+      const bool prev = done[l] != 0;
+      const long long wb0 = wblk_all[w * CHX_T + 2 * t4], wb1 = wblk_all[w * CHX_T + 2 * t4 + 1];
       for (int k0 = warp * 32; k0 < nrad2; k0 += 256) {
         const int kg = k0 + gid;
         unsigned so[4];  // element offsets inside the dense P fit 32 bits (ldp^2 < 2^32 is checked by the engine)
@@ -242,9 +258,10 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
           }
         }
       }
-      if (tid == 0) done[l] = 1;
+      }  // w
     }
     __syncthreads();
+    for (int q = tid; q < nang; q += 256) { done[q] |= cur[q]; cur[q] = 0; }
   }
 }
 
