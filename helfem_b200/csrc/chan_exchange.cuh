@@ -253,8 +253,8 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
             double* W0 = prm.W + (size_t)wb * st * nrad2 + k;
             double v0 = acc[mt][0][i], v1 = acc[mt][1][i];
             if (prev) { v0 += W0[0]; if (st == 2) v1 += W0[nrad2]; }
-            W0[0] = v0;
-            if (st == 2) W0[nrad2] = v1;
+            __stcs(W0, v0);  // streaming: W is far larger than L2 and is next read by x2
+            if (st == 2) __stcs(W0 + nrad2, v1);
           }
         }
       }
@@ -399,9 +399,9 @@ static __global__ void __launch_bounds__(256, HFB_X2_MINB) chan_x2_mma_kernel(Ch
 #pragma unroll 1
         while (o4.x >= 0) {
           const unsigned o = ob0 + (unsigned)o4.x;
-          if (ubase == 0) {
-            if (it_ok0) { prm.Rsub[o] = v00; if (st == 2) prm.Rsub[o + bst] = v10; }
-            if (it_ok1) { prm.Rsub[o + ist] = v01; if (st == 2) prm.Rsub[o + ist + bst] = v11; }
+          if (ubase == 0) {  // streaming stores: Rsub is far larger than L2 and is next read by x3
+            if (it_ok0) { __stcs(prm.Rsub + o, v00); if (st == 2) __stcs(prm.Rsub + o + bst, v10); }
+            if (it_ok1) { __stcs(prm.Rsub + o + ist, v01); if (st == 2) __stcs(prm.Rsub + o + ist + bst, v11); }
           } else {
             if (it_ok0) { prm.Rsub[o] += v00; if (st == 2) prm.Rsub[o + bst] += v10; }
             if (it_ok1) { prm.Rsub[o + ist] += v01; if (st == 2) prm.Rsub[o + ist + bst] += v11; }

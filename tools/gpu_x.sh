@@ -5,4 +5,3 @@ import json;d=json.load(open('gpurun_out/x_l12m3_$1.json'));print('$1', d['ms_pe
 run base
 python bench.py --workload n2_hf_cfg4 --steps 3 > gpurun_out/x_cfg4.json 2> gpurun_out/x_cfg4.err; tail -c 300 gpurun_out/x_cfg4.err; python -c "
 import json;d=json.load(open('gpurun_out/x_cfg4.json'));print('base', d['ms_per_step'], d['roofline'].get('exchange_stage_ms'))"
-ncu --set full --clock-control none --import-source on -k "regex:chan_x1_mma" -c 1 -s 3 -o gpurun_out/x_chan_x1_mma -f python bench.py --kernels-only --workload n2_hf_l12m3 --steps 1 --warmup 1 > gpurun_out/ncu_x3.log 2>&1; tail -1 gpurun_out/ncu_x3.log
