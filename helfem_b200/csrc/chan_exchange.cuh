@@ -503,7 +503,7 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
 #pragma unroll
           for (int cc = 0; cc < 2; cc++) {
             const int n = 8 * nt + 2 * t4 + cc;
-            if (row < np2 && n < nn) Obase[(size_t)n * nel2 * np2 + row] = acc[mi][nt][cc];
+            if (row < np2 && n < nn) __stcs(Obase + (size_t)n * nel2 * np2 + row, acc[mi][nt][cc]);
             acc[mi][nt][cc] = 0.0;
           }
       }
@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
           for (int ks = 0; ks < 2 * NTL; ks++) {
             const int kk = 4 * ks + t4;
 #pragma unroll
-            for (int nt = 0; nt < NTL; nt++) rf[ks][nt] = (kk < np && 8 * nt + gid < np) ? Rn[kk + (8 * nt + gid) * np] : 0.0;
+            for (int nt = 0; nt < NTL; nt++) rf[ks][nt] = (kk < np && 8 * nt + gid < np) ? __ldcs(Rn + kk + (8 * nt + gid) * np) : 0.0;
           }
           double y[NTL][NTL][2];
 #pragma unroll
@@ -599,7 +599,7 @@ __global__ void __launch_bounds__(256, 2) chan_x3_kernel(ChanXParams prm, const 
 #pragma unroll
             for (int cc = 0; cc < 2; cc++) {
               const int row = 8 * mt + gid, col = 8 * qt + 2 * t4 + cc;
-              if (row < np && col < np) On[row + col * np] = kacc[it][mt][qt][cc];
+              if (row < np && col < np) __stcs(On + row + col * np, kacc[it][mt][qt][cc]);
             }
       }
     }
