@@ -444,3 +444,108 @@ int hfb200_sadatom_fock_host(hfb200_ctx* c, int nbatch, int x_func, int c_func, 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of hfb200_sadatom_fock_batch (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The per-build scratch of the batch kernels (triangle-folded densities `pc`, disjoint traces, partial
+// XC scalars) lives in ONE file-scope device array of HFB200_STATIC_SCRATCH_BYTES instead of the context's growable
+// cudaMalloc'ed buffers.  Every GPU that loads the library holds the array until the process exits.  All calls (of all
+// contexts on one device) share it and it keeps the last call's contents: the range a call uses is cleared on the
+// call's stream first, and calls that overlap on the GPU (different streams, or different host threads) race.
+// ------------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+static_assert(HFB200_STATIC_SCRATCH_BYTES % 256 == 0, "scratch size must keep the 256-byte alignment of its parts");
+static __device__ __align__(256) double g_static_scratch[HFB200_STATIC_SCRATCH_BYTES / sizeof(double)];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+double* g_static_ptr[kMaxDevices] = {};  // DEVICE address of g_static_scratch on each device, resolved once per device
+
+// In host code `g_static_scratch` is only the host-side stand-in of the symbol, not a device address: it must never be
+// handed to a kernel.  Resolve the device address once per device, with that device current.
+int static_scratch_address(int device, double** out) {
+  if (device < 0 || device >= kMaxDevices) { set_error("device %d out of range", device); return HFB200_EINVAL; }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    int cur = -1;
+    HFB_CUDA_OK(cudaGetDevice(&cur));
+    if (cur != device) HFB_CUDA_OK(cudaSetDevice(device));
+    double* p = nullptr;
+    HFB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_static_scratch));
+    if (!p) { set_error("cudaGetSymbolAddress returned a null address for the static scratch"); return HFB200_ECUDA; }
+    g_static_ptr[device] = p;
+  }
+  *out = g_static_ptr[device];
+  return 0;
+}
+
+size_t round32(size_t n) { return (n + 31) & ~(size_t)31; }  // 32 doubles = 256 bytes
+
+}  // namespace
+
+extern "C" int hfb200_sadatom_fock_batch_static(hfb200_ctx* c, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                                                double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
+                                                double* dScalars, void* stream) {
+  if (!c || c->kind != CTX_SADATOM || nbatch < 1 || (nspin != 1 && nspin != 2) || nslices < 1 || !dP_band) {
+    set_error("hfb200_sadatom_fock_batch_static: invalid argument");
+    return HFB200_EINVAL;
+  }
+  if (dJ_band && !c->dTeiF) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  int fam = 0;
+  if (dH_band && !valid_pair(x_func, c_func, &fam)) {
+    set_error("functional pair (%d,%d) has no device implementation (no CPU fallback)", x_func, c_func);
+    return HFB200_EFUNC;
+  }
+  // layout inside the static array: [pc | traces | partial], each part starting on a 256-byte boundary
+  const size_t nPc = dJ_band ? round32((size_t)nbatch * c->nel * 4 * c->jKS) : 0;
+  const size_t nTr = dJ_band ? round32((size_t)nbatch * c->nel * 2) : 0;
+  const size_t nPa = dH_band ? round32((size_t)nbatch * c->nel * 4) : 0;
+  const size_t need = (nPc + nTr + nPa) * sizeof(double);
+  if (need > (size_t)HFB200_STATIC_SCRATCH_BYTES) {
+    set_error("hfb200_sadatom_fock_batch_static: %d builds need %zu bytes of scratch, the static array holds %zu "
+              "(HFB200_STATIC_SCRATCH_BYTES); split the batch or use hfb200_sadatom_fock_batch",
+              nbatch, need, (size_t)HFB200_STATIC_SCRATCH_BYTES);
+    return HFB200_EINVAL;
+  }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  double* scratch = nullptr;
+  int rc;
+  if ((rc = static_scratch_address(c->device, &scratch))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the previous call's contents; every part is rewritten in full before it is read, the clear makes
+  // that independent of the kernels' write patterns
+  if (need) HFB_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));
+  double* sPtot = dJ_band ? scratch : nullptr;
+  double* sTraces = dJ_band ? scratch + nPc : nullptr;
+  double* sPartial = dH_band ? scratch + nPc + nTr : nullptr;
+  const bool fused_pack = dJ_band && dH_band;
+  if (dH_band) {
+    SadGridParams g;
+    g.Bt = c->dBt; g.dBt = c->ddBt; g.r = c->dR; g.wrad = c->dW;
+    g.nel = c->nel; g.nq = c->nq; g.nq8 = c->nq8; g.ldq = c->ldq; g.np_max = c->np_max; g.np_pad = c->np_pad;
+    g.nslices = nslices; g.nb = nbatch;
+    g.x_func = x_func; g.c_func = c_func; g.dens_thr = dens_thr;
+    g.P = dP_band; g.H = dH_band; g.partial = sPartial;
+    g.pc = fused_pack ? sPtot : nullptr;
+    g.traces = sTraces; g.dLc = c->dLc; g.dm1Lc = c->dm1Lc; g.tri = c->dTri;
+    g.ntri = c->ntri; g.jKP = fused_pack ? 4 * c->jKS : 0; g.jMP = 8 * c->jMT;
+    if ((rc = launch_grid(fam, nspin, g, st))) return rc;
+    if (dScalars) {
+      sad_reduce_scalars_kernel<<<nbatch, 32, 0, st>>>(sPartial, c->nel, dScalars);
+      HFB_CUDA_OK(cudaGetLastError());
+    }
+  }
+  if (dJ_band) {
+    SadJParams q;
+    q.teiF = c->dTeiF; q.dLc = c->dLc; q.dm1Lc = c->dm1Lc; q.tri = c->dTri;
+    q.nel = c->nel; q.np_max = c->np_max; q.ntri = c->ntri; q.MT = c->jMT; q.KS = c->jKS;
+    q.nslices = nslices; q.nspin = nspin; q.nb = nbatch;
+    q.P = dP_band; q.pc = sPtot; q.traces = sTraces; q.J = dJ_band;
+    if ((rc = launch_coulomb(q, !fused_pack, st))) return rc;
+  }
+  return HFB200_OK;
+}

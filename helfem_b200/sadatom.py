@@ -137,6 +137,12 @@ class SadatomBasis:
                                               ctypes.c_double(thr), ctypes.c_void_p(dP), ctypes.c_void_p(dJ), ctypes.c_void_p(dH),
                                               ctypes.c_void_p(dS), ctypes.c_void_p(stream)))
 
+    def fock_batch_static(self, nbatch, x_func, c_func, nspin, nslices, thr, dP, dJ, dH, dS, stream=0):
+        """fock_batch without any allocation inside the call (static device scratch, bounded batch size)."""
+        check(lib().hfb200_sadatom_fock_batch_static(self.context(), int(nbatch), int(x_func), int(c_func), int(nspin),
+                                                     int(nslices), ctypes.c_double(thr), ctypes.c_void_p(dP), ctypes.c_void_p(dJ),
+                                                     ctypes.c_void_p(dH), ctypes.c_void_p(dS), ctypes.c_void_p(stream)))
+
     def fock_host(self, nbatch, x_func, c_func, nspin, nslices, thr, hP, hJ=None, hH=None, hS=None):
         """Host element-band arrays (numpy, C-contiguous float64) in and out; see include/helfem_b200.h."""
         check(lib().hfb200_sadatom_fock_host(self.context(), int(nbatch), int(x_func), int(c_func), int(nspin), int(nslices),

@@ -107,6 +107,20 @@ int hfb200_sadatom_fock_batch(hfb200_ctx* ctx, int nbatch, int x_func, int c_fun
                               double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
                               double* dScalars, void* stream);
 
+/* Allocation-free variant of hfb200_sadatom_fock_batch.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, kernels and results as hfb200_sadatom_fock_batch, but
+ * the per-build scratch (folded densities, disjoint traces, partial XC scalars) lives in one static device array of
+ * HFB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call makes no cudaMalloc /
+ * cudaFree and calls no allocating library routine.  Batches whose scratch exceeds the array (about
+ * (nel*(4*ceil8(np(np+1)/2)) + 6*nel)*8 bytes per build: 416 builds of configs[1], 54 of configs[2]) are refused with
+ * HFB200_EINVAL.  All calls on a device share the array, which keeps the last call's contents (the range in use is
+ * cleared on `stream` first): calls that overlap on the GPU race -- serialise them on one stream. */
+#define HFB200_STATIC_SCRATCH_BYTES (8u << 20)
+int hfb200_sadatom_fock_batch_static(hfb200_ctx* ctx, int nbatch, int x_func, int c_func, int nspin, int nslices,
+                                     double dens_thr, const double* dP_band, double* dJ_band, double* dH_band,
+                                     double* dScalars, void* stream);
+
 /* The same batch with HOST element-band buffers (layout as above): one H2D copy of the densities, the
  * kernels, D2H copies of J / H bands and scalars; returns when the results are on the host.  hJ_band,
  * hH_band, hScalars may each be NULL to skip that operator. */
