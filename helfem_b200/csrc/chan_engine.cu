@@ -535,11 +535,8 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
 namespace {
 template <int NI, int NTL, bool OFFD>
 int launch_x3_one(const ChanXParams& q, const int2* groups, int ngroups, size_t smem, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  // per launch: the attribute belongs to the current device's context (one process can hold contexts on several GPUs)
+  HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int ny = OFFD ? q.nel * (q.nel - 1) : q.nel;
   if (ny == 0) return 0;
   chan_x3_kernel<NI, NTL, OFFD><<<dim3(ngroups, ny), 256, smem, st>>>(q, groups);

@@ -61,6 +61,16 @@ class DiatomicBasis:
         check_host(lib().hfh_diatomic_get_tei(self._h, int(which), int(ilm), int(iel), _p(out)))
         return out
 
+    def tei_view(self, which, ilm, iel):
+        """Same block as tei() WITHOUT a copy (read-only numpy view of the host library's storage; keep the basis alive)."""
+        ptr, n = ctypes.POINTER(ctypes.c_double)(), ctypes.c_long()
+        check_host(lib().hfh_diatomic_tei_view(self._h, int(which), int(ilm), int(iel), ctypes.byref(ptr), ctypes.byref(n)))
+        npe = int(self.last[iel] - self.first[iel] + 1)
+        d = npe if which < 4 else npe * npe
+        a = np.ctypeslib.as_array(ptr, shape=(n.value,)).reshape((d, d), order="F")
+        a.flags.writeable = False
+        return a
+
     def context(self):
         """The hfb200_ctx of this basis (device tables are uploaded on first use)."""
         ctx = ctypes.c_void_p()

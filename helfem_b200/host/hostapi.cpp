@@ -384,6 +384,24 @@ int hfh_diatomic_get_tei(void* h, int which, int ilm, int iel, double* out) {
   memcpy(out, m->ptr(), m->size() * sizeof(double));
   HFH_CATCH
 }
+// Zero-copy view of one stored block (same indexing as hfh_diatomic_get_tei): at BASELINE configs[3] the stored
+// integrals are 9.5 GB, a second copy for the checker is not affordable.  The pointer lives as long as the basis.
+int hfh_diatomic_tei_view(void* h, int which, int ilm, int iel, const double** ptr, long* n) {
+  HFH_TRY
+  auto* b = (diatomic::TwoDBasis*)h;
+  const size_t idx = (size_t)ilm * b->get_radial().Nel() + iel;
+  const Mat* m = nullptr;
+  if (b->get_prim_tei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+  if (which < 4) m = &b->get_disjoint(which)[idx];
+  else if (which < 8) m = &b->get_prim_tei()[4 * idx + which - 4];
+  else {
+    if (b->get_prim_ktei().empty()) throw std::logic_error("Primitive teis have not been computed!\n");
+    m = &b->get_prim_ktei()[4 * idx + which - 8];
+  }
+  *ptr = m->ptr();
+  *n = (long)m->size();
+  HFH_CATCH
+}
 int hfh_diatomic_coulomb(void* h, const double* P, double* J) {
   HFH_TRY
   ((diatomic::TwoDBasis*)h)->coulomb(P, J);

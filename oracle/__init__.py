@@ -194,7 +194,7 @@ class DiatomicOracle:
         self.lval, self.mval, self.first, self.last, self.Lmap, self.Mmap = map(ci, (lval, mval, first, last, Lmap, Mmap))
         self.Rhalf = float(Rhalf)
         self.dis = [[np.asfortranarray(a) for a in d] for d in dis]
-        self.tei = [np.asfortranarray(a) for a in tei]
+        self.tei = None if tei is None else [np.asfortranarray(a) for a in tei]
         self.ktei = None if ktei is None else [np.asfortranarray(a) for a in ktei]
         self.pure = np.asarray(pure)
         self.nd = len(self.lval) * (int(self.last[-1]) + 1)
@@ -214,6 +214,42 @@ class DiatomicOracle:
 
     def exchange(self, P):
         return self._apply(lib().oracle_diatomic_exchange, self.ktei, P)
+
+
+    def _blocks(self, fn, teis, Ppure, alist, blist):
+        """Block-restricted oracle (chan_oracle.cpp): the listed output angular blocks only, from the caller's
+        PURE-basis matrix (no dense dummy-space copy): returns (nblk, nrad, nrad) blocks in the dummy space,
+        block[q][a, b] = F[(alist[q], a), (blist[q], b)]."""
+        P = np.asfortranarray(Ppure, dtype=np.float64)
+        amap = np.full(self.nd, -1, dtype=np.int32)
+        amap[self.pure] = np.arange(len(self.pure), dtype=np.int32)
+        al, bl = np.ascontiguousarray(alist, dtype=np.int32), np.ascontiguousarray(blist, dtype=np.int32)
+        nrad = int(self.last[-1]) + 1
+        out = np.zeros((len(al), nrad * nrad))
+        fn.argtypes = None
+        rc = fn(len(self.lval), _ip(self.lval), _ip(self.mval), len(self.first), _ip(self.first), _ip(self.last), len(self.Lmap),
+                _ip(self.Lmap), _ip(self.Mmap), ctypes.c_double(self.Rhalf), _ptr_array(self.dis[0]), _ptr_array(self.dis[1]),
+                _ptr_array(self.dis[2]), _ptr_array(self.dis[3]), _ptr_array(teis), _p(P), ctypes.c_long(P.shape[0]), _ip(amap),
+                len(al), _ip(al), _ip(bl), _p(out))
+        assert rc == 0
+        return out.reshape(len(al), nrad, nrad).transpose(0, 2, 1)  # column-major blocks -> [q][a, b]
+
+    def exchange_blocks(self, P, jlist, klist):
+        return self._blocks(lib().oracle_diatomic_exchange_blocks, self.ktei, P, jlist, klist)
+
+    def coulomb_blocks(self, P, ilist, jlist):
+        return self._blocks(lib().oracle_diatomic_coulomb_blocks, self.tei, P, ilist, jlist)
+
+    def pure_block(self, F, a, b):
+        """Block (a, b) of a PURE-basis matrix, expanded to the dummy space (zeros on the removed rows / columns)."""
+        nrad = int(self.last[-1]) + 1
+        amap = np.full(self.nd, -1, dtype=np.int64)
+        amap[self.pure] = np.arange(len(self.pure))
+        ra, rb = amap[a * nrad:(a + 1) * nrad], amap[b * nrad:(b + 1) * nrad]
+        out = np.zeros((nrad, nrad))
+        ia, ib = np.nonzero(ra >= 0)[0], np.nonzero(rb >= 0)[0]
+        out[np.ix_(ia, ib)] = F[np.ix_(ra[ia], rb[ib])]
+        return out
 
 
 def angular_grid(lang, mang):

@@ -116,3 +116,63 @@ def xc_pointwise_check(evaluate, oracle_xc, funcs=(1, 12, 101, 130, 497, 498), n
                 if m.any():
                     worst = max(worst, float(np.max(np.abs(g_ - w_)[m] / np.abs(w_)[m])))
     return worst
+
+
+# ---- diatomic program: overlap-normalised synthetic orbitals (full-size parity tests, bench) ----
+def _cos2_matrix(lval, mval):
+    """<Y_a| cos^2(theta) |Y_b> for the angular list: closed forms of the standard recursion
+    cos(t) Y_lm = A_{l+1,m} Y_{l+1,m} + A_{l,m} Y_{l-1,m},  A_{l,m} = sqrt((l^2 - m^2) / (4 l^2 - 1))."""
+    def A(l, m):
+        return np.sqrt(max(l * l - m * m, 0) / (4.0 * l * l - 1.0)) if l > 0 else 0.0
+    n = len(lval)
+    c2 = np.zeros((n, n))
+    for a in range(n):
+        for b in range(n):
+            if mval[a] != mval[b]:
+                continue
+            l, lp, m = int(lval[a]), int(lval[b]), int(mval[a])
+            if l == lp:
+                c2[a, b] = A(l + 1, m) ** 2 + A(l, m) ** 2
+            elif l == lp + 2:
+                c2[a, b] = A(l, m) * A(l - 1, m)
+            elif lp == l + 2:
+                c2[a, b] = A(lp, m) * A(lp - 1, m)
+    return c2
+
+
+def diatomic_overlap_apply(b, C):
+    """S C for coefficient arrays C (nang, nrad, norb) in the dummy space of a DiatomicBasis harness object:
+    S = Rh^3 [ delta_ab I2 - <a|cos^2|b> I0 ],  I_k = int B_i B_j sinh(mu) cosh^k(mu) dmu  (the prolate volume element
+    Rh^3 sinh(mu) (cosh^2(mu) - cos^2(nu)); /root/reference/src/diatomic/basis.cpp overlap())."""
+    nrad = b.nrad
+    I0, I2 = np.zeros((nrad, nrad)), np.zeros((nrad, nrad))
+    for e in range(b.nel):
+        mu, w, bf, _ = b.radial(e)
+        f, l = int(b.first[e]), int(b.last[e])
+        I0[f:l + 1, f:l + 1] += bf.T @ (bf * (w * np.sinh(mu))[:, None])
+        I2[f:l + 1, f:l + 1] += bf.T @ (bf * (w * np.sinh(mu) * np.cosh(mu) ** 2)[:, None])
+    c2 = _cos2_matrix(b.lval, b.mval)
+    return b.Rhalf ** 3 * (np.einsum("ij,ajo->aio", I2, C) - np.einsum("ab,ij,bjo->aio", c2, I0, C))
+
+
+def diatomic_orbitals(b, occ_m=(0, 0, 0, 0, 0, 1, -1), seed=100, decay_l=0.35, decay_r=0.06):
+    """Synthetic occupied orbitals of a linear molecule, each pure in m (N2-like by default: five sigma, pi+, pi-):
+    smooth seeded coefficients decaying with l and the radial index, then Loewdin-ORTHONORMALISED in the overlap
+    metric, so that P = 2 C C^T has tr(P S) = 2 norb like a converged closed-shell density and J, K have physical
+    magnitudes.  Returns C (ndummy, norb); rows of the removed boundary functions are zero."""
+    nrad, nang = b.nrad, b.nang
+    cols = []
+    for q, m in enumerate(occ_m):
+        c = np.zeros((nang, nrad))
+        sel = np.where(b.mval == m)[0]
+        noise = splitmix64(len(sel) * nrad, seed=seed + q).reshape(len(sel), nrad)
+        c[sel] = noise * np.exp(-decay_l * b.lval[sel])[:, None] * np.exp(-decay_r * np.arange(nrad))[None, :]
+        if m != 0:
+            c[sel, 0] = 0.0
+        cols.append(c)
+    C = np.stack(cols, axis=2)
+    SC = diatomic_overlap_apply(b, C)
+    G = np.einsum("aio,aip->op", C, SC)
+    ev, U = np.linalg.eigh(G)
+    C = C @ (U @ np.diag(ev ** -0.5) @ U.T)
+    return C.reshape(nang * nrad, len(occ_m))
