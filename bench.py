@@ -611,12 +611,13 @@ def run_chan(args, w, rank, world, local_rank):
         cpu = {"value": 1.0 / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
                "sample": "1 Fock build (coulomb + exchange) of the same workload",
                "max_dJ": float(np.max(np.abs(np.asarray(Jh) - Jo))), "max_dK": float(np.max(np.abs(np.asarray(Kh) - Ko)))}
-    tf = x3_flops / (stage[3] * 1e-3) / 1e12 if stage[3] > 0 else None
-    roofline = {"kernel": "chan_x3_kernel", "bound": "tensor", "achieved": tf, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s",
-                "frac": (tf / FP64_TFLOPS_MEASURED) if tf else None, "traffic": ncu_traffic(args.workload, "chan_x3_kernel"),
+    t_rad = stage[2] + stage[3]
+    tf = x3_flops / (t_rad * 1e-3) / 1e12 if t_rad > 0 else None
+    roofline = {"kernel": "chan_xf_same_kernel + chan_xf_pair_kernel", "bound": "tensor", "achieved": tf, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s",
+                "frac": (tf / FP64_TFLOPS_MEASURED) if tf else None, "traffic": ncu_traffic(args.workload, "chan_xf_same_kernel"),
                 "peak_source": "measured cuBLAS DGEMM FP64 (profiles/r01_fp64_peak.json); tcgen05 has no FP64 kind, DMMA.8x8x4 is the FP64 tensor path",
-                "algorithmic_flops_per_build": x3_flops, "ms_per_build": stage[3],
-                "exchange_stage_ms": dict(zip(["mask", "x1_left_angular", "x2_right_angular", "x3_radial_dmma", "x4_assemble"], stage)),
+                "algorithmic_flops_per_build": x3_flops, "ms_per_build": t_rad,
+                "exchange_stage_ms": dict(zip(["mask", "x1_left_angular", "xf_same_element", "xf_element_pairs", "x4_assemble"], stage)),
                 "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items, "family_batches": b.exchange_batches()}
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,

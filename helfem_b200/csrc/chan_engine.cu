@@ -8,6 +8,7 @@
 #include <map>
 #include "../../include/helfem_b200.h"
 #include "chan_exchange.cuh"
+#include "chan_exchange_fused.cuh"
 
 namespace hfb {
 
@@ -156,21 +157,8 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     }
   }
   if ((rc = up(this, &xprm.first, first)) || (rc = up(this, &xprm.npe, npe)) || (rc = up(this, &xprm.elem_of, elem_of))) return rc;
-  {
-    // where the radial pair (A,B) lives inside the element-pair sub-blocks of Rsub (x2 scatter)
-    std::vector<int4> eltab((size_t)nrad * nrad);
-    for (int B = 0; B < nrad; B++)
-      for (int A = 0; A < nrad; A++) {
-        int o[4] = {-1, -1, -1, -1}, no = 0;  // valid offsets first
-        for (int x = 0; x < 2; x++)
-          for (int y = 0; y < 2; y++) {
-            const int ie = elem_of[2 * A + x], je = elem_of[2 * B + y];
-            if (ie >= 0 && je >= 0) o[no++] = (ie * nel + je) * np2 + (A - first[ie]) + (B - first[je]) * np;
-          }
-        eltab[A + (size_t)B * nrad] = make_int4(o[0], o[1], o[2], o[3]);
-      }
-    if ((rc = up(this, &xprm.eltab, eltab))) return rc;
-  }
+  xprm.PB = (np2 + 7) & ~7;  // W sub-block of an element pair: whole 8-row m-tiles (64-byte multiples: bulk-copy granularity)
+  xprm.WB = nel * nel * xprm.PB;
   fam_fac = S.fac;
   // disjoint factors, zero padded squares
   {
@@ -246,7 +234,8 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     for (size_t q = 0; q < (size_t)nchan * nang; q++) cnt[q + 1] += cnt[q];
     xrowptr = cnt;
     xrow_i.assign(cnt.back(), 0);
-    std::vector<double> coef(2 * (size_t)cnt.back(), 0.0);
+    std::vector<double>& coef = xrow_coef;
+    coef.assign(2 * (size_t)cnt.back(), 0.0);
     std::vector<int> fill(cnt.begin(), cnt.end() - 1);
     for (int j = 0; j < nang; j++)
       for (int i = 0; i < nang; i++)  // i ascending within a row
@@ -293,16 +282,17 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
   }
   {
     unsigned char* p = nullptr;
-    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang));
+    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang + 8));  // + the symmetry flag of P
     owned.push_back(p);
     dNzP = p;
     if (hNzP) cudaFreeHost(hNzP);
-    HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang));
+    HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang + 8));
   }
   if ((rc = up(this, &dFamFac, fam_fac))) return rc;
-  // x3 tile: NI output blocks per CTA, as many as the shared-memory tile allows
-  x3_ni = 32;
-  while (x3_ni > 8 && (size_t)x3_ni * xprm.LDK * sizeof(double) > 200 * 1024) x3_ni >>= 1;
+  // items per CTA of the fused kernels: as many as the shared-memory tiles allow with two CTAs per SM
+  ni_same = 32;
+  while (ni_same > 8 && ((size_t)ni_same * xprm.LDK + chxf_ring_doubles(xprm.PB)) * sizeof(double) > 110 * 1024) ni_same >>= 1;
+  ni_pair = (np <= 16) ? 8 : 4;
   mask_cached.clear();
   have_k = true;
   return 0;
@@ -326,12 +316,13 @@ int up_list(ChanEngine::DevList& L, const std::vector<T>& v) {
 
 // Everything that depends on the sparsity pattern of P (one block mask), built once per pattern:
 //  * L(c,j) = { l : some partner i of the coupling row (c,j) has P[i,l] != 0 } -> compact layout of W
-//  * items of family r: (j,k) such that some channel c of r has rows (c,j), (c,k) and L(c,j) meets row (c,k)
-//  * x2 tiles, x3 groups, the CSR of distinct output blocks for x4
-//  * batches of consecutive families whose W and R workspaces fit the budget
-int ChanEngine::build_items(const unsigned char* nz) {
+//  * items of family r: (j,k) such that some channel c of r has rows (c,j), (c,k) and L(c,j) meets row (c,k);
+//    with an exactly symmetric P only j <= k (K[k,j] = K[j,k]^T is written by x4)
+//  * tiles (<= CHX_T consecutive items with one j), their slot tables for the fused kernels, item groups,
+//    the CSR of distinct output blocks for x4
+//  * batches of consecutive families whose W and output workspaces fit the budget
+int ChanEngine::build_items(const unsigned char* nz, bool sym) {
   const int nang = xprm.nang, nr = prm.nr, nw = (nang + 63) / 64, st = prm.stack, nel = prm.nel, np2 = prm.np2;
-  const size_t nrad2 = (size_t)nrad * nrad;
   std::vector<uint64_t> nzrow((size_t)nang * nw, 0);  // nzrow[i] = { l : P[i,l] != 0 }
   for (int i = 0; i < nang; i++)
     for (int l = 0; l < nang; l++)
@@ -369,6 +360,7 @@ int ChanEngine::build_items(const unsigned char* nz) {
         for (int j : js) {
           const unsigned long long* ls = &wbits[((size_t)c * nang + j) * nw];
           for (int k : js) {
+            if (sym && k < j) continue;
             if (hit[(size_t)j * nang + k]) continue;
             uint64_t any = 0;
             for (int w = 0; w < nw; w++) any |= ls[w] & rowset[(size_t)k * nw + w];
@@ -380,9 +372,21 @@ int ChanEngine::build_items(const unsigned char* nz) {
         const size_t b0 = fam_items[r].size();
         for (int k = 0; k < nang; k++)
           if (hit[(size_t)j * nang + k]) fam_items[r].push_back(make_int2(j, k));
-        // within one j: order by angular group so that the x2 tiles (consecutive items) share their partners
+        // within one j: order by angular group so that the tiles (consecutive items) share their partners
         std::stable_sort(fam_items[r].begin() + b0, fam_items[r].end(),
                          [&](const int2& a, const int2& b) { return ang_group[a.y] < ang_group[b.y]; });
+      }
+      if (sym) {  // rows (c, j) that no item j <= k uses produce nothing that is read: drop their W blocks
+        for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
+          for (int j = 0; j < nang; j++) {
+            if (!wcount[(size_t)c * nang + j]) continue;
+            bool used = false;
+            for (int k = j; k < nang && !used; k++) used = hit[(size_t)j * nang + k] != 0;
+            if (!used) {
+              wcount[(size_t)c * nang + j] = 0;
+              for (int w = 0; w < nw; w++) wbits[((size_t)c * nang + j) * nw + w] = 0;
+            }
+          }
       }
     }
   }
@@ -391,19 +395,21 @@ int ChanEngine::build_items(const unsigned char* nz) {
   size_t wcap_bytes = 16ull << 30, rcap_bytes = 12ull << 30;
   if (const char* e = getenv("HFB200_X_WCAP_MB")) wcap_bytes = std::max<size_t>(1, (size_t)atoll(e)) << 20;
   if (const char* e = getenv("HFB200_X_RCAP_MB")) rcap_bytes = std::min<size_t>(std::max<size_t>(1, (size_t)atoll(e)) << 20, 30ull << 30);
-  const long long wcap = (long long)(wcap_bytes / ((size_t)st * nrad2 * sizeof(double)));
-  const long long icap = (long long)(rcap_bytes / ((size_t)st * st * nel * nel * np2 * sizeof(double)));
-  std::vector<int2> items, tiles2, groups;
+  const long long wcap = (long long)(wcap_bytes / ((size_t)st * xprm.WB * sizeof(double)));
+  const long long icap = (long long)(rcap_bytes / ((size_t)nel * nel * np2 * sizeof(double)));  // output sub-blocks of the batch
+  std::vector<int2> items, tiles2;
+  std::vector<int4> groupsS, groupsP;
   std::vector<int> item_fam, out_ptr, out_item;
   std::vector<long long> wbase((size_t)nchan * nang, -1);
   batches.clear();
   max_wblocks = 0;
   max_batch_items = 0;
-  XBatch cur{fam_t1[0], fam_t1[0], 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  XBatch cur{fam_t1[0], fam_t1[0], 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   auto close_batch = [&]() {
     cur.item1 = (int)items.size();
     cur.t2_1 = (int)tiles2.size();
-    cur.g1 = (int)groups.size();
+    cur.gs1 = (int)groupsS.size();
+    cur.gp1 = (int)groupsP.size();
     // distinct output blocks of the batch, items of one block in family order
     std::vector<int> idx(cur.item1 - cur.item0);
     for (size_t q = 0; q < idx.size(); q++) idx[q] = cur.item0 + (int)q;
@@ -424,6 +430,14 @@ int ChanEngine::build_items(const unsigned char* nz) {
     max_wblocks = std::max(max_wblocks, cur.wblocks);
     max_batch_items = std::max(max_batch_items, cur.item1 - cur.item0);
   };
+  auto make_groups = [&](std::vector<int4>& groups, int t_begin, int ni) {  // dense packing of a family's tiles into groups of <= ni items
+    for (int t = t_begin; t < (int)tiles2.size();) {
+      int e = t, n = 0;
+      while (e < (int)tiles2.size() && e - t < CHXF_TMAX && n + tiles2[e].y <= ni) n += tiles2[e++].y;
+      groups.push_back(make_int4(tiles2[t].x, n, t, e - t));
+      t = e;
+    }
+  };
   for (int r = 0; r < nr; r++) {
     long long wr = 0;
     for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
@@ -433,7 +447,7 @@ int ChanEngine::build_items(const unsigned char* nz) {
     if (nonempty && (cur.wblocks + wr > wcap || (long long)items.size() - cur.item0 + ir > icap)) {
       cur.t1_1 = fam_t1[r];
       close_batch();
-      cur = XBatch{fam_t1[r], fam_t1[r], (int)tiles2.size(), 0, (int)groups.size(), 0, (int)items.size(), 0, 0, 0, 0};
+      cur = XBatch{fam_t1[r], fam_t1[r], (int)tiles2.size(), 0, (int)groupsS.size(), 0, (int)groupsP.size(), 0, (int)items.size(), 0, 0, 0, 0};
     }
     for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
       for (int j = 0; j < nang; j++)
@@ -442,14 +456,15 @@ int ChanEngine::build_items(const unsigned char* nz) {
           cur.wblocks += wcount[(size_t)c * nang + j];
         }
     const std::vector<int2>& it = fam_items[r];
-    const int g0 = (int)items.size();
-    for (size_t q = 0; q < it.size();) {  // x2 tiles: <= CHX_T consecutive items with one j and one angular group of k
+    const int g0 = (int)items.size(), tb = (int)tiles2.size();
+    for (size_t q = 0; q < it.size();) {  // tiles: <= CHX_T consecutive items with one j and one angular group of k
       size_t e = q;
       while (e < it.size() && e - q < (size_t)CHX_T && it[e].x == it[q].x && ang_group[it[e].y] == ang_group[it[q].y]) e++;
       tiles2.push_back(make_int2(g0 + (int)q, (int)(e - q)));
       q = e;
     }
-    for (size_t q = 0; q < it.size(); q += x3_ni) groups.push_back(make_int2(g0 + (int)q, (int)std::min<size_t>(x3_ni, it.size() - q)));
+    make_groups(groupsS, tb, ni_same);
+    make_groups(groupsP, tb, ni_pair);
     items.insert(items.end(), it.begin(), it.end());
     item_fam.insert(item_fam.end(), it.size(), r);
     cur.t1_1 = fam_t1[r + 1];
@@ -457,10 +472,85 @@ int ChanEngine::build_items(const unsigned char* nz) {
   cur.t1_1 = fam_t1[nr];
   close_batch();
   total_items = (long long)items.size();
+
+  // ---- slot tables of the tiles (fused kernels): union of the W blocks (c, l) the tile's rows couple to, in
+  //      ascending (channel, l) order, and the dense coefficient table [slot][b][item of the tile] ----
+  const int ntile = (int)tiles2.size();
+  std::vector<int2> tile_u(ntile);
+  std::vector<std::vector<int>> tslots(ntile);
+#pragma omp parallel
+  {
+    std::vector<int> dom((size_t)std::max(nch_max, 1) * nang);
+#pragma omp for schedule(dynamic, 64)
+    for (int t = 0; t < ntile; t++) {
+      const int it0 = tiles2[t].x, nk = tiles2[t].y, j = items[it0].x, r = item_fam[it0];
+      const int c0 = fam_c0_host[r], nch = fam_c0_host[r + 1] - c0;
+      std::fill(dom.begin(), dom.begin() + (size_t)nch * nang, 0);
+      for (int kk = 0; kk < nk; kk++) {
+        const int k = items[it0 + kk].y;
+        for (int cl = 0; cl < nch; cl++) {
+          const size_t row = (size_t)(c0 + cl) * nang + k, jrow = (size_t)(c0 + cl) * nang + j;
+          const unsigned long long* bits = &wbits[jrow * nw];
+          for (int e = xrowptr[row]; e < xrowptr[row + 1]; e++) {
+            const int l = xrow_i[e];
+            if ((bits[l >> 6] >> (l & 63)) & 1ull) dom[(size_t)cl * nang + l] = 1;
+          }
+        }
+      }
+      for (int q = 0; q < nch * nang; q++)
+        if (dom[q]) tslots[t].push_back(q);
+    }
+  }
+  size_t nslots = 0;
+  for (int t = 0; t < ntile; t++) {
+    const int nu = ((int)tslots[t].size() + CHXF_SLOTS - 1) / CHXF_SLOTS * CHXF_SLOTS;
+    tile_u[t] = make_int2((int)nslots, nu);
+    nslots += nu;
+  }
+  if (nslots >= ((size_t)1 << 31)) { set_error("exchange: slot tables exceed 32-bit indexing"); return HFB200_EINVAL; }
+  std::vector<long long> slot_wblk(std::max<size_t>(nslots, 1), 0);
+  std::vector<double> slot_coef(std::max<size_t>(nslots, 1) * 16, 0.0);
+#pragma omp parallel
+  {
+    std::vector<int> slot_of((size_t)std::max(nch_max, 1) * nang);
+#pragma omp for schedule(dynamic, 64)
+    for (int t = 0; t < ntile; t++) {
+      const int it0 = tiles2[t].x, nk = tiles2[t].y, j = items[it0].x, r = item_fam[it0];
+      const int c0 = fam_c0_host[r], nch = fam_c0_host[r + 1] - c0;
+      const size_t u0 = (size_t)tile_u[t].x;
+      const std::vector<int>& sl = tslots[t];
+      for (size_t u = 0; u < sl.size(); u++) {
+        const int cl = sl[u] / nang, l = sl[u] - cl * nang;
+        const size_t jrow = (size_t)(c0 + cl) * nang + j;
+        const unsigned long long* bits = &wbits[jrow * nw];
+        long long idx = wbase[jrow];
+        for (int w = 0; w < (l >> 6); w++) idx += __builtin_popcountll(bits[w]);
+        idx += __builtin_popcountll(bits[l >> 6] & (((unsigned long long)1 << (l & 63)) - 1ull));
+        slot_wblk[u0 + u] = idx;
+        slot_of[sl[u]] = (int)u;
+      }
+      for (size_t u = sl.size(); u < (size_t)tile_u[t].y; u++) slot_wblk[u0 + u] = sl.empty() ? 0 : slot_wblk[u0];  // padding: zero coefficients
+      for (int kk = 0; kk < nk; kk++) {
+        const int k = items[it0 + kk].y;
+        for (int cl = 0; cl < nch; cl++) {
+          const size_t row = (size_t)(c0 + cl) * nang + k, jrow = (size_t)(c0 + cl) * nang + j;
+          const unsigned long long* bits = &wbits[jrow * nw];
+          for (int e = xrowptr[row]; e < xrowptr[row + 1]; e++) {
+            const int l = xrow_i[e];
+            if (!((bits[l >> 6] >> (l & 63)) & 1ull)) continue;
+            const size_t u = u0 + slot_of[(size_t)cl * nang + l];
+            slot_coef[u * 16 + kk] = xrow_coef[2 * (size_t)e];
+            slot_coef[u * 16 + 8 + kk] = xrow_coef[2 * (size_t)e + 1];
+          }
+        }
+      }
+    }
+  }
   int rc;
   if ((rc = up_list(dItems, items)) || (rc = up_list(dItemFam, item_fam)) || (rc = up_list(dTiles2, tiles2)) ||
-      (rc = up_list(dGroups, groups)) || (rc = up_list(dWbase, wbase)) || (rc = up_list(dWbits, wbits)) ||
-      (rc = up_list(dOutPtr, out_ptr)) || (rc = up_list(dOutItem, out_item)))
+      (rc = up_list(dGroupsS, groupsS)) || (rc = up_list(dGroupsP, groupsP)) || (rc = up_list(dTileU, tile_u)) ||
+      (rc = up_list(dSlotWblk, slot_wblk)) || (rc = up_list(dSlotCoef, slot_coef)) || (rc = up_list(dWbase, wbase)) ||
+      (rc = up_list(dWbits, wbits)) || (rc = up_list(dOutPtr, out_ptr)) || (rc = up_list(dOutItem, out_item)))
     return rc;
   return 0;
 }
@@ -533,27 +623,24 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
 }
 
 namespace {
-template <int NI, int NTL, bool OFFD>
-int launch_x3_one(const ChanXParams& q, const int2* groups, int ngroups, size_t smem, cudaStream_t st) {
-  // per launch: the attribute belongs to the current device's context (one process can hold contexts on several GPUs)
-  HFB_CUDA_OK(cudaFuncSetAttribute(chan_x3_kernel<NI, NTL, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  const int ny = OFFD ? q.nel * (q.nel - 1) : q.nel;
-  if (ny == 0) return 0;
-  chan_x3_kernel<NI, NTL, OFFD><<<dim3(ngroups, ny), 256, smem, st>>>(q, groups);
+// the max-dynamic-shared-memory attribute is set per launch: it belongs to the current device's context (one process can
+// hold contexts on several GPUs)
+template <int NI>
+int launch_xf_same(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, cudaStream_t st) {
+  const size_t smem = ((size_t)NI * q.LDK + chxf_ring_doubles(q.PB)) * sizeof(double);
+  HFB_CUDA_OK(cudaFuncSetAttribute(chan_xf_same_kernel<NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  chan_xf_same_kernel<NI><<<dim3(ngroups, q.nel), 256, smem, st>>>(q, groups, tiles);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }
-template <int NI>
-int launch_x3(const ChanXParams& q, const int2* groups, int ngroups, size_t smem_d, size_t smem_o, cudaStream_t st) {
-  const int ntl = (q.np + 7) / 8;
-  int rc;
-  if ((rc = launch_x3_one<NI, 1, false>(q, groups, ngroups, smem_d, st))) return rc;  // the same-element path does not depend on NTL
-  switch (ntl) {
-    case 1: return launch_x3_one<NI, 1, true>(q, groups, ngroups, smem_o, st);
-    case 2: return launch_x3_one<NI, 2, true>(q, groups, ngroups, smem_o, st);
-    case 3: return launch_x3_one<NI, 3, true>(q, groups, ngroups, smem_o, st);
-    default: return launch_x3_one<NI, 4, true>(q, groups, ngroups, smem_o, st);
-  }
+template <int NI, int NTL>
+int launch_xf_pair(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, cudaStream_t st) {
+  if (q.nel < 2) return 0;
+  const size_t smem = ((size_t)NI * q.stack * ChxfPair<NTL>::RS + std::max(chxf_ring_doubles(q.PB), (size_t)8 * ChxfPair<NTL>::YS)) * sizeof(double);
+  HFB_CUDA_OK(cudaFuncSetAttribute(chan_xf_pair_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  chan_xf_pair_kernel<NI, NTL><<<dim3(ngroups, q.nel * (q.nel - 1)), 256, smem, st>>>(q, groups, tiles);
+  HFB_CUDA_OK(cudaGetLastError());
+  return 0;
 }
 }  // namespace
 
@@ -658,9 +745,9 @@ int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cud
 
 int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ldkm, cudaStream_t st) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack, st2 = stack * stack;
+  const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack;
   if ((size_t)ldpm * (size_t)ntot >= ((size_t)1 << 32)) { set_error("exchange: density matrix too large for 32-bit block offsets"); return HFB200_EINVAL; }
-  const size_t nang2 = (size_t)nang * nang, nrad2 = (size_t)nrad * nrad;
+  const size_t nang2 = (size_t)nang * nang;
   int rc;
   HFB_CUDA_OK(cudaMemset2DAsync(dKm, (size_t)ldkm * sizeof(double), 0, (size_t)ntot * sizeof(double), ntot, st));
   size_t ev_used = 0;
@@ -671,71 +758,79 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     if (begin) ev_marks.push_back({stage, ev_used});
     cudaEventRecord(ev_pool[ev_used++], st);
   };
-  // block mask of P; the per-pattern lists are rebuilt only when the sparsity pattern changes
+  // block mask of P and its exact-symmetry flag; the per-pattern lists are rebuilt only when either changes
+  static const bool allow_sym = getenv("HFB200_X_NOSYM") == nullptr;
   tick(0, true);
-  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP);
+  HFB_CUDA_OK(cudaMemsetAsync(dNzP + nang2, allow_sym ? 1 : 0, 1, st));
+  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP, allow_sym ? dNzP + nang2 : nullptr);
   tick(0, false);
   HFB_CUDA_OK(cudaGetLastError());
-  HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2, cudaMemcpyDeviceToHost, st));
+  HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2 + 1, cudaMemcpyDeviceToHost, st));
   HFB_CUDA_OK(cudaStreamSynchronize(st));
-  if (mask_cached.size() != nang2 || memcmp(mask_cached.data(), hNzP, nang2) != 0) {
-    if ((rc = build_items(hNzP))) return rc;
-    mask_cached.assign(hNzP, hNzP + nang2);
+  if (mask_cached.size() != nang2 + 1 || memcmp(mask_cached.data(), hNzP, nang2 + 1) != 0) {
+    if ((rc = build_items(hNzP, hNzP[nang2] != 0))) return rc;
+    mask_cached.assign(hNzP, hNzP + nang2 + 1);
   }
+  last_sym = hNzP[nang2] != 0;
   last_items = total_items;
   if (total_items > 0) {
-    const size_t need_r = (size_t)max_batch_items * st2 * nel * nel * np2;
-    if (need_r >= ((size_t)1 << 32)) { set_error("exchange: a family batch of %d output blocks exceeds the 32-bit offsets of its workspace", max_batch_items); return HFB200_EINVAL; }
-    if (need_r > dRsub.cap) {
-      if ((rc = dRsub.reserve(need_r))) return rc;
-      HFB_CUDA_OK(cudaMemsetAsync(dRsub.p, 0, need_r * sizeof(double), st));  // padding positions stay zero for good
-    }
     if ((rc = dKblocks.reserve((size_t)max_batch_items * nel * nel * np2)) ||
-        (rc = dW.reserve((size_t)std::max<long long>(max_wblocks, 1) * stack * nrad2)))
+        (rc = dW.reserve((size_t)std::max<long long>(max_wblocks, 1) * stack * xprm.WB)))
       return rc;
+    if (x1tab_ldp != ldpm) {  // W index (element pair, i, l) -> offset inside an angular block of the dense P
+      std::vector<unsigned> tab((size_t)xprm.WB, 0xffffffffu);
+      const int np = prm.np;
+      for (int ie = 0; ie < nel; ie++)
+        for (int je = 0; je < nel; je++)
+          for (int l = 0; l <= last[je] - first[je]; l++)
+            for (int i = 0; i <= last[ie] - first[ie]; i++)
+              tab[(size_t)(ie * nel + je) * xprm.PB + i + l * np] = (unsigned)(first[ie] + i) + (unsigned)(first[je] + l) * (unsigned)ldpm;
+      if ((rc = up_list(dX1tab, tab))) return rc;
+      x1tab_ldp = ldpm;
+    }
     ChanXParams q = xprm;
-    q.P = dPm; q.ldp = ldpm; q.nzP = dNzP; q.W = dW.p; q.Rsub = dRsub.p; q.blocks = dKblocks.p; q.K = dKm; q.ldk = ldkm;
+    q.P = dPm; q.ldp = ldpm; q.nzP = dNzP; q.W = dW.p; q.blocks = dKblocks.p; q.K = dKm; q.ldk = ldkm;
+    q.x1tab = (const unsigned*)dX1tab.p;
     q.fam_c0 = prm.fam_c0; q.fam_fac = dFamFac; q.items = (const int2*)dItems.p; q.item_fam = (const int*)dItemFam.p;
     q.wbase = (const long long*)dWbase.p; q.wbits = (const unsigned long long*)dWbits.p; q.nw = (nang + 63) / 64;
-    const int ntl = (prm.np + 7) / 8, NI = x3_ni;
-    const size_t ybytes = (size_t)8 * 8 * ntl * ((8 * ntl + 15) / 16 * 16 + 4) * sizeof(double);  // per-warp Y tiles of x3 (pairs)
-    const size_t smem3 = (size_t)NI * q.LDK * sizeof(double);
-    if (smem3 > 227 * 1024 || ybytes > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
-    const int nchunk = (int)((nrad2 + 255) / 256);
+    q.tile_u = (const int2*)dTileU.p; q.slot_wblk = (const long long*)dSlotWblk.p; q.slot_coef = (const double*)dSlotCoef.p;
+    q.sym = last_sym ? 1 : 0;
+    const int ntl = (prm.np + 7) / 8;
+    if (((size_t)ni_same * q.LDK + chxf_ring_doubles(q.PB)) * sizeof(double) > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const size_t smem1 = (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + 8 * CHX_T * sizeof(long long) +
                          (size_t)(2 * nang + 16 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)2 * nang;
-    const size_t smem2 = (size_t)2 * CHX_UMAX * CHX_LDC * sizeof(double) + CHX_UMAX * sizeof(size_t) + (size_t)2 * nch_max * nang * sizeof(int) +
-                         (size_t)8 * CHX_X2_STAGES * 128 * sizeof(double);
-    if (smem1 > 48 * 1024 || smem2 > 48 * 1024) {
-      if (smem1 > 227 * 1024 || smem2 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
-      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-      HFB_CUDA_OK(cudaFuncSetAttribute(chan_x2_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-    }
+    if (smem1 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
+    HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem1, 48 * 1024)));
+    const int2* tiles = (const int2*)dTiles2.p;
     for (const XBatch& B : batches) {
       q.item0 = B.item0;
-      const int nt1 = B.t1_1 - B.t1_0, nt2 = B.t2_1 - B.t2_0, ng = B.g1 - B.g0;
+      const int nt1 = B.t1_1 - B.t1_0, ngs = B.gs1 - B.gs0, ngp = B.gp1 - B.gp0;
       if (nt1 > 0 && B.wblocks > 0) {
         tick(1, true);
         chan_x1_mma_kernel<<<dim3(nt1, std::min(nang, 7)), 256, smem1, st>>>(q, dTiles1 + (size_t)B.t1_0 * (2 + CHX_T));
         HFB_CUDA_OK(cudaGetLastError());
         tick(1, false);
       }
-      if (nt2 == 0) continue;
+      if (ngs == 0) continue;
       tick(2, true);
-      const int ny2 = std::max(1, std::min(nchunk, 2368 / std::max(nt2, 1)));
-      chan_x2_mma_kernel<<<dim3(nt2, ny2, stack), 256, smem2, st>>>(q, (const int2*)dTiles2.p + B.t2_0, nch_max);
-      HFB_CUDA_OK(cudaGetLastError());
+      const int4* gS = (const int4*)dGroupsS.p + B.gs0;
+      if (ni_same == 32) rc = launch_xf_same<32>(q, gS, ngs, tiles, st);
+      else if (ni_same == 16) rc = launch_xf_same<16>(q, gS, ngs, tiles, st);
+      else rc = launch_xf_same<8>(q, gS, ngs, tiles, st);
+      if (rc) return rc;
       tick(2, false);
       tick(3, true);
-      if (NI == 32) rc = launch_x3<32>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
-      else if (NI == 16) rc = launch_x3<16>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
-      else rc = launch_x3<8>(q, (const int2*)dGroups.p + B.g0, ng, smem3, ybytes, st);
+      const int4* gP = (const int4*)dGroupsP.p + B.gp0;
+      switch (ntl) {
+        case 1: rc = launch_xf_pair<8, 1>(q, gP, ngp, tiles, st); break;
+        case 2: rc = launch_xf_pair<8, 2>(q, gP, ngp, tiles, st); break;
+        case 3: rc = launch_xf_pair<4, 3>(q, gP, ngp, tiles, st); break;
+        default: rc = launch_xf_pair<4, 4>(q, gP, ngp, tiles, st); break;
+      }
       if (rc) return rc;
       tick(3, false);
       tick(4, true);
-      const size_t work = (size_t)B.nout * nrad2;
-      chan_x4_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(q, (const int*)dOutPtr.p + B.out0,
-                                                                                              (const int*)dOutItem.p, B.nout);
+      chan_x4_kernel<<<(unsigned)std::min(B.nout, 148 * 8), 256, 0, st>>>(q, (const int*)dOutPtr.p + B.out0, (const int*)dOutItem.p, B.nout);
       HFB_CUDA_OK(cudaGetLastError());
       tick(4, false);
     }
@@ -749,16 +844,20 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       }
     }
   }
-  // algorithmic flops of the radial contraction (x3) per output block and family: same-element products
-  // 2 np_e^4 and two (np x np x np) products per ordered pair of different elements, per stack combination
+  // algorithmic flops of the radial contraction per output block and family: same-element products 2 np_e^4 and two
+  // (np x np x np) products per ordered pair of different elements, per stack combination.  The count is that of the
+  // FULL item list (both (j,k) and (k,j)): with a symmetric P the engine computes half of them and mirrors the rest,
+  // so last_items is the number of blocks actually contracted and last_x3_flops the work actually executed.
   {
-    double per = 0.0;
+    double per = 0.0, per_same = 0.0;
     for (int a = 0; a < nel; a++)
       for (int b = 0; b < nel; b++) {
         const double na = last[a] - first[a] + 1, nb = last[b] - first[b] + 1;
         per += (a == b) ? 2.0 * na * na * na * na : 2.0 * na * na * nb + 2.0 * na * nb * nb;
+        if (a == b) per_same += 2.0 * na * na * na * na;
       }
-    last_x3_flops = per * st2 * (double)last_items;
+    last_x3_flops = per * stack * stack * (double)last_items;
+    last_same_flops = per_same * stack * stack * (double)last_items;
   }
   return 0;
 }
@@ -766,8 +865,8 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
 void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
-  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRsub}) b->release();
-  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroups, &dWbase, &dWbits, &dOutPtr, &dOutItem}) {
+  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW}) b->release();
+  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab}) {
     if (L->p) cudaFree(L->p);
     L->p = nullptr;
     L->cap = 0;

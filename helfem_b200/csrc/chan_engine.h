@@ -4,6 +4,7 @@
 #include <functional>
 #include <vector>
 #include "chan_exchange.cuh"
+#include "chan_exchange_fused.cuh"
 #include "chan_kernels.cuh"
 #include "context.h"
 
@@ -44,26 +45,30 @@ struct ChanEngine {
   // exchange tables (chan_exchange.cuh)
   bool have_k = false;
   ChanXParams xprm{};
-  int nch_max = 0, x3_ni = 32;
+  int nch_max = 0;
   std::vector<double> fam_fac;                      // [nr]
   std::vector<int> xrowptr, xrow_i;                 // host copy of the coupling rows (item lists are derived from them)
+  std::vector<double> xrow_coef;                    // [nnz][2]
   std::vector<int> fam_rows;                        // [nr] non-empty coupling rows of each family
   // per sparsity pattern of P (build_items): output blocks of every family, compact W layout, tiles, batches
   std::vector<unsigned char> mask_cached;
-  struct XBatch { int t1_0, t1_1, t2_0, t2_1, g0, g1, item0, item1, out0, nout; long long wblocks; };
+  struct XBatch { int t1_0, t1_1, t2_0, t2_1, gs0, gs1, gp0, gp1, item0, item1, out0, nout; long long wblocks; };
   std::vector<XBatch> batches;
   long long total_items = 0, max_wblocks = 0;
   int max_batch_items = 0;
   struct DevList { void* p = nullptr; size_t cap = 0; };
-  DevList dItems, dItemFam, dTiles2, dGroups, dWbase, dWbits, dOutPtr, dOutItem;
+  DevList dItems, dItemFam, dTiles2, dGroupsS, dGroupsP, dTileU, dSlotWblk, dSlotCoef, dWbase, dWbits, dOutPtr, dOutItem, dX1tab;
+  int x1tab_ldp = -1;                               // leading dimension dX1tab was built for
+  int ni_same = 32, ni_pair = 16;                   // items per CTA of the fused same-element / element-pair kernels
+  bool last_sym = false;                            // the last exchange call used the symmetric (j <= k) item list
   const double* dFamFac = nullptr;
   std::vector<int> fam_t1;                          // [nr+1] x1 tiles of each family in dTiles1 ([c, nj, j x CHX_T] each)
   int* dTiles1 = nullptr;
   std::vector<int> ang_group;                       // [nang]
   unsigned char *dNzP = nullptr, *hNzP = nullptr;
-  DevBuf dPdense, dKdense, dKblocks, dW, dRsub;
+  DevBuf dPdense, dKdense, dKblocks, dW;
 
-  int build_items(const unsigned char* nz);
+  int build_items(const unsigned char* nz, bool sym);
   int build_exchange(const ChanSpec& spec);
   int build(const ChanSpec& spec, bool with_exchange);
   // dense HOST matrices; map (optional, length nang*nrad): operator index -> row/column of the caller's nout x nout
@@ -79,7 +84,7 @@ struct ChanEngine {
   // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
   long long last_items = 0;
   int nbatches() const { return (int)batches.size(); }
-  double last_x3_flops = 0.0;
+  double last_x3_flops = 0.0, last_same_flops = 0.0;
   // optional per-stage device timing of exchange_device (x0 mask, x1, x2, x3, x4), summed over families
   bool profile_stages = false;
   float stage_ms[5] = {0, 0, 0, 0, 0};
