@@ -66,7 +66,11 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   ChanSpec S;
   S.nel = c->nel; S.nang = nang; S.stack = 1; S.nr = nL;
   S.first = c->first; S.last = c->last;
-  S.ang_group = c->mval;
+  // tiling hint of the exchange contractions: functions with equal m AND equal parity of l couple to the same partners
+  // (a Gaunt or cos^2-modified Gaunt coefficient <l_j m_j| L M |l_i m_i> vanishes unless l_j + L + l_i is even), so a
+  // tile of such rows / items has a dense coefficient table instead of a checkerboard
+  S.ang_group.resize(nang);
+  for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.fac.resize(nL);
   for (int L = 0; L < nL; L++) S.fac[L] = 4.0 * M_PI / (2 * L + 1);
   // channels (L, M), sorted by L (atomic/TwoDBasis.cpp:836-842)

@@ -87,7 +87,11 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   ChanSpec S;
   S.nel = nel; S.nang = nang; S.stack = 2; S.nr = nlm;
   S.first = c->first; S.last = c->last;
-  S.ang_group = c->mval;
+  // tiling hint of the exchange contractions: functions with equal m AND equal parity of l couple to the same partners
+  // (a Gaunt or cos^2-modified Gaunt coefficient <l_j m_j| L M |l_i m_i> vanishes unless l_j + L + l_i is even), so a
+  // tile of such rows / items has a dense coefficient table instead of a checkerboard
+  S.ang_group.resize(nang);
+  for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.fac.resize(nlm);
   for (int r = 0; r < nlm; r++) {
     // LMfac = 4 pi Rh^5 (-1)^M (L-|M|)!/(L+|M|)!   (basis.cpp:1421)

@@ -291,7 +291,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
   if ((rc = up(this, &dFamFac, fam_fac))) return rc;
   // items per CTA of the fused kernels: as many as the shared-memory tiles allow with two CTAs per SM
   ni_same = 32;
-  while (ni_same > 8 && ((size_t)ni_same * xprm.LDK + chxf_ring_doubles(xprm.PB)) * sizeof(double) > 110 * 1024) ni_same >>= 1;
+  while (ni_same > 8 && ((size_t)ni_same * xprm.LDK + chxf_inline_ring_doubles(xprm.PB)) * sizeof(double) > 110 * 1024) ni_same >>= 1;
   ni_pair = (np <= 16) ? 8 : 4;
   mask_cached.clear();
   have_k = true;
@@ -546,6 +546,15 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
       }
     }
   }
+  if (getenv("HFB200_X_VERBOSE")) {
+    long long wtot = 0;
+    for (const XBatch& B : batches) wtot += B.wblocks;
+    size_t real = 0;
+    for (int t = 0; t < ntile; t++) real += tslots[t].size();
+    fprintf(stderr, "[hfb200] exchange lists: sym %d, items %lld, tiles %d, slots %zu (padded %zu), groups %zu / %zu, W blocks %lld (%.1f GB), "
+            "batches %zu\n", (int)sym, total_items, ntile, real, nslots, groupsS.size(), groupsP.size(), wtot,
+            (double)wtot * st * xprm.WB * 8e-9, batches.size());
+  }
   int rc;
   if ((rc = up_list(dItems, items)) || (rc = up_list(dItemFam, item_fam)) || (rc = up_list(dTiles2, tiles2)) ||
       (rc = up_list(dGroupsS, groupsS)) || (rc = up_list(dGroupsP, groupsP)) || (rc = up_list(dTileU, tile_u)) ||
@@ -626,19 +635,21 @@ namespace {
 // the max-dynamic-shared-memory attribute is set per launch: it belongs to the current device's context (one process can
 // hold contexts on several GPUs)
 template <int NI>
-int launch_xf_same(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, cudaStream_t st) {
-  const size_t smem = ((size_t)NI * q.LDK + chxf_ring_doubles(q.PB)) * sizeof(double);
+int launch_xf_same(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, int nsm, cudaStream_t st) {
+  (void)nsm;
+  const size_t smem = ((size_t)NI * q.LDK + chxf_inline_ring_doubles(q.PB)) * sizeof(double);
   HFB_CUDA_OK(cudaFuncSetAttribute(chan_xf_same_kernel<NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   chan_xf_same_kernel<NI><<<dim3(ngroups, q.nel), 256, smem, st>>>(q, groups, tiles);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }
 template <int NI, int NTL>
-int launch_xf_pair(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, cudaStream_t st) {
+int launch_xf_pair(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, int nsm, cudaStream_t st) {
   if (q.nel < 2) return 0;
-  const size_t smem = ((size_t)NI * q.stack * ChxfPair<NTL>::RS + std::max(chxf_ring_doubles(q.PB), (size_t)8 * ChxfPair<NTL>::YS)) * sizeof(double);
+  const size_t smem = ((size_t)NI * q.stack * ChxfPair<NTL>::RS + (size_t)8 * ChxfPair<NTL>::YS + chxf_ring_doubles(q.PB)) * sizeof(double);
   HFB_CUDA_OK(cudaFuncSetAttribute(chan_xf_pair_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  chan_xf_pair_kernel<NI, NTL><<<dim3(ngroups, q.nel * (q.nel - 1)), 256, smem, st>>>(q, groups, tiles);
+  const long long units = (long long)ngroups * q.nel * (q.nel - 1);
+  chan_xf_pair_kernel<NI, NTL><<<(unsigned)std::min<long long>(units, (NTL <= 2 ? 2LL : 1LL) * nsm), CHXF_THREADS, smem, st>>>(q, groups, ngroups, tiles);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -796,12 +807,15 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
     q.tile_u = (const int2*)dTileU.p; q.slot_wblk = (const long long*)dSlotWblk.p; q.slot_coef = (const double*)dSlotCoef.p;
     q.sym = last_sym ? 1 : 0;
     const int ntl = (prm.np + 7) / 8;
-    if (((size_t)ni_same * q.LDK + chxf_ring_doubles(q.PB)) * sizeof(double) > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
+    if (((size_t)ni_same * q.LDK + chxf_inline_ring_doubles(q.PB)) * sizeof(double) > 227 * 1024) { set_error("exchange: element block too large for the shared-memory tile"); return HFB200_EINVAL; }
     const size_t smem1 = (size_t)2 * (CHX_UMAX + 1) * CHX_LDC * sizeof(double) + 8 * CHX_T * sizeof(long long) +
                          (size_t)(2 * nang + 16 * (CHX_UMAX + 4)) * sizeof(int) + (size_t)2 * nang;
     if (smem1 > 227 * 1024) { set_error("exchange: angular basis too large for the shared-memory coupling tables"); return HFB200_EINVAL; }
     HFB_CUDA_OK(cudaFuncSetAttribute(chan_x1_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem1, 48 * 1024)));
     const int2* tiles = (const int2*)dTiles2.p;
+    int nsm = 148, dev = 0;
+    HFB_CUDA_OK(cudaGetDevice(&dev));
+    HFB_CUDA_OK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
     for (const XBatch& B : batches) {
       q.item0 = B.item0;
       const int nt1 = B.t1_1 - B.t1_0, ngs = B.gs1 - B.gs0, ngp = B.gp1 - B.gp0;
@@ -814,18 +828,18 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       if (ngs == 0) continue;
       tick(2, true);
       const int4* gS = (const int4*)dGroupsS.p + B.gs0;
-      if (ni_same == 32) rc = launch_xf_same<32>(q, gS, ngs, tiles, st);
-      else if (ni_same == 16) rc = launch_xf_same<16>(q, gS, ngs, tiles, st);
-      else rc = launch_xf_same<8>(q, gS, ngs, tiles, st);
+      if (ni_same == 32) rc = launch_xf_same<32>(q, gS, ngs, tiles, nsm, st);
+      else if (ni_same == 16) rc = launch_xf_same<16>(q, gS, ngs, tiles, nsm, st);
+      else rc = launch_xf_same<8>(q, gS, ngs, tiles, nsm, st);
       if (rc) return rc;
       tick(2, false);
       tick(3, true);
       const int4* gP = (const int4*)dGroupsP.p + B.gp0;
       switch (ntl) {
-        case 1: rc = launch_xf_pair<8, 1>(q, gP, ngp, tiles, st); break;
-        case 2: rc = launch_xf_pair<8, 2>(q, gP, ngp, tiles, st); break;
-        case 3: rc = launch_xf_pair<4, 3>(q, gP, ngp, tiles, st); break;
-        default: rc = launch_xf_pair<4, 4>(q, gP, ngp, tiles, st); break;
+        case 1: rc = launch_xf_pair<8, 1>(q, gP, ngp, tiles, nsm, st); break;
+        case 2: rc = launch_xf_pair<8, 2>(q, gP, ngp, tiles, nsm, st); break;
+        case 3: rc = launch_xf_pair<4, 3>(q, gP, ngp, tiles, nsm, st); break;
+        default: rc = launch_xf_pair<4, 4>(q, gP, ngp, tiles, nsm, st); break;
       }
       if (rc) return rc;
       tick(3, false);

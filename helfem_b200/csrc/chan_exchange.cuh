@@ -300,23 +300,47 @@ static __global__ void __launch_bounds__(256) chan_x4_kernel(ChanXParams prm, co
     for (int tb = 0; tb < ntile; tb++)
       for (int ta = 0; ta < ntile; ta++) {
         const int a = ta * 32 + tx;
-        for (int yy = ty; yy < 32; yy += 8) {
-          const int b = tb * 32 + yy;
-          double s = 0.0;
+        // this thread's four elements (a, b_v), b_v = 32 tb + ty + 8 v.  Every element has a first home (the sub-block of the
+        // first elements its row and column belong to); rows / columns on an element boundary have up to three more.  One
+        // pass over the items with the four first-home loads independent of each other, the rare extra homes afterwards.
+        int off0[4];
+        bool extra = false;
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          const int b = tb * 32 + ty + 8 * v;
+          off0[v] = -1;
           if (a < nrad && b < nrad) {
-            for (int x = 0; x < 2; x++) {
-              const int ie = prm.elem_of[2 * a + x];
-              if (ie < 0) continue;
-              for (int y = 0; y < 2; y++) {
-                const int je = prm.elem_of[2 * b + y];
-                if (je < 0) continue;
-                const size_t off = (size_t)(ie * nel + je) * np2 + (a - prm.first[ie]) + (b - prm.first[je]) * np;
-                for (int q = q0; q < q1; q++) s += prm.blocks[(size_t)(out_item[q] - prm.item0) * nel2 * np2 + off];
-              }
-            }
-            prm.K[(size_t)(jk.x * nrad + a) + (size_t)(jk.y * nrad + b) * prm.ldk] -= s;
+            const int ie = prm.elem_of[2 * a], je = prm.elem_of[2 * b];
+            off0[v] = (ie * nel + je) * np2 + (a - prm.first[ie]) + (b - prm.first[je]) * np;
+            extra = extra || prm.elem_of[2 * a + 1] >= 0 || prm.elem_of[2 * b + 1] >= 0;
           }
-          tile[yy][tx] = s;
+        }
+        double s[4] = {0.0, 0.0, 0.0, 0.0};
+        const size_t istride = (size_t)nel2 * np2;
+        for (int q = q0; q < q1; q++) {
+          const double* Bq = prm.blocks + (size_t)(out_item[q] - prm.item0) * istride;
+#pragma unroll
+          for (int v = 0; v < 4; v++)
+            if (off0[v] >= 0) s[v] += Bq[off0[v]];
+        }
+        if (extra) {
+#pragma unroll
+          for (int v = 0; v < 4; v++) {
+            const int b = tb * 32 + ty + 8 * v;
+            if (a >= nrad || b >= nrad) continue;
+            for (int h = 1; h < 4; h++) {
+              const int ie = prm.elem_of[2 * a + (h >> 1)], je = prm.elem_of[2 * b + (h & 1)];
+              if (ie < 0 || je < 0) continue;
+              const int o = (ie * nel + je) * np2 + (a - prm.first[ie]) + (b - prm.first[je]) * np;
+              for (int q = q0; q < q1; q++) s[v] += prm.blocks[(size_t)(out_item[q] - prm.item0) * istride + o];
+            }
+          }
+        }
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          const int b = tb * 32 + ty + 8 * v;
+          if (a < nrad && b < nrad) prm.K[(size_t)(jk.x * nrad + a) + (size_t)(jk.y * nrad + b) * prm.ldk] -= s[v];
+          tile[ty + 8 * v][tx] = s[v];
         }
         if (mirror) {  // block-uniform
           __syncthreads();

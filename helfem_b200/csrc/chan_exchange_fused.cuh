@@ -27,11 +27,15 @@
 namespace hfb {
 
 constexpr int CHXF_TMAX = 16;  // tiles per group (a group closes at NI items or CHXF_TMAX tiles)
-constexpr int CHXF_SLOTS = 8;  // W sub-blocks per pipeline stage (two DMMA k-steps); the host pads every tile's slot count to it
-#ifndef HFB_XF_STAGES
-#define HFB_XF_STAGES 3
+#ifndef HFB_XF_SLOTS
+#define HFB_XF_SLOTS 4
 #endif
-constexpr int CHXF_STAGES = HFB_XF_STAGES;
+#ifndef HFB_XF_STAGES
+#define HFB_XF_STAGES 6
+#endif
+constexpr int CHXF_SLOTS = HFB_XF_SLOTS;    // W sub-blocks per pipeline stage (a multiple of 4 = one DMMA k-step); the host pads every tile's slot count to it
+constexpr int CHXF_STAGES = HFB_XF_STAGES;  // stages of the bulk-copy ring
+constexpr int CHXF_THREADS = 288;           // 8 consumer warps + 1 producer warp
 
 // Rows of the (np x np) sub-block a CTA fetches per sweep (32 m-tiles of 8 rows), and the stage geometry: every slot of a
 // stage owns PBS doubles, PBS = 4 (mod 16) so that the DMMA A-fragment read (slot 4 ks + t4, row 8 mt + gid) is
@@ -39,6 +43,7 @@ constexpr int CHXF_STAGES = HFB_XF_STAGES;
 __host__ __device__ inline int chxf_rows(int PB) { return PB < 256 ? PB : 256; }
 __host__ __device__ inline int chxf_pbs(int PB) { return (chxf_rows(PB) - 4 + 15) / 16 * 16 + 4; }
 __host__ __device__ inline size_t chxf_ring_doubles(int PB) { return (size_t)CHXF_STAGES * CHXF_SLOTS * chxf_pbs(PB); }
+__host__ __device__ inline size_t chxf_inline_ring_doubles(int PB) { return chxf_ring_doubles(PB); }
 
 // ---- mbarrier / bulk-copy primitives (PTX) ----
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
@@ -68,15 +73,113 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                    (unsigned)__cvta_generic_to_shared(dst)),
                "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
+// barrier of the 8 consumer warps only (the producer warp never joins it)
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-// Pipeline state that survives from one phase-1 call of a kernel to the next (the barriers keep their phases).
+// The fused kernels are PERSISTENT and WARP-SPECIALISED.  A CTA walks through work units u = blockIdx.x, + gridDim.x, ...
+// (unit = group of tiles x element pair).  Warp 8 is the PRODUCER: one lane issues, for every unit, stack half and tile in
+// the order the consumers will need them, one BULK COPY (cp.async.bulk, the TMA engine) per W sub-block -- W is stored
+// element pair by element pair, so a sub-block is one contiguous run -- into a ring of CHXF_STAGES stages of CHXF_SLOTS
+// sub-blocks; a stage's `full` mbarrier completes by byte count, its `empty` mbarrier when the 8 consumer warps have
+// arrived.  The producer is only ever held back by `empty`, so it runs ahead ACROSS phases and units: while the
+// consumers multiply (phase 2) the first stages of their next angular contraction (phase 1) are already landing.
 struct ChxfPipe {
+  unsigned long long* full;   // [CHXF_STAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
+  unsigned long long* empty;  // [CHXF_STAGES]  all 8 consumer warps are done with it (8 arrivals)
+  int stage = 0;
+  unsigned phase = 0;
+  __device__ __forceinline__ void advance() {
+    if (++stage == CHXF_STAGES) { stage = 0; phase ^= 1u; }
+  }
+};
+__device__ __forceinline__ void chxf_pipe_init(ChxfPipe& pipe, unsigned long long* bars) {
+  pipe.full = bars;
+  pipe.empty = bars + CHXF_STAGES;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < CHXF_STAGES; s++) { mbar_init(pipe.full + s, 1); mbar_init(pipe.empty + s, 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+}
+
+// Producer side of one phase-1 pass over the slots [s_begin, s_end) (the slots of a group's tiles are consecutive and every
+// tile's count is a multiple of CHXF_SLOTS, so a stage never straddles tiles), rows [k0, k0 + 256) of sub-block `pair`, stack
+// half a (Wa = W + a WB).  Called by the whole producer WARP: lane q < CHXF_SLOTS fetches slot q of every stage; the block
+// number of the next stage's slot is requested before the wait on the current stage's `empty` barrier.
+__device__ __forceinline__ void chxf_produce(const ChanXParams& prm, ChxfPipe& pipe, const double* __restrict__ Wa, int s_begin, int s_end,
+                                             int pair, int k0, double* ring) {
+  const int lane = threadIdx.x & 31;
+  const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: 64-byte multiples
+  const size_t wstride = (size_t)prm.stack * prm.WB;
+  const double* src0 = Wa + (size_t)pair * PB + k0;
+  const unsigned bytes = (unsigned)rows * 8u;
+  long long wb = (lane < CHXF_SLOTS && s_begin < s_end) ? __ldg(prm.slot_wblk + s_begin + lane) : 0;
+  for (int s0 = s_begin; s0 < s_end; s0 += CHXF_SLOTS) {
+    const long long wb_next = (lane < CHXF_SLOTS && s0 + CHXF_SLOTS < s_end) ? __ldg(prm.slot_wblk + s0 + CHXF_SLOTS + lane) : 0;
+    if (lane == 0) {
+      mbar_wait(pipe.empty + pipe.stage, pipe.phase ^ 1u);  // passes at once on the first trip round the ring
+      mbar_expect_tx(pipe.full + pipe.stage, bytes * CHXF_SLOTS);
+    }
+    __syncwarp();
+    if (lane < CHXF_SLOTS)
+      bulk_g2s(ring + (size_t)(pipe.stage * CHXF_SLOTS + lane) * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pipe.stage);
+    wb = wb_next;
+    pipe.advance();
+  }
+}
+
+// Consumer side of the same pass (all 8 consumer warps):   R[row][item] = sum_slots W^a_slot[row] coef^b[slot][item]
+// (b = b0 .. b0 + NB - 1) as a DMMA GEMM (M = rows, N = the tile's 8 items, K = slots).  Warp w owns the m-tiles w, w + 8,
+// w + 16, w + 24; `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt after the
+// tile's last stage.  sU: the tiles' (first slot, slot count).
+template <int NB, class Emit>
+__device__ __forceinline__ void chxf_consume(const ChanXParams& prm, ChxfPipe& pipe, const int2* sU, int ntl, int k0, int b0, const double* ring, Emit emit) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
+  const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);
+  for (int tt = 0; tt < ntl; tt++) {
+    const int2 U = sU[tt];  // (first slot, slot count) of the tile, staged in shared memory by the caller
+    double acc[4][NB][2];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+      for (int b = 0; b < NB; b++) { acc[mi][b][0] = 0.0; acc[mi][b][1] = 0.0; }
+    for (int s0 = 0; s0 < U.y; s0 += CHXF_SLOTS) {
+      double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments: requested before the wait
+#pragma unroll
+      for (int ks = 0; ks < CHXF_SLOTS / 4; ks++)
+#pragma unroll
+        for (int b = 0; b < NB; b++) bf[ks][b] = __ldg(prm.slot_coef + (size_t)(U.x + s0 + 4 * ks + t4) * 16 + (b0 + b) * 8 + gid);
+      mbar_wait(pipe.full + pipe.stage, pipe.phase);
+      const double* S = ring + (size_t)(pipe.stage * CHXF_SLOTS) * PBS + gid;
+#pragma unroll
+      for (int ks = 0; ks < CHXF_SLOTS / 4; ks++) {
+#pragma unroll
+        for (int mi = 0; mi < 4; mi++) {
+          if (8 * (warp + 8 * mi) < rows) {  // warp-uniform
+            const double af = S[(4 * ks + t4) * PBS + 8 * (warp + 8 * mi)];
+#pragma unroll
+            for (int b = 0; b < NB; b++) dmma(acc[mi][b][0], acc[mi][b][1], af, bf[ks][b]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pipe.empty + pipe.stage);
+      pipe.advance();
+    }
+    emit(tt, acc);
+  }
+}
+
+// ---- same-element kernel: one CTA per (group, element), 256 threads, the producer is lane 0 of warp 0 inline with the
+//      consumers (the kernel needs 128 registers per thread for its 4 x 4 accumulator tiles, which a ninth warp at two
+//      CTAs per SM does not leave) ----
+struct ChxfPipeInline {
   unsigned long long* full;   // [CHXF_STAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
   unsigned long long* empty;  // [CHXF_STAGES]  all 8 warps are done with the stage   (8 arrivals)
   int c_stage = 0, p_stage = 0;
   unsigned c_phase = 0, p_phase = 0;
 };
-__device__ __forceinline__ void chxf_pipe_init(ChxfPipe& pipe, unsigned long long* bars) {
+__device__ __forceinline__ void chxf_pipe_inline_init(ChxfPipeInline& pipe, unsigned long long* bars) {
   pipe.full = bars;
   pipe.empty = bars + CHXF_STAGES;
   if (threadIdx.x == 0) {
@@ -93,9 +196,9 @@ __device__ __forceinline__ void chxf_pipe_init(ChxfPipe& pipe, unsigned long lon
 // element pair by element pair, so a sub-block is one contiguous run -- which signals the stage's `full` mbarrier by byte
 // count; every warp arrives on the stage's `empty` mbarrier when it is done with it; the producer runs CHXF_STAGES - 1
 // stages ahead ACROSS tiles and no block-wide barrier is involved.  Warp w owns the m-tiles w, w + 8, w + 16, w + 24;
-// `emit(tt, mi, b, c, value)` receives R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt after the tile's last stage.
+// `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt after the tile's last stage.
 template <int NB, class Emit>
-__device__ __forceinline__ void chxf_phase1(const ChanXParams& prm, ChxfPipe& pipe, const double* __restrict__ Wa, int t0, int ntl, int pair,
+__device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfPipeInline& pipe, const double* __restrict__ Wa, int t0, int ntl, int pair,
                                             int k0, int b0, double* ring, Emit emit) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
   const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: whole m-tiles, 64-byte multiples
@@ -160,13 +263,7 @@ __device__ __forceinline__ void chxf_phase1(const ChanXParams& prm, ChxfPipe& pi
       if (lane == 0) mbar_arrive(pipe.empty + pipe.c_stage);
       if (++pipe.c_stage == CHXF_STAGES) { pipe.c_stage = 0; pipe.c_phase ^= 1u; }
     }
-#pragma unroll
-    for (int mi = 0; mi < 4; mi++)
-#pragma unroll
-      for (int b = 0; b < NB; b++) {
-        emit(tt, mi, b, 0, acc[mi][b][0]);
-        emit(tt, mi, b, 1, acc[mi][b][1]);
-      }
+    emit(tt, acc);
   }
 }
 
@@ -186,8 +283,8 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
   __shared__ unsigned long long bars[2 * CHXF_STAGES];
   double* ring = Bt + (size_t)NI * LDK;
   for (int q = tid; q < NI * LDK; q += 256) Bt[q] = 0.0;
-  ChxfPipe pipe;
-  chxf_pipe_init(pipe, bars);
+  ChxfPipeInline pipe;
+  chxf_pipe_inline_init(pipe, bars);
 
   double acc[4][NTN][2];
 #pragma unroll
@@ -204,10 +301,16 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
       // ---- phase 1: Bt[n][k] = sg sum_slots W^a_slot[k] coef^b[slot][n] ----
       const double* Wa = prm.W + (size_t)a * prm.WB;
       for (int k0 = 0; k0 < np2; k0 += 256) {
-        chxf_phase1<1>(prm, pipe, Wa, t0, ntl, e * nel + e, k0, b, ring, [&](int tt, int mi, int, int c, double v) {
+        chxf_phase1_inline<1>(prm, pipe, Wa, t0, ntl, e * nel + e, k0, b, ring, [&](int tt, double (&ra)[4][1][2]) {
           const int2 T = tiles[t0 + tt];
-          const int row = k0 + 8 * (warp + 8 * mi) + gid, kk = 2 * t4 + c;
-          if (row < np2 && kk < T.y) Bt[(T.x - it0 + kk) * LDK + row] = sg * v;  // rows outside the element are zero in W
+          double* Bn = Bt + (T.x - it0 + 2 * t4) * LDK + k0 + 8 * warp + gid;  // rows outside the element are zero in W
+          const bool ok0 = 2 * t4 < T.y, ok1 = 2 * t4 + 1 < T.y;
+#pragma unroll
+          for (int mi = 0; mi < 4; mi++)
+            if (k0 + 8 * (warp + 8 * mi) + gid < np2) {
+              if (ok0) Bn[64 * mi] = sg * ra[mi][0][0];
+              if (ok1) Bn[64 * mi + LDK] = sg * ra[mi][0][1];
+            }
         });
       }
       __syncthreads();
@@ -267,63 +370,103 @@ struct ChxfPair {
   static constexpr int YS = 8 * NTL * LDY;
 };
 
-// grid (groups of the batch, nel (nel - 1)), 256 threads, dynamic smem NI * stack * RS + max(chxf_ring_doubles(PB), 8 * YS)
-// doubles (the per-warp staging of the first product aliases the cp.async ring of phase 1).
+// persistent grid, CHXF_THREADS threads, dynamic smem NI * stack * RS + 8 * YS + chxf_ring_doubles(PB) doubles.
+// Units: (group, ordered pair of different elements).
 template <int NI, int NTL>
-__global__ void __launch_bounds__(256, (NTL <= 2) ? 2 : 1) chan_xf_pair_kernel(ChanXParams prm, const int4* __restrict__ groups, const int2* __restrict__ tiles) {
+__global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair_kernel(ChanXParams prm, const int4* __restrict__ groups, int ngroups,
+                                                                                        const int2* __restrict__ tiles) {
   extern __shared__ __align__(128) double sm[];
+  __shared__ unsigned long long bars[2 * CHXF_STAGES];
+  __shared__ int2 sT[CHXF_TMAX], sU[CHXF_TMAX];
   using Geo = ChxfPair<NTL>;
   constexpr int LDR = Geo::LDR, RS = Geo::RS, LDY = Geo::LDY;
   constexpr int NIT = (NI + 7) / 8;  // items a warp carries
-  const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2, st = prm.stack;
-  const int ie = blockIdx.y / (nel - 1);
-  const int jj = blockIdx.y % (nel - 1);
-  const int je = jj + (jj >= ie ? 1 : 0);
-  const int4 G = groups[blockIdx.x];
-  const int it0 = G.x, nn = G.y, t0 = G.z, ntl = G.w;
-  const int r = prm.item_fam[it0];
-  const double fac = prm.fam_fac[r];
+  const int nel = prm.nel, nel2 = nel * nel, np = prm.np, np2 = prm.np2, st = prm.stack, npairs = nel * (nel - 1);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
-  __shared__ unsigned long long bars[2 * CHXF_STAGES];
-  double* Rt = sm;                                            // [NI][st][RS]
-  double* ring = sm + (size_t)NI * st * RS;                   // phase 1: cp.async stages
-  double* Y = ring + warp * Geo::YS;                          // phase 2: per-warp staging of the first product (aliases the ring)
-  const bool lower = ie > je;
-  for (int q = tid; q < NI * st * RS; q += 256) Rt[q] = 0.0;  // padding rows / columns stay zero for good
+  double* Rt = sm;                                                   // [NI][st][RS]
+  double* Y = sm + (size_t)NI * st * RS + (warp & 7) * Geo::YS;      // per-warp staging of the first product
+  double* ring = sm + (size_t)NI * st * RS + (size_t)8 * Geo::YS;    // bulk-copy stages
+  for (int q = tid; q < NI * st * RS; q += CHXF_THREADS) Rt[q] = 0.0;  // padding rows / columns stay zero for good
   ChxfPipe pipe;
   chxf_pipe_init(pipe, bars);
-  // where this lane's rows of a sweep land inside an item's (i, l) matrix (no integer division in the hot loop)
-  int rofs[4];  // first sweep (all of the sub-block when np <= 16)
+  const int nunits = ngroups * npairs;
+
+  if (warp == 8) {  // ---------------- producer warp ----------------
+    // slot range of a unit's group: first slot of its first tile .. end of its last tile (requested one unit ahead)
+    auto slot_range = [&](int u, int& sb, int& se, int& pair) {
+      const int4 G = groups[u / npairs];
+      const int pq = u % npairs, ie = pq / (nel - 1), jj = pq % (nel - 1), je = jj + (jj >= ie ? 1 : 0);
+      const int2 U0 = prm.tile_u[G.z], U1 = prm.tile_u[G.z + G.w - 1];
+      sb = U0.x; se = U1.x + U1.y; pair = ie * nel + je;
+    };
+    int sb = 0, se = 0, pair = 0;
+    if ((int)blockIdx.x < nunits) slot_range(blockIdx.x, sb, se, pair);
+    for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+      int sb_n = 0, se_n = 0, pair_n = 0;
+      if (u + (int)gridDim.x < nunits) slot_range(u + gridDim.x, sb_n, se_n, pair_n);
+      for (int a = 0; a < st; a++)
+        for (int k0 = 0; k0 < np2; k0 += 256) chxf_produce(prm, pipe, prm.W + (size_t)a * prm.WB, sb, se, pair, k0, ring);
+      sb = sb_n; se = se_n; pair = pair_n;
+    }
+    return;
+  }
+  // ---------------- consumer warps ----------------
+  // where this lane's rows of the first sweep land inside an item's (i, l) matrix (no integer division in the hot loop)
+  int rofs[4];
 #pragma unroll
   for (int mi = 0; mi < 4; mi++) {
     const int row = 8 * (warp + 8 * mi) + gid;
     rofs[mi] = (row % np) + (row / np) * LDR;
   }
+  for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+    const int4 G = groups[u / npairs];
+    const int pq = u % npairs, ie = pq / (nel - 1), jj = pq % (nel - 1), je = jj + (jj >= ie ? 1 : 0);
+    const int it0 = G.x, nn = G.y, t0 = G.z, ntl = G.w;
+    const int r = prm.item_fam[it0];
+    const double fac = prm.fam_fac[r];
+    const bool lower = ie > je;
+    // the group's tile tables (item range, slot range): staged once per unit; the barrier at the top of the a loop
+    // publishes them (and the previous unit's last readers are behind its phase-1 / phase-2 barrier)
+    if (tid < ntl) { sT[tid] = tiles[t0 + tid]; sU[tid] = prm.tile_u[t0 + tid]; }
+    double kacc[NIT][NTL][NTL][2];
+#pragma unroll
+    for (int it = 0; it < NIT; it++)
+#pragma unroll
+      for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+        for (int qt = 0; qt < NTL; qt++) { kacc[it][mt][qt][0] = 0.0; kacc[it][mt][qt][1] = 0.0; }
 
-  double kacc[NIT][NTL][NTL][2];
+    for (int a = 0; a < st; a++) {
+      consumer_sync();  // the previous products are done with Rt
+      // ---- phase 1: Rt[n][b](i, l) = (+-) fac sum_slots W^a_slot(i, l) coef^b[slot][n], both stack halves b at once ----
+      for (int k0 = 0; k0 < np2; k0 += 256) {
+        auto store = [&](int tt, int mi, int b, double v0, double v1) {
+          const int2 T = sT[tt];
+          const int row = k0 + 8 * (warp + 8 * mi) + gid;
+          if (row >= np2) return;
+          int ro = rofs[mi];
+          if constexpr (NTL > 2) {  // several sweeps (np > 16): the later ones pay the integer division
+            if (k0 != 0) ro = (row % np) + (row / np) * LDR;
+          }
+          double* Rn = Rt + ((T.x - it0 + 2 * t4) * st + b) * RS + ro;
+          const double sg = (a == b) ? fac : -fac;
+          if (2 * t4 < T.y) Rn[0] = sg * v0;
+          if (2 * t4 + 1 < T.y) Rn[st * RS] = sg * v1;
+        };
+        auto emit2 = [&](int tt, double (&ra)[4][2][2]) {
 #pragma unroll
-  for (int it = 0; it < NIT; it++)
+          for (int mi = 0; mi < 4; mi++)
 #pragma unroll
-    for (int mt = 0; mt < NTL; mt++)
+            for (int b = 0; b < 2; b++) store(tt, mi, b, ra[mi][b][0], ra[mi][b][1]);
+        };
+        auto emit1 = [&](int tt, double (&ra)[4][1][2]) {
 #pragma unroll
-      for (int qt = 0; qt < NTL; qt++) { kacc[it][mt][qt][0] = 0.0; kacc[it][mt][qt][1] = 0.0; }
-
-  for (int a = 0; a < st; a++) {
-    __syncthreads();
-    // ---- phase 1: Rt[n][b](i, l) = (+-) fac sum_slots W^a_slot(i, l) coef^b[slot][n], both stack halves b at once ----
-    const double* Wa = prm.W + (size_t)a * prm.WB;
-    for (int k0 = 0; k0 < np2; k0 += 256) {
-      auto emit = [&](int tt, int mi, int b, int c, double v) {
-        const int2 T = tiles[t0 + tt];
-        const int kk = 2 * t4 + c;
-        const int row = k0 + 8 * (warp + 8 * mi) + gid;
-        if (row < np2 && kk < T.y)
-          Rt[((size_t)(T.x - it0 + kk) * st + b) * RS + (k0 == 0 ? rofs[mi] : (row % np) + (row / np) * LDR)] = ((a == b) ? fac : -fac) * v;
-      };
-      if (st == 2) chxf_phase1<2>(prm, pipe, Wa, t0, ntl, ie * nel + je, k0, 0, ring, emit);
-      else chxf_phase1<1>(prm, pipe, Wa, t0, ntl, ie * nel + je, k0, 0, ring, emit);
-    }
-    __syncthreads();
+          for (int mi = 0; mi < 4; mi++) store(tt, mi, 0, ra[mi][0][0], ra[mi][0][1]);
+        };
+        if (st == 2) chxf_consume<2>(prm, pipe, sU, ntl, k0, 0, ring, emit2);
+        else chxf_consume<1>(prm, pipe, sU, ntl, k0, 0, ring, emit1);
+      }
+      consumer_sync();
     // ---- phase 2: Ksub += iint^a . Rsub^{ab} . (jint^b)^T for the warp's items ----
     const double* iint = (lower ? prm.big_f : prm.small_f) + (((size_t)r * nel + ie) * st + a) * np2;
     double af[2 * NTL][NTL];
@@ -402,6 +545,7 @@ __global__ void __launch_bounds__(256, (NTL <= 2) ? 2 : 1) chan_xf_pair_kernel(C
           if (row < np && col < np) __stcs(On + row + col * np, kacc[it][mt][qt][cc]);
         }
   }
+  }  // units
 }
 
 }  // namespace hfb
