@@ -4,15 +4,20 @@
     python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
     python bench.py --impl reference ...                      (the CPU arm: oracle port on the host cores)
 
-A *step* is one pass of the hot path over one batch of synthetic densities on one basis:
-`batch` independent Fock builds (coulomb + eval_Fxc; exchange is not called for a pure functional,
-sadatom/solver.cpp:822) of BASELINE.json configs[1] (Kr, PBE, 20 LIP-15 elements, lmax 3), the
-situation of the sadatom configuration search / Z sweep where many trial densities share one basis.
-`value` = builds/s with the densities already resident in HBM (element-band layout);
-`e2e`   = the same through the reference-facing dense C-ABI calls with HOST matrices in and out
-          (pack + H2D + kernels + D2H + scatter inside the timed region).
-Ranks (N>1) each process their own batch: the path shards by atom / trial configuration with no
-data-path collective ("weak" scaling); only the timing is reduced (max over ranks).
+Default workload: BASELINE.json configs[3], the largest configuration that fits one GPU -- N2 Hartree-Fock in prolate
+spheroidal coordinates, lmax 24, mmax 6, 5 LIP-15 elements (19 552 basis functions, 585 integral families).  A *step* is ONE
+Fock build: coulomb(P) + exchange(P) (HF has no XC term) for an overlap-orthonormalised N2-like closed-shell density.
+`value` = builds/s with P, J, K resident in HBM (hfb200_chan_coulomb_device + hfb200_chan_exchange_device);
+`e2e`   = the same through the reference-facing host-matrix calls TwoDBasis::coulomb / TwoDBasis::exchange.
+N > 1:   STRONG scaling of that one build: every rank holds the integral families r % N == rank and the library all-reduces
+         J (per-channel radial results) and K (packed non-zero angular blocks) over NCCL inside the timed region.
+`roofline` carries every stage of the build with its algorithmic flops / bytes, the dominant kernel on top.
+`cpu_baseline` / `--impl reference`: the CPU port of the reference loops on a uniform SAMPLE of output blocks, scaled to
+the full operator (kind "port-sampled"; the full port would need ~1e13 flop per exchange call).
+
+Other workloads (--workload): the sadatom batches kr_pbe_cfg2 (configs[1]) and rn_r2scan_cfg3 (configs[2]): a step is `batch`
+independent Fock builds (coulomb + eval_Fxc) on one basis, ranks process their own batches (weak scaling, no collective);
+ne_hf_cfg1 (configs[0]); smaller diatomic cases; the product-grid XC cases.
 """
 import argparse
 import ctypes
@@ -433,22 +438,129 @@ def run_gpu(args, w, rank, world, local_rank):
 # atomic / diatomic Hartree-Fock builds: J + K through the Gaunt-coupled channel engine
 # ------------------------------------------------------------------------------------------------
 def chan_orbitals(b, kind, rank):
-    """Synthetic occupied orbitals, each pure in m (what an SCF of an atom / linear molecule produces): smooth seeded
-    coefficients decaying with l and with the radial index.  Returns C (ndim x norb) in the operator's index space."""
-    from util import splitmix64
+    """Synthetic occupied orbitals, each pure in m (what an SCF of an atom / linear molecule produces).  Diatomic: seven
+    N2-like orbitals (five sigma, pi+, pi-) Loewdin-ORTHONORMALISED in the overlap metric (tests/util.py), so J and K have the
+    magnitude of a converged SCF density; atomic: five s-type orbitals.  Returns C (ndim x norb) in the operator's index space."""
+    from util import splitmix64, diatomic_orbitals
+    if kind == "diatomic" and int(np.max(np.abs(b.mval))) >= 1:
+        return diatomic_orbitals(b, seed=100 + 17 * rank)
     nrad, nang = b.nrad, b.nang
     ndim = nang * nrad
-    occ_m = [0, 0, 0, 0, 0, 1, -1] if (kind == "diatomic" and int(np.max(np.abs(b.mval))) >= 1) else [0] * 5
     cols = []
-    for q, m in enumerate(occ_m):
+    for q, m in enumerate([0] * 5):
         c = np.zeros((nang, nrad))
         sel = np.where(b.mval == m)[0]
         noise = splitmix64(len(sel) * nrad, seed=100 + q + 17 * rank).reshape(len(sel), nrad)
         c[sel] = noise * np.exp(-0.35 * b.lval[sel])[:, None] * np.exp(-0.06 * np.arange(nrad))[None, :]
-        if kind == "diatomic" and m != 0:
-            c[sel, 0] = 0.0  # boundary function of the m != 0 shells (diatomic/basis.cpp:482-499)
         cols.append(c.reshape(ndim))
     return np.stack(cols, axis=1)
+
+
+def make_chan_basis(w, device=0):
+    import helfem_b200 as hb
+    if w["kind"] == "atomic":
+        return hb.AtomicBasis(w["Z"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"], lmax=w["lmax"], mmax=w["mmax"], device=device)
+    return hb.DiatomicBasis(w["Z1"], w["Z2"], w["Rbond"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"],
+                            lmax=w["lmax"], mmax=w["mmax"], device=device)
+
+
+def chan_oracle(b, kind):
+    """CPU port of the reference's coulomb / exchange (oracle/chan_oracle.cpp) on the SAME stored integrals (zero-copy views)."""
+    import oracle
+    if kind == "diatomic":
+        dis = [[b.tei_view(ww, r, e) for r in range(b.nlm) for e in range(b.nel)] for ww in range(4)]
+        tei = [b.tei_view(4 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
+        ktei = [b.tei_view(8 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
+        return oracle.DiatomicOracle(b.lval, b.mval, b.first, b.last, b.Lmap, b.Mmap, b.Rhalf, dis, tei, ktei, b.pure_indices())
+    nL = 2 * int(np.max(b.lval)) + 1
+    t = [b.tei(L, e) for L in range(nL) for e in range(b.nel)]
+    return oracle.AtomicOracle(b.lval, b.mval, b.first, b.last, [x[0] for x in t], [x[1] for x in t], [x[2] for x in t], [x[3] for x in t])
+
+
+def cpu_chan_build(b, kind, Ph, budget_s=12.0, seed=2026):
+    """Seconds per Fock build (coulomb + exchange) of the CPU port on the host cores.  Small bases: one full build.  Large
+    diatomic bases: a UNIFORM SAMPLE of output blocks through the block-restricted oracle (the same loops, evaluated for the
+    sampled blocks only), scaled to the full operator: exchange by the number of output blocks with m_j = m_k (the others
+    vanish for an m-diagonal density and cost the port nothing), coulomb by the number of channels.  Returns
+    (seconds, kind, sample description, extra)."""
+    import oracle
+    from util import splitmix64
+    oracle.lib().oracle_set_num_threads(host_threads())
+    o = chan_oracle(b, kind)
+    n = Ph.shape[0]
+    if kind != "diatomic" or n <= 2500:
+        t0 = time.perf_counter()
+        Jo, Ko = o.coulomb(Ph), o.exchange(Ph)
+        return time.perf_counter() - t0, "port", "1 Fock build (coulomb + exchange) of the same workload", {"J": Jo, "K": Ko}
+    nang = b.nang
+    mdiag = [(j, k) for j in range(nang) for k in range(nang) if b.mval[j] == b.mval[k]]
+    u = splitmix64(4096, seed=seed)
+    pick = lambda lst, cnt, off: [lst[int((u[off + q] + 1.0) * 0.5 * len(lst)) % len(lst)] for q in range(cnt)]
+    t0 = time.perf_counter()
+    o.exchange_blocks(Ph, [], [])  # the block-norm screen of the density alone (a fixed cost of every exchange call)
+    t_mask = time.perf_counter() - t0
+    nk = 16
+    t0 = time.perf_counter()
+    ks = pick(mdiag, nk, 0)
+    o.exchange_blocks(Ph, [p[0] for p in ks], [p[1] for p in ks])
+    t1 = time.perf_counter() - t0 - t_mask
+    nk2 = int(max(16, min(len(mdiag), nk * 0.6 * budget_s / max(t1, 1e-3))))
+    ks = pick(mdiag, nk2, 100)
+    t0 = time.perf_counter()
+    o.exchange_blocks(Ph, [p[0] for p in ks], [p[1] for p in ks])
+    tK = max(time.perf_counter() - t0 - t_mask, 1e-6)
+    est_K = t_mask + tK * len(mdiag) / nk2
+    allp = [(i, j) for i in range(nang) for j in range(nang)]
+    js = pick(allp, 6, 2000)
+    chans = set()
+    for i, j in js:
+        li, mi, lj, mj = int(b.lval[i]), int(b.mval[i]), int(b.lval[j]), int(b.mval[j])
+        for L in range(max(abs(lj - li) - 2, abs(mj - mi)), lj + li + 3):
+            chans.add((L, mj - mi))
+    t0 = time.perf_counter()
+    o.coulomb_blocks(Ph, [p[0] for p in js], [p[1] for p in js])
+    tJ = time.perf_counter() - t0
+    nchan_all = len({(L, int(b.mval[k]) - int(b.mval[l])) for k in range(nang) for l in range(nang)
+                     for L in range(max(abs(int(b.lval[k]) - int(b.lval[l])) - 2, abs(int(b.mval[k]) - int(b.mval[l]))), int(b.lval[k]) + int(b.lval[l]) + 3)})
+    est_J = tJ * nchan_all / max(len(chans), 1)
+    sample = ("exchange: %d of the %d output blocks with m_j = m_k (uniform, seeded) in %.1f s -> %.0f s per call; coulomb: %d of %d channels "
+              "in %.1f s -> %.0f s per call" % (nk2, len(mdiag), tK + t_mask, est_K, len(chans), nchan_all, tJ, est_J))
+    return est_K + est_J, "port-sampled", sample, {"fraction_exchange": nk2 / len(mdiag), "fraction_coulomb": len(chans) / nchan_all}
+
+
+def run_chan_reference(args, w, rank):
+    """CPU arm of the atomic / diatomic workloads: the oracle port on the host cores (stored integrals from the host library's
+    compute_tei, which is setup, not the timed path; no device context is created).  A step = one (sampled) Fock build."""
+    if rank != 0:
+        return
+    b = make_chan_basis(w)
+    b.compute_tei(True)
+    kind = w["kind"]
+    C = chan_orbitals(b, kind, 0)
+    P = 2.0 * C @ C.T
+    if kind == "diatomic":
+        idx = b.pure_indices()
+        P = P[np.ix_(idx, idx)]
+    Ph = np.asfortranarray(P)
+    import oracle
+    steps = max(1, min(args.steps, 3))
+    ts, info = [], None
+    for q in range(steps):
+        t, k, sample, extra = cpu_chan_build(b, kind, Ph, budget_s=10.0, seed=2026 + q)
+        ts.append(t)
+        info = (k, sample, extra)
+    sec = float(np.mean(ts))
+    value = 1.0 / sec
+    extra = {kk: vv for kk, vv in info[2].items() if not hasattr(vv, "shape")}
+    line = {"impl": "reference", "metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": 0, "ms_per_step": 1e3 * sec, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "operators": "coulomb + exchange (HF)", "nbf": int(Ph.shape[0]),
+                       "note": "CPU restatement of the reference loops (oracle/chan_oracle.cpp, -O3 -fopenmp); the reference itself cannot be "
+                               "compiled here (no Armadillo/GSL/libxc/HDF5/gfortran)"},
+            "cpu_baseline": dict({"value": value, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": info[0], "sample": info[1]}, **extra),
+            "e2e": {"value": value, "unit": "builds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
 
 
 def run_chan(args, w, rank, world, local_rank):
@@ -464,15 +576,11 @@ def run_chan(args, w, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     kind = w["kind"]
     t0 = time.perf_counter()
-    if kind == "atomic":
-        b = hb.AtomicBasis(w["Z"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"], lmax=w["lmax"], mmax=w["mmax"],
-                           device=local_rank)
-    else:
-        b = hb.DiatomicBasis(w["Z1"], w["Z2"], w["Rbond"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"],
-                             lmax=w["lmax"], mmax=w["mmax"], device=local_rank)
-    sharded = bool(args.shard) and world > 1
+    b = make_chan_basis(w, device=local_rank)
+    # N > 1: STRONG scaling of one build.  The integral families r % world == rank live on this rank; the library all-reduces
+    # J (per-channel radial results) and K (packed non-zero angular blocks) over NCCL inside the timed region.
+    sharded = world > 1 and not args.replicas
     if sharded:
-        # integral families r % world == rank; partial operators are all-reduced (NCCL)
         if kind == "diatomic":
             b.set_shard(rank, world, owned_only=True)
         else:
@@ -482,8 +590,13 @@ def run_chan(args, w, rank, world, local_rank):
     t0 = time.perf_counter()
     n = b.chan_dim()  # uploads the integral tables
     t_upload = time.perf_counter() - t0
+    if sharded:
+        uid = [hb.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        b.comm_init(uid[0], rank, world)
     C = torch.from_numpy(chan_orbitals(b, kind, 0 if sharded else rank)).cuda()
-    dP = (2.0 * C @ C.T).contiguous()  # symmetric, so row- and column-major coincide
+    dP = (2.0 * C @ C.T).contiguous()
+    dP = (0.5 * (dP + dP.T)).contiguous()  # exactly symmetric (what C C^T through syrk gives a host driver)
     dJ = torch.zeros_like(dP)
     dK = torch.zeros_like(dP)
     torch.cuda.synchronize()
@@ -493,18 +606,11 @@ def run_chan(args, w, rank, world, local_rank):
     sh = stream.cuda_stream
     assert sh != 0
 
-    from helfem_b200 import shard as shard_mod
-
     def step(J=True, K=True):
         if J:
             b.coulomb_device(dP.data_ptr(), dJ.data_ptr(), n, sh)
         if K:
             b.exchange_device(dP.data_ptr(), dK.data_ptr(), n, sh)
-        if sharded:  # NCCL moves the non-zero angular blocks only
-            if J:
-                shard_mod.allreduce_blocksparse_(dJ, b.nang, b.nrad, pattern_key="J of the bench density")
-            if K:
-                shard_mod.allreduce_blocksparse_(dK, b.nang, b.nrad, pattern_key="K of the bench density")
 
     def barrier():
         if dist is not None:
@@ -537,55 +643,42 @@ def run_chan(args, w, rank, world, local_rank):
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    units = 1 if sharded else world
+    units = 1 if (sharded or world == 1) else world
     value = units * args.steps / (ms * 1e-3)
+    barrier()
     ms_j = timed(lambda: step(K=False), args.steps) / args.steps
+    barrier()
     ms_k = timed(lambda: step(J=False), args.steps) / args.steps
+    barrier()
     b.set_profile(True)
     step(J=False)
     torch.cuda.synchronize()
     items, x3_flops, stage = b.exchange_stats()
+    ms_ar = b.allreduce_ms()
+    cnt = b.exchange_counts()
     b.set_profile(False)
     if args.kernels_only:
         if rank == 0:
             print(json.dumps({"kernels_only": True, "ms_per_step": ms / args.steps, "ms_coulomb": ms_j, "ms_exchange": ms_k,
-                              "stage_ms": stage, "items": items}), flush=True)
+                              "stage_ms": stage, "allreduce_ms": ms_ar, "items": items}), flush=True)
+        if dist is not None:
+            dist.destroy_process_group()
         return
 
-    # ---- end to end: dense HOST matrices through the reference-facing calls (coulomb + exchange) ----
+    # ---- end to end: dense HOST matrices through the reference-facing calls TwoDBasis::coulomb + TwoDBasis::exchange (every rank
+    #      passes the same host density and gets the complete host J and K, like an SPMD driver would) ----
     Ph = dP.cpu().numpy()
     if kind == "diatomic":
         idx = b.pure_indices()
         Ph = np.asfortranarray(Ph[np.ix_(idx, idx)])
     else:
         Ph = np.asfortranarray(Ph)
-    ne2e = 1 if n > 8000 else 3
-
-    if sharded:
-        # sharded end to end: every rank uploads P from pinned host memory, contracts its families through the
-        # device-resident entry points, J and K are summed over NCCL on the device, rank 0 downloads the result
-        hP = torch.empty((n, n), dtype=torch.float64).pin_memory()
-        hP.copy_(dP.cpu())
-        hJ = torch.empty((n, n), dtype=torch.float64).pin_memory()
-        hK = torch.empty((n, n), dtype=torch.float64).pin_memory()
-
-        def host_build():
-            dP.copy_(hP, non_blocking=True)
-            step()
-            if rank == 0:
-                hJ.copy_(dJ, non_blocking=True)
-                hK.copy_(dK, non_blocking=True)
-            torch.cuda.synchronize()
-            return hJ, hK
-    else:
-        def host_build():
-            return b.coulomb(Ph), b.exchange(Ph)
-
-    host_build()
+    ne2e = 2 if n > 8000 else 5
+    Jh, Kh = b.coulomb(Ph), b.exchange(Ph)
     barrier()
     t0 = time.perf_counter()
     for _ in range(ne2e):
-        Jh, Kh = host_build()
+        Jh, Kh = b.coulomb(Ph), b.exchange(Ph)
     torch.cuda.synchronize()
     t_e2e = (time.perf_counter() - t0) / ne2e
     if dist is not None:
@@ -598,44 +691,81 @@ def run_chan(args, w, rank, world, local_rank):
         return
     nb = Ph.shape[0]
     cpu = None
-    if world == 1 and nb <= 2500 and kind == "diatomic":
+    if world == 1:
+        sec, ckind, sample, extra = cpu_chan_build(b, kind, Ph)
         import oracle
-        oracle.lib().oracle_set_num_threads(host_threads())
-        dis = [[b.tei(ww, r, e) for r in range(b.nlm) for e in range(b.nel)] for ww in range(4)]
-        tei = [b.tei(4 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
-        ktei = [b.tei(8 + ab, r, e) for r in range(b.nlm) for e in range(b.nel) for ab in range(4)]
-        o = oracle.DiatomicOracle(b.lval, b.mval, b.first, b.last, b.Lmap, b.Mmap, b.Rhalf, dis, tei, ktei, b.pure_indices())
-        t0 = time.perf_counter()
-        Jo, Ko = o.coulomb(Ph), o.exchange(Ph)
-        tc = time.perf_counter() - t0
-        cpu = {"value": 1.0 / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
-               "sample": "1 Fock build (coulomb + exchange) of the same workload",
-               "max_dJ": float(np.max(np.abs(np.asarray(Jh) - Jo))), "max_dK": float(np.max(np.abs(np.asarray(Kh) - Ko)))}
-    t_rad = stage[2] + stage[3]
-    tf = x3_flops / (t_rad * 1e-3) / 1e12 if t_rad > 0 else None
-    roofline = {"kernel": "chan_xf_same_kernel + chan_xf_pair_kernel", "bound": "tensor", "achieved": tf, "peak": FP64_TFLOPS_MEASURED, "unit": "TFLOP/s",
-                "frac": (tf / FP64_TFLOPS_MEASURED) if tf else None, "traffic": ncu_traffic(args.workload, "chan_xf_same_kernel"),
-                "peak_source": "measured cuBLAS DGEMM FP64 (profiles/r01_fp64_peak.json); tcgen05 has no FP64 kind, DMMA.8x8x4 is the FP64 tensor path",
-                "algorithmic_flops_per_build": x3_flops, "ms_per_build": t_rad,
-                "exchange_stage_ms": dict(zip(["mask", "x1_left_angular", "xf_same_element", "xf_element_pairs", "x4_assemble"], stage)),
-                "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items, "family_batches": b.exchange_batches()}
+        cpu = {"value": 1.0 / sec, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": ckind, "sample": sample}
+        if "K" in extra:
+            cpu["max_dJ"] = float(np.max(np.abs(np.asarray(Jh) - extra["J"])))
+            cpu["max_dK"] = float(np.max(np.abs(np.asarray(Kh) - extra["K"])))
+        else:
+            cpu.update(extra)
+    # ---- per-stage rooflines: algorithmic flops / bytes against the measured peaks ----
+    hbm_peak, hbm_src = peaks()
+    st2 = 4 if kind == "diatomic" else 1
+    stack = 2 if kind == "diatomic" else 1
+    nel, nrad, np2 = int(b.nel), int(b.nrad), int(np.max(b.last - b.first + 1)) ** 2
+    npe = (b.last - b.first + 1).astype(np.float64)
+    per_same = float(np.sum(2.0 * npe ** 4))
+    per_pair = float(sum(2.0 * a * a * c + 2.0 * a * c * c for ia, a in enumerate(npe) for ic, c in enumerate(npe) if ia != ic))
+    ang_pair = 2.0 * cnt[9] * np2 * st2  # right angular contraction per element pair
+    f_same = (per_same * st2 * items + ang_pair * nel)
+    f_pair = (per_pair * st2 * items + ang_pair * nel * (nel - 1))
+    w_bytes = float(cnt[4]) * stack * cnt[5] * 8
+    blocks_bytes = float(items) * nel * nel * np2 * 8
+    stages = []
+
+    def add(name, kernel, msv, bound, flops=None, nbytes=None):
+        e = {"stage": name, "kernel": kernel, "ms": msv, "bound": bound}
+        if flops is not None:
+            e["algorithmic_flops"] = flops
+            e["tflops"] = flops / (msv * 1e-3) / 1e12 if msv > 0 else None
+            e["frac_fp64"] = e["tflops"] / FP64_TFLOPS_MEASURED if e["tflops"] else None
+        if nbytes is not None:
+            e["algorithmic_bytes"] = nbytes
+            e["gbs"] = nbytes / (msv * 1e-3) / 1e9 if msv > 0 else None
+            e["frac_hbm"] = e["gbs"] / hbm_peak if e["gbs"] else None
+        e["traffic"] = ncu_traffic(args.workload, kernel)
+        stages.append(e)
+
+    add("mask", "chan_x0_mask_kernel", stage[0], "hbm", nbytes=float(n) * n * 8)
+    add("x1_left_angular", "chan_x1_mma_kernel", stage[1], "hbm", nbytes=w_bytes + float(np.count_nonzero(np.asarray(b.mval)[:, None] == np.asarray(b.mval)[None, :])) * nrad * nrad * 8)
+    add("xf_same_element", "chan_xf_same_kernel", stage[2], "tensor", flops=f_same, nbytes=w_bytes / nel + blocks_bytes / nel)
+    add("xf_element_pairs", "chan_xf_pair_kernel", stage[3], "tensor", flops=f_pair, nbytes=w_bytes * (nel - 1) / nel + blocks_bytes * (nel - 1) / nel)
+    add("x4_assemble", "chan_x4_kernel", stage[4], "hbm", nbytes=blocks_bytes + float(cnt[6]) * nrad * nrad * 8 * (2 if cnt[8] else 1))
+    add("coulomb (pack, pre, DMMA, post, unpack)", "chan_pre_kernel", ms_j, "hbm", nbytes=2.0 * n * n * 8)
+    if sharded:
+        stages.append({"stage": "nccl_allreduce_K (gather + all-reduce + scatter)", "ms": ms_ar, "payload_bytes": float(cnt[10]) * nrad * nrad * 8})
+    dom = max(stages[:5], key=lambda e: e["ms"])
+    t_dmma = stage[2] + stage[3]
+    tf = (f_same + f_pair) / (t_dmma * 1e-3) / 1e12 if t_dmma > 0 else None
+    roofline = {"kernel": dom["kernel"], "bound": dom["bound"],
+                "achieved": dom.get("tflops") if dom["bound"] == "tensor" else dom.get("gbs"),
+                "peak": FP64_TFLOPS_MEASURED if dom["bound"] == "tensor" else hbm_peak, "unit": "TFLOP/s" if dom["bound"] == "tensor" else "GB/s",
+                "frac": dom.get("frac_fp64") if dom["bound"] == "tensor" else dom.get("frac_hbm"), "traffic": dom["traffic"],
+                "peak_source": "FP64: measured cuBLAS DGEMM (profiles/r01_fp64_peak.json; MEASURED_PEAKS.json has no FP64 entry; tcgen05 has no FP64 kind, "
+                               "DMMA.8x8x4 is the FP64 tensor path); HBM: " + hbm_src,
+                "ms_per_launch_sum": dom["ms"], "stages": stages,
+                "fused_dmma_tflops": tf, "fused_dmma_frac": tf / FP64_TFLOPS_MEASURED if tf else None,
+                "whole_build_tflops": (f_same + f_pair) / (ms / args.steps * 1e-3) / 1e12,
+                "whole_build_frac_fp64": (f_same + f_pair) / (ms / args.steps * 1e-3) / 1e12 / FP64_TFLOPS_MEASURED,
+                "radial_flops_per_build": x3_flops, "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items,
+                "symmetric_item_list": bool(cnt[8]), "family_batches": b.exchange_batches(), "w_bytes": w_bytes}
+    nlaunch = 5 + 1 + 4 * b.exchange_batches() + (2 if sharded else 0)
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "desc": w["desc"], "operators": "coulomb + exchange (HF)", "ndim": n, "nbf": nb,
                        "nang": int(b.nang), "nrad": int(b.nrad),
-                       "l2": "dense P/J/K = %.0f MB per build%s" % (3 * n * n * 8 / 1e6, "" if 3 * n * n * 8 > 126e6 else " (fits L2: launch-bound regime)"),
-                       "partition": ("integral families sharded over ranks, NCCL all-reduce of J and K" if sharded
-                                     else "independent builds per rank, no data-path collective"),
+                       "l2": "dense P/J/K = %.0f MB per build, W = %.1f GB%s" % (3 * n * n * 8 / 1e6, w_bytes / 1e9, "" if 3 * n * n * 8 > 126e6 else " (fits L2: launch-bound regime)"),
+                       "partition": ("one build by all ranks: integral families r %% %d == rank, NCCL all-reduce of J (channel results) and K (packed blocks) "
+                                     "inside the library and inside the timed region" % world if sharded
+                                     else "independent builds per rank, no data-path collective" if world > 1 else "one GPU"),
                        "setup_s": {"compute_tei_host": t_tei, "upload": t_upload, "first_build": t_first}},
             "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": {"value": units / t_e2e, "unit": "builds/s",
-                    "h2d_bytes_per_step": (n * n * 8 * world) if sharded else 2 * nb * nb * 8,
-                    "d2h_bytes_per_step": (2 * n * n * 8) if sharded else 2 * nb * nb * 8,
-                    "api": ("pinned host P -> hfb200_chan_coulomb_device + hfb200_chan_exchange_device on every rank -> NCCL all-reduce -> "
-                            "host J, K on rank 0" if sharded else "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis)")},
-            # coulomb: pack, pre, DMMA, post, unpack; exchange: mask + (x1, x2, x3 same-element, x3 pairs, x4) per family batch
-            "gpu_launches": int(args.steps * (5 + 1 + 5 * b.exchange_batches())), "clocks": clocks}
+            "e2e": {"value": units / t_e2e, "unit": "builds/s", "h2d_bytes_per_step": 2 * nb * nb * 8, "d2h_bytes_per_step": 2 * nb * nb * 8,
+                    "api": "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis), every rank"},
+            "gpu_launches": int(args.steps * nlaunch), "clocks": clocks}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -697,15 +827,16 @@ def run_grid2d(args, w, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="kr_pbe_cfg2", choices=list(WORKLOADS))
+    ap.add_argument("--workload", default="n2_hf_cfg4", choices=list(WORKLOADS))
     ap.add_argument("--batch", type=int, default=1024, help="independent Fock builds per step per GPU")
     ap.add_argument("--kernels-only", action="store_true", help="run only the timed device steps (ncu captures)")
     ap.add_argument("--split", action="store_true", help="with --kernels-only: also time the grid and the Coulomb kernels alone")
-    ap.add_argument("--shard", action="store_true", help="atomic/diatomic workloads, N>1: shard the integral families over the ranks "
-                    "and all-reduce J and K (strong scaling) instead of independent builds per rank")
+    ap.add_argument("--replicas", action="store_true", help="atomic/diatomic workloads, N>1: independent builds per rank instead of the "
+                    "default (one build sharded over the ranks by integral family, NCCL all-reduce inside the library: strong scaling)")
+    ap.add_argument("--shard", action="store_true", help="(default for N>1; kept for older scripts)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -717,9 +848,7 @@ def main():
         return
     if w.get("kind") in ("atomic", "diatomic"):
         if args.impl == "reference":
-            if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "CPU arm of the atomic/diatomic workloads is the oracle leg inside "
-                                  "the b200 line (cpu_baseline) at sizes the oracle finishes; default workload has the full arm"}))
+            run_chan_reference(args, w, rank)
             return
         run_chan(args, w, rank, world, local_rank)
     elif args.impl == "reference":

@@ -108,6 +108,13 @@ def parse_method(method):
     return xc_id(parts[0]), xc_id(parts[1])
 
 
+def comm_unique_id():
+    """NCCL unique id (bytes) for hfb200_comm_init; call on rank 0 and hand it to the other ranks."""
+    buf = ctypes.create_string_buffer(128)
+    check(lib().hfb200_comm_unique_id(buf, 128))
+    return buf.raw
+
+
 def device_count():
     return lib().hfb200_device_count()
 

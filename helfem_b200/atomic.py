@@ -106,6 +106,21 @@ class AtomicBasis:
         """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""
         check_host(lib().hfh_atomic_set_shard(self._h, int(rank), int(nranks)))
 
+    def exchange_counts(self):
+        out = (ctypes.c_longlong * 12)()
+        check(lib().hfb200_chan_exchange_counts(self.context(), out, 12))
+        return list(out)
+
+    def allreduce_ms(self):
+        ms = ctypes.c_double()
+        check(lib().hfb200_chan_allreduce_ms(self.context(), ctypes.byref(ms)))
+        return ms.value
+
+    def comm_init(self, uid, rank, nranks):
+        """Attach an NCCL communicator (id from helfem_b200.comm_unique_id() of rank 0) to the sharded context: the operators
+        then return the complete J / K on every rank (all-reduce inside the library)."""
+        check(lib().hfb200_comm_init(self.context(), ctypes.c_char_p(uid), int(rank), int(nranks)))
+
     def coulomb(self, P):
         P = np.asfortranarray(P, dtype=np.float64)
         J = np.zeros_like(P, order="F")

@@ -71,6 +71,9 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   // tile of such rows / items has a dense coefficient table instead of a checkerboard
   S.ang_group.resize(nang);
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
+  S.ang_m = c->mval;
+  S.fam_owned.resize(nL);
+  for (int L = 0; L < nL; L++) S.fam_owned[L] = (L % c->shard_n == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nL);
   for (int L = 0; L < nL; L++) S.fac[L] = 4.0 * M_PI / (2 * L + 1);
   // channels (L, M), sorted by L (atomic/TwoDBasis.cpp:836-842)
@@ -88,7 +91,6 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
     for (int l = 0; l < nang; l++) {
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;
       for (int L = std::max(std::abs(lk - ll), std::abs(M)); L <= lk + ll; L++) {
-        if (L % c->shard_n != c->shard_rank) continue;  // family owned by another rank
         const double g = angular::gaunt_coefficient(lk, mk, L, M, ll, ml);
         if (g == 0.0) continue;
         S.pair_coupl[(size_t)k * nang + l].push_back({chan_of[(size_t)L * (2 * Mmax + 1) + M + Mmax], {g, 0.0}});
@@ -103,6 +105,7 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   S.big_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return r % sn == sr ? disjoint_m1L[r * nel + e] : (cptr) nullptr; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
+  c->chan->comm = c->comm;
   const int rc = c->chan->build(S, prim_ktei != nullptr);
   if (rc) return rc;
   c->nL = nL;

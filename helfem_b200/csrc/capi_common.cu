@@ -57,6 +57,7 @@ int hfb200_set_shard(hfb200_ctx* c, int rank, int nranks) {
 void hfb200_destroy(hfb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  if (c->comm) hfb200_comm_destroy(c);
   double* ptrs[] = {c->dBt, c->ddBt, c->dR, c->dW, c->dDisL, c->dDisM1L, c->dTeiF, c->dLc, c->dm1Lc, c->dKtei, c->dCpl};
   if (c->dTri) cudaFree(c->dTri);
   int* iptrs[] = {c->dFirst, c->dNpe, c->dElemOf};

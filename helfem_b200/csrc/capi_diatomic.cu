@@ -92,6 +92,9 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   // tile of such rows / items has a dense coefficient table instead of a checkerboard
   S.ang_group.resize(nang);
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
+  S.ang_m = c->mval;
+  S.fam_owned.resize(nlm);
+  for (int r = 0; r < nlm; r++) S.fam_owned[r] = (r % c->shard_n == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nlm);
   for (int r = 0; r < nlm; r++) {
     // LMfac = 4 pi Rh^5 (-1)^M (L-|M|)!/(L+|M|)!   (basis.cpp:1421)
@@ -130,7 +133,6 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
       const int lk = c->lval[k], mk = c->mval[k], ll = c->lval[l], ml = c->mval[l], M = mk - ml;
       for (int L = std::max(std::abs(lk - ll) - 2, std::abs(M)); L <= lk + ll + 2; L++) {
         const int r = cfam.find({L, std::abs(M)})->second;
-        if (r % c->shard_n != c->shard_rank) continue;  // family owned by another rank
         const double c0 = mod_coeff(lk, mk, L, M, ll, ml), c2 = gcoeff(lk, mk, L, M, ll, ml);
         if (c0 == 0.0 && c2 == 0.0) continue;
         S.pair_coupl[(size_t)k * nang + l].push_back({cchan.find({r, M})->second, {c0, c2}});
@@ -145,6 +147,7 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   S.big_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return r % sn != sr ? (cptr) nullptr : h ? Q2[r * nel + e] : Q0[r * nel + e]; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
+  c->chan->comm = c->comm;
   const int rc = c->chan->build(S, prim_ktei != nullptr);
   if (rc) return rc;
   c->nL = nlm;

@@ -12,6 +12,8 @@
 
 namespace hfb {
 
+int comm_allreduce_sum(void* comm, double* buf, size_t n, cudaStream_t st);  // comm.cu
+
 namespace {
 template <class T>
 int up(ChanEngine* E, const T** dst, const std::vector<T>& src) {
@@ -38,6 +40,8 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
   const int MP = (st * ntri + 7) & ~7, KP = (st * ntri + 3) & ~3, MT = MP / 8, KS = KP / 4;
   prm.nel = nel; prm.np = np; prm.np2 = np2; prm.ntri = ntri; prm.stack = st; prm.MT = MT; prm.KS = KS;
   prm.nr = nr; prm.nchan = nchan; prm.npair = npair;
+  fam_owned = S.fam_owned.size() == (size_t)nr ? S.fam_owned : std::vector<char>(nr, 1);
+  ang_m = S.ang_m.size() == (size_t)nang ? S.ang_m : std::vector<int>(nang, 0);
 
   std::vector<int2> tri(ntri);
   for (int j = 0; j < np; j++)
@@ -96,9 +100,10 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
     for (int r = 0; r < nr; r++) fam_c0[r + 1] += fam_c0[r];
     std::vector<std::vector<std::pair<int, const ChanCoupling*>>> by_chan(nchan);
     for (int pr = 0; pr < npair; pr++)
-      for (const auto& cp : S.pair_coupl[pr]) by_chan[cp.chan].push_back({pr, &cp});
-    std::vector<int> pre_ptr(nchan + 1, 0), pre_pair, post_ptr(npair + 1, 0), post_chan;
-    std::vector<double> pre_coef, post_coef;
+      for (const auto& cp : S.pair_coupl[pr])
+        if (fam_owned[S.chan_r[cp.chan]]) by_chan[cp.chan].push_back({pr, &cp});  // ket contraction: owned channels only
+    std::vector<int> pre_ptr(nchan + 1, 0), pre_pair, post_ptr(npair + 1, 0), post_chan, pall_ptr(npair + 1, 0), pall_chan;
+    std::vector<double> pre_coef, post_coef, pall_coef;
     for (int c = 0; c < nchan; c++) {
       for (auto& en : by_chan[c]) {
         pre_pair.push_back(en.first);
@@ -107,19 +112,26 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
       }
       pre_ptr[c + 1] = (int)pre_pair.size();
     }
-    // bra contraction of block (i,j) uses the couplings of the pair (j,i)
+    // bra contraction of block (i,j) uses the couplings of the pair (j,i): over the owned channels (partial operator, summed
+    // by the caller) and over all channels (complete operator after the all-reduce of the channel results)
     for (int i = 0; i < nang; i++)
       for (int j = 0; j < nang; j++) {
         for (const auto& cp : S.pair_coupl[j * nang + i]) {
+          pall_chan.push_back(cp.chan);
+          pall_coef.push_back(cp.coef[0]);
+          pall_coef.push_back(cp.coef[1]);
+          if (!fam_owned[S.chan_r[cp.chan]]) continue;
           post_chan.push_back(cp.chan);
           post_coef.push_back(cp.coef[0]);
           post_coef.push_back(cp.coef[1]);
         }
         post_ptr[i * nang + j + 1] = (int)post_chan.size();
+        pall_ptr[i * nang + j + 1] = (int)pall_chan.size();
       }
     if ((rc = up(this, &prm.chan_r, S.chan_r)) || (rc = up(this, &prm.fam_c0, fam_c0)) || (rc = up(this, &prm.pre_ptr, pre_ptr)) ||
         (rc = up(this, &prm.pre_pair, pre_pair)) || (rc = up(this, &prm.pre_coef, pre_coef)) || (rc = up(this, &prm.post_ptr, post_ptr)) ||
-        (rc = up(this, &prm.post_chan, post_chan)) || (rc = up(this, &prm.post_coef, post_coef)))
+        (rc = up(this, &prm.post_chan, post_chan)) || (rc = up(this, &prm.post_coef, post_coef)) || (rc = up(this, &dPostAllPtr, pall_ptr)) ||
+        (rc = up(this, &dPostAllChan, pall_chan)) || (rc = up(this, &dPostAllCoef, pall_coef)))
       return rc;
     fam_c0_host = fam_c0;
   }
@@ -230,7 +242,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     for (int j = 0; j < nang; j++)
       for (int i = 0; i < nang; i++)
         for (const auto& cp : S.pair_coupl[(size_t)j * nang + i])
-          if (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0)) cnt[(size_t)cp.chan * nang + j + 1]++;
+          if (fam_owned[S.chan_r[cp.chan]] && (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0))) cnt[(size_t)cp.chan * nang + j + 1]++;
     for (size_t q = 0; q < (size_t)nchan * nang; q++) cnt[q + 1] += cnt[q];
     xrowptr = cnt;
     xrow_i.assign(cnt.back(), 0);
@@ -240,7 +252,7 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     for (int j = 0; j < nang; j++)
       for (int i = 0; i < nang; i++)  // i ascending within a row
         for (const auto& cp : S.pair_coupl[(size_t)j * nang + i])
-          if (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0)) {
+          if (fam_owned[S.chan_r[cp.chan]] && (cp.coef[0] != 0.0 || (st == 2 && cp.coef[1] != 0.0))) {
             const int pos = fill[(size_t)cp.chan * nang + j]++;
             xrow_i[pos] = i;
             coef[2 * (size_t)pos] = cp.coef[0];
@@ -546,6 +558,28 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
       }
     }
   }
+  // blocks (j,k) of K that can be non-zero for this mask: m_j - m_k = m_i - m_l for some non-zero P[i,l] (the same list on
+  // every rank of a sharded run: it depends on the mask only)
+  {
+    int mlo = 0, mhi = 0;
+    for (int a = 0; a < nang; a++) { mlo = std::min(mlo, ang_m[a]); mhi = std::max(mhi, ang_m[a]); }
+    const int span = mhi - mlo;
+    std::vector<char> dset(2 * span + 1, 0);
+    for (int i = 0; i < nang; i++)
+      for (int l = 0; l < nang; l++)
+        if (nz[(size_t)i * nang + l]) dset[ang_m[i] - ang_m[l] + span] = 1;
+    red_blocks.clear();
+    for (int j = 0; j < nang; j++)
+      for (int k = sym ? j : 0; k < nang; k++)
+        if (dset[ang_m[j] - ang_m[k] + span]) red_blocks.push_back(make_int2(j, k));
+  }
+  {
+    long long wtot = 0, nout = 0, real = 0, mac = 0;
+    for (const XBatch& B : batches) { wtot += B.wblocks; nout += B.nout; }
+    for (int t = 0; t < ntile; t++) { real += (long long)tslots[t].size(); mac += (long long)tslots[t].size() * tiles2[t].y; }
+    counts[0] = total_items; counts[1] = ntile; counts[2] = real; counts[3] = (long long)nslots; counts[4] = wtot; counts[5] = xprm.WB;
+    counts[6] = nout; counts[7] = (long long)batches.size(); counts[8] = sym ? 1 : 0; counts[9] = mac; counts[10] = (long long)red_blocks.size();
+  }
   if (getenv("HFB200_X_VERBOSE")) {
     long long wtot = 0;
     for (const XBatch& B : batches) wtot += B.wblocks;
@@ -559,7 +593,8 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
   if ((rc = up_list(dItems, items)) || (rc = up_list(dItemFam, item_fam)) || (rc = up_list(dTiles2, tiles2)) ||
       (rc = up_list(dGroupsS, groupsS)) || (rc = up_list(dGroupsP, groupsP)) || (rc = up_list(dTileU, tile_u)) ||
       (rc = up_list(dSlotWblk, slot_wblk)) || (rc = up_list(dSlotCoef, slot_coef)) || (rc = up_list(dWbase, wbase)) ||
-      (rc = up_list(dWbits, wbits)) || (rc = up_list(dOutPtr, out_ptr)) || (rc = up_list(dOutItem, out_item)))
+      (rc = up_list(dWbits, wbits)) || (rc = up_list(dOutPtr, out_ptr)) || (rc = up_list(dOutItem, out_item)) ||
+      (rc = up_list(dRedBlocks, red_blocks)))
     return rc;
   return 0;
 }
@@ -674,6 +709,11 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
     chan_jmma_kernel<false, 2><<<dim3(nel * rts, (maxcol + 127) / 128, prm.nr), 256, 0, st>>>(q);
   }
   HFB_CUDA_OK(cudaGetLastError());
+  if (comm) {  // sum the per-channel radial results over the ranks (each holds its own families), then contract ALL channels
+    int rc;
+    if ((rc = comm_allreduce_sum(comm, dJc.p, (size_t)nchan * nel * 8 * prm.MT, st))) return rc;
+    q.post_ptr = dPostAllPtr; q.post_chan = dPostAllChan; q.post_coef = dPostAllCoef;
+  }
   chan_post_kernel<<<dim3(nel * npair, 1, 1), 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -784,7 +824,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
   }
   last_sym = hNzP[nang2] != 0;
   last_items = total_items;
-  if (total_items > 0) {
+  if (total_items > 0 || comm) {
     if ((rc = dKblocks.reserve((size_t)max_batch_items * nel * nel * np2)) ||
         (rc = dW.reserve((size_t)std::max<long long>(max_wblocks, 1) * stack * xprm.WB)))
       return rc;
@@ -848,6 +888,18 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       HFB_CUDA_OK(cudaGetLastError());
       tick(4, false);
     }
+    if (comm && !red_blocks.empty()) {  // sum the blocks of K that can be non-zero over the ranks, packed; with a symmetric P
+      // only j <= k travels and the scatter writes both triangles
+      const size_t nb = red_blocks.size();
+      if ((rc = dRed.reserve(nb * nrad * nrad))) return rc;
+      tick(5, true);
+      chan_blocks_gather_kernel<<<(unsigned)nb, 256, 0, st>>>(dKm, ldkm, nrad, (const int2*)dRedBlocks.p, dRed.p);
+      HFB_CUDA_OK(cudaGetLastError());
+      if ((rc = comm_allreduce_sum(comm, dRed.p, nb * nrad * nrad, st))) return rc;
+      chan_blocks_scatter_kernel<<<(unsigned)nb, 256, 0, st>>>(dKm, ldkm, nrad, (const int2*)dRedBlocks.p, dRed.p, last_sym ? 1 : 0);
+      HFB_CUDA_OK(cudaGetLastError());
+      tick(5, false);
+    }
     if (profile_stages) {
       HFB_CUDA_OK(cudaStreamSynchronize(st));
       for (float& v : stage_ms) v = 0.f;
@@ -879,8 +931,8 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
 void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
-  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW}) b->release();
-  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab}) {
+  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRed}) b->release();
+  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab, &dRedBlocks}) {
     if (L->p) cudaFree(L->p);
     L->p = nullptr;
     L->cap = 0;
@@ -919,6 +971,16 @@ int hfb200_chan_exchange_stats(hfb200_ctx* c, long long* items, double* x3_flops
   if (x3_flops) *x3_flops = c->chan->last_x3_flops;
   if (stage_ms)
     for (int q = 0; q < 5; q++) stage_ms[q] = c->chan->stage_ms[q];
+  return HFB200_OK;
+}
+int hfb200_chan_exchange_counts(hfb200_ctx* c, long long* out, int n) {
+  if (!c || !c->chan || !out || n < 1) { hfb::set_error("hfb200_chan_exchange_counts: invalid argument"); return HFB200_EINVAL; }
+  for (int q = 0; q < n; q++) out[q] = q < 12 ? c->chan->counts[q] : 0;
+  return HFB200_OK;
+}
+int hfb200_chan_allreduce_ms(hfb200_ctx* c, double* ms) {
+  if (!c || !c->chan || !ms) { hfb::set_error("hfb200_chan_allreduce_ms: invalid argument"); return HFB200_EINVAL; }
+  *ms = c->chan->stage_ms[5];
   return HFB200_OK;
 }
 int hfb200_chan_exchange_batches(hfb200_ctx* c, int* nbatches) {

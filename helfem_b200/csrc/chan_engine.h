@@ -25,6 +25,9 @@ struct ChanSpec {
   std::vector<std::vector<ChanCoupling>> pair_coupl;  // [nang*nang], index k*nang + l
   std::vector<int> ang_group;              // [nang] optional: angular functions with equal value (m) share their coupling
                                            // partners; only used to tile the exchange contractions efficiently
+  std::vector<int> ang_m;                  // [nang] m of every angular function (which blocks of K can be non-zero for a given P)
+  std::vector<char> fam_owned;             // [nr] multi-GPU: this rank holds the integrals of family r (empty: all).  pair_coupl lists the
+                                           // couplings of ALL families: the bra contraction of a communicator-attached context needs them
   // in-element integrals of family r, element e, block (hout, hin) of the stacked matrix:
   // returns the (np_e^2 x np_e^2) column-major block and its sign, nullptr if the block is absent
   std::function<const double*(int r, int e, int hout, int hin, double* sign)> tei;
@@ -35,6 +38,7 @@ struct ChanSpec {
 };
 
 struct ChanEngine {
+  struct DevList { void* p = nullptr; size_t cap = 0; };
   ChanParams prm{};                 // device pointers + sizes
   int nrad = 0, nchan = 0, npair = 0;
   std::vector<int> first, last;
@@ -42,6 +46,16 @@ struct ChanEngine {
   DevBuf dP, dPc, dTr, dJc, dJ;
   PinBuf hIn, hOut;
   std::vector<int> fam_c0_host;
+  void* comm = nullptr;             // ncclComm_t (comm.cu) or null
+  std::vector<char> fam_owned;      // [nr]
+  std::vector<int> ang_m;           // [nang]
+  // bra-contraction CSR over the couplings of ALL families (prm.post_* covers the owned ones only)
+  const int *dPostAllPtr = nullptr, *dPostAllChan = nullptr;
+  const double* dPostAllCoef = nullptr;
+  // exchange all-reduce: the angular blocks of K that can be non-zero for the cached mask of P, packed
+  std::vector<int2> red_blocks;
+  DevList dRedBlocks;
+  DevBuf dRed;
   // exchange tables (chan_exchange.cuh)
   bool have_k = false;
   ChanXParams xprm{};
@@ -56,7 +70,6 @@ struct ChanEngine {
   std::vector<XBatch> batches;
   long long total_items = 0, max_wblocks = 0;
   int max_batch_items = 0;
-  struct DevList { void* p = nullptr; size_t cap = 0; };
   DevList dItems, dItemFam, dTiles2, dGroupsS, dGroupsP, dTileU, dSlotWblk, dSlotCoef, dWbase, dWbits, dOutPtr, dOutItem, dX1tab;
   int x1tab_ldp = -1;                               // leading dimension dX1tab was built for
   int ni_same = 32, ni_pair = 16;                   // items per CTA of the fused same-element / element-pair kernels
@@ -83,11 +96,12 @@ struct ChanEngine {
   const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;
   // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
   long long last_items = 0;
+  long long counts[12] = {0};       // per-pattern list sizes, see hfb200_chan_exchange_counts
   int nbatches() const { return (int)batches.size(); }
   double last_x3_flops = 0.0, last_same_flops = 0.0;
   // optional per-stage device timing of exchange_device (x0 mask, x1, x2, x3, x4), summed over families
   bool profile_stages = false;
-  float stage_ms[5] = {0, 0, 0, 0, 0};
+  float stage_ms[6] = {0, 0, 0, 0, 0, 0};  // mask, x1, fused same-element, fused pairs, x4, all-reduce
   std::vector<cudaEvent_t> ev_pool;
   void release();
 };

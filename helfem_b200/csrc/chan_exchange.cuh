@@ -355,4 +355,26 @@ static __global__ void __launch_bounds__(256) chan_x4_kernel(ChanXParams prm, co
   }
 }
 
+// Packed copies of a list of (nrad x nrad) angular blocks (j,k) of a dense matrix: the payload of the exchange all-reduce of a
+// sharded run.  grid (blocks), 256 threads.  mirror: also write block (k,j) = block(j,k)^T (symmetric operator, j <= k listed).
+static __global__ void __launch_bounds__(256) chan_blocks_gather_kernel(const double* M, int ld, int nrad, const int2* blk, double* packed) {
+  const int2 jk = blk[blockIdx.x];
+  const double* src = M + (size_t)jk.x * nrad + (size_t)jk.y * nrad * ld;
+  double* dst = packed + (size_t)blockIdx.x * nrad * nrad;
+  for (int e = threadIdx.x; e < nrad * nrad; e += 256) dst[e] = src[(e % nrad) + (size_t)(e / nrad) * ld];
+}
+static __global__ void __launch_bounds__(256) chan_blocks_scatter_kernel(double* M, int ld, int nrad, const int2* blk, const double* packed, int mirror) {
+  const int2 jk = blk[blockIdx.x];
+  const double* src = packed + (size_t)blockIdx.x * nrad * nrad;
+  double* dst = M + (size_t)jk.x * nrad + (size_t)jk.y * nrad * ld;
+  double* dstT = M + (size_t)jk.y * nrad + (size_t)jk.x * nrad * ld;
+  const bool mir = mirror && jk.x != jk.y;
+  for (int e = threadIdx.x; e < nrad * nrad; e += 256) {
+    const int a = e % nrad, b = e / nrad;
+    const double v = src[e];
+    dst[a + (size_t)b * ld] = v;
+    if (mir) dstT[b + (size_t)a * ld] = v;
+  }
+}
+
 }  // namespace hfb

@@ -84,6 +84,7 @@ struct hfb200_ctx {
   std::vector<int> lval, mval;
   double Rhalf = 0.0;
   int shard_rank = 0, shard_n = 1;  // integral families r with r % shard_n == shard_rank are owned
+  void* comm = nullptr;             // ncclComm_t of the sharded operators (comm.cu), or null: the caller sums the partial operators
   hfb::ChanEngine* chan = nullptr;
   hfb::Grid2D* g2d = nullptr;  // product-grid XC engine (grid2d.h)
   // ---- scratch ----

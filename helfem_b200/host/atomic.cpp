@@ -98,6 +98,12 @@ void TwoDBasis::compute_tei(bool exchange) {
   tei_uploaded = false;
 }
 
+void TwoDBasis::set_shard(int rank, int nranks) {
+  if (ctx) throw std::logic_error("set_shard must precede the first use of the device context\n");
+  shard_rank = rank;
+  shard_n = nranks;
+}
+
 hfb200_ctx* TwoDBasis::context() const {
   if (!ctx) {
     const size_t Nel = radial.Nel();

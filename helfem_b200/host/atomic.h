@@ -6,6 +6,7 @@
 // atomic/TwoDBasis.cpp:290-300), sign conventions (exchange returns -K) and error behaviour.
 // coulomb / exchange run on the GPU through the C ABI; there is no host implementation here.
 #pragma once
+#include <stdexcept>
 #include "fem.h"
 
 struct hfb200_ctx;
@@ -50,7 +51,7 @@ class TwoDBasis {
   const std::vector<Mat>& get_prim_ktei() const { return prim_ktei; }
   int get_nL() const { return nL_stored; }
   /// multi-GPU: this object contracts only the integral families r % nranks == rank (see hfb200_set_shard)
-  void set_shard(int rank, int nranks) { shard_rank = rank; shard_n = nranks; }
+  void set_shard(int rank, int nranks);  // throws std::logic_error once the device context exists (it is sharded at creation)
   hfb200_ctx* context() const;
 
  private:

@@ -9,6 +9,7 @@
 // basis.cpp:482-499) and sign conventions (exchange returns -K).  coulomb / exchange run on the GPU
 // through the C ABI; there is no host implementation of them here.
 #pragma once
+#include <stdexcept>
 #include <utility>
 #include "fem.h"
 
@@ -92,7 +93,7 @@ class TwoDBasis {
   const std::vector<Mat>& get_prim_tei() const { return prim_tei; }
   const std::vector<Mat>& get_prim_ktei() const { return prim_ktei; }
   /// multi-GPU: this object contracts only the integral families r % nranks == rank (see hfb200_set_shard)
-  void set_shard(int rank, int nranks) { shard_rank = rank; shard_n = nranks; }
+  void set_shard(int rank, int nranks);  // throws std::logic_error once the device context exists (it is sharded at creation)
   /// with a shard set: compute_tei only builds the stored integrals of the owned families (1/nranks of the setup
   /// time and host memory); the others stay empty and are never read
   void set_owned_only(bool on) { owned_only = on; }

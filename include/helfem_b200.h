@@ -81,6 +81,19 @@ void hfb200_destroy(hfb200_ctx* ctx);
  * the caller (NCCL over NVLink).  Call before *_set_tei. */
 int hfb200_set_shard(hfb200_ctx* ctx, int rank, int nranks);
 
+/* NCCL communicator of a sharded context (one process per GPU, like `mpirun`-style SPMD drivers; the reference's own drivers
+ * are single-process, diatomic/main.cpp:810-828).  Rank 0 obtains an id with hfb200_comm_unique_id (HFB200_COMM_ID_BYTES
+ * bytes) and hands it to the other ranks by any means; every rank then calls hfb200_comm_init on its context, sharded
+ * as the same (rank, nranks) with hfb200_set_shard.  From then on hfb200_chan_coulomb_device / hfb200_chan_exchange_device
+ * and the host-matrix calls of that context return the COMPLETE operator on every rank: the partial results are
+ * all-reduced inside the library on the call's stream over NVLink (coulomb: the per-channel radial results, a few MB;
+ * exchange: the angular blocks of K that can be non-zero for the sparsity pattern of P, packed).  The density must be
+ * the same on every rank.  NCCL is resolved with dlopen at the first hfb200_comm_* call. */
+#define HFB200_COMM_ID_BYTES 128
+int hfb200_comm_unique_id(void* id, int nbytes);
+int hfb200_comm_init(hfb200_ctx* ctx, const void* id, int rank, int nranks);
+int hfb200_comm_destroy(hfb200_ctx* ctx);
+
 /* J = coulomb(P): P, J are nrad x nrad (host). */
 int hfb200_sadatom_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);
 /* K = exchange(P): P, K are nrad x nrad x nslices cubes (slice stride ld*nrad); returns -K
@@ -167,11 +180,19 @@ int hfb200_diatomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* 
  * `stream` a cudaStream_t (NULL: the context's stream).  Same kernels as the host-matrix calls above without the
  * PCIe legs; the work is enqueued on `stream` (exchange synchronises it once to read back the block mask of P).
  * hfb200_chan_exchange_stats: output blocks (summed over integral families) and algorithmic flops of the
- * radial contraction of the last exchange call; stage_ms is filled when hfb200_chan_set_profile(ctx, 1) is on. */
+ * radial contraction of the last exchange call; stage_ms (mask, x1 left angular, fused same-element, fused element pairs, x4 assembly) is filled when
+ * hfb200_chan_set_profile(ctx, 1) is on. */
 int hfb200_chan_dim(hfb200_ctx* ctx, int* ndim);
 int hfb200_chan_coulomb_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dJ, int ldj, void* stream);
 int hfb200_chan_exchange_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dK, int ldk, void* stream);
 int hfb200_chan_exchange_stats(hfb200_ctx* ctx, long long* items, double* x3_flops, double* stage_ms /* [5] or NULL */);
+/* sizes of the per-sparsity-pattern lists of the last exchange call (bench accounting): out[0] output blocks contracted (summed
+ * over families), [1] tiles, [2] W sub-block slots read by the fused kernels, [3] the same padded to whole pipeline stages, [4] W blocks
+ * written by x1, [5] doubles per stack half of a W block, [6] distinct output blocks summed over batches, [7] family batches,
+ * [8] 1 if the symmetric (j <= k) list was used, [9] sum over tiles of slots x items (angular multiply-adds per sub-block entry and
+ * stack pair), [10] angular blocks in the all-reduce payload. */
+int hfb200_chan_exchange_counts(hfb200_ctx* ctx, long long* out, int n);
+int hfb200_chan_allreduce_ms(hfb200_ctx* ctx, double* ms); /* with profiling on: gather + NCCL all-reduce + scatter of the last exchange call */
 int hfb200_chan_exchange_batches(hfb200_ctx* ctx, int* nbatches); /* family batches of the last exchange call (5 launches each) */
 int hfb200_chan_set_profile(hfb200_ctx* ctx, int on); /* per-stage CUDA-event timing of exchange (mask, x1..x4) */
 
