@@ -146,6 +146,11 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
     }
     if ((rc = up(this, &dFirstJ, first)) || (rc = up(this, &dNpeJ, npe)) || (rc = up(this, &dElemOfJ, elem_of))) return rc;
   }
+  for (unsigned char** f : {&dPnz, &dCnz, &dOnz}) {
+    const size_t nbytes = (f == &dCnz) ? (size_t)nchan : (size_t)npair;
+    HFB_CUDA_OK(cudaMalloc(f, std::max<size_t>(nbytes, 1)));
+    owned.push_back(*f);
+  }
   have_k = false;
   if (with_exchange && S.ktei) return build_exchange(S);
   return 0;
@@ -611,11 +616,13 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
       (rc = dPc.reserve((size_t)nchan * nel * KP)) || (rc = dTr.reserve((size_t)nchan * nel * 2)) ||
       (rc = dJc.reserve((size_t)nchan * nel * MP)))
     return rc;
-  // pack: [pair = k*nang + l][element][np2]
+  // pack: [pair = k*nang + l][element][np2]; hPnzJ flags the pairs whose band has a non-zero entry (zero screening)
+  hPnzJ.assign((size_t)npair, 0);
 #pragma omp parallel for collapse(2) schedule(static)
   for (int k = 0; k < nang; k++)
     for (int l = 0; l < nang; l++) {
       double* dst = hIn.p + ((size_t)(k * nang + l) * nel) * np2;
+      unsigned char any = 0;
       for (int e = 0; e < nel; e++) {
         const int f = first[e], npe = last[e] - f + 1;
         double* blk = dst + (size_t)e * np2;
@@ -632,8 +639,11 @@ int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cuda
             }
           }
         }
+        for (int q = 0; q < np2 && !any; q++) any = blk[q] != 0.0;
       }
+      hPnzJ[(size_t)k * nang + l] = any;
     }
+  HFB_CUDA_OK(cudaMemcpyAsync(dPnz, hPnzJ.data(), (size_t)npair, cudaMemcpyHostToDevice, st));
   HFB_CUDA_OK(cudaMemcpyAsync(dP.p, hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, st));
   if ((rc = coulomb_kernels(nang, st))) return rc;
   HFB_CUDA_OK(cudaMemcpyAsync(hOut.p, dJ.p, nband * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -696,6 +706,7 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
   const int nel = prm.nel;
   ChanParams q = prm;
   q.nb = 1; q.P = dP.p; q.pc = dPc.p; q.traces = dTr.p; q.jc = dJc.p; q.J = dJ.p;
+  q.pnz = dPnz; q.cnz = dCnz; q.onz = dOnz;  // dPnz was filled by the caller's pack pass
   chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   int maxcol = 1;
@@ -714,6 +725,9 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
     if ((rc = comm_allreduce_sum(comm, dJc.p, (size_t)nchan * nel * 8 * prm.MT, st))) return rc;
     q.post_ptr = dPostAllPtr; q.post_chan = dPostAllChan; q.post_coef = dPostAllCoef;
   }
+  chan_flag_kernel<<<nchan, 128, 0, st>>>(q);
+  HFB_CUDA_OK(cudaGetLastError());
+  HFB_CUDA_OK(cudaMemsetAsync(dOnz, 0, (size_t)npair, st));
   chan_post_kernel<<<dim3(nel * npair, 1, 1), 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
@@ -727,11 +741,11 @@ int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj,
   if ((rc = dP.reserve(nband)) || (rc = dJ.reserve(nband)) || (rc = dPc.reserve((size_t)nchan * nel * KP)) ||
       (rc = dTr.reserve((size_t)nchan * nel * 2)) || (rc = dJc.reserve((size_t)nchan * nel * MP)))
     return rc;
-  chan_band_pack_kernel<<<dim3(nel * npair), 128, 0, st>>>(prm, dFirstJ, dNpeJ, nang, nrad, dPm, ldp, dP.p);
+  HFB_CUDA_OK(cudaMemsetAsync(dPnz, 0, (size_t)npair, st));
+  chan_band_pack_kernel<<<dim3(nel * npair), 128, 0, st>>>(prm, dFirstJ, dNpeJ, nang, nrad, dPm, ldp, dP.p, dPnz);
   HFB_CUDA_OK(cudaGetLastError());
   if ((rc = coulomb_kernels(nang, st))) return rc;
-  const size_t work = (size_t)npair * nrad * nrad;
-  chan_band_unpack_kernel<<<(unsigned)std::min<size_t>((work + 255) / 256, 148 * 16), 256, 0, st>>>(prm, dFirstJ, dElemOfJ, nang, nrad, dJ.p, dJm, ldj);
+  chan_band_unpack_kernel<<<(unsigned)npair, 256, 0, st>>>(prm, dFirstJ, dElemOfJ, nang, nrad, dJ.p, dJm, ldj, dOnz);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }

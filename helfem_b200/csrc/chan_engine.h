@@ -94,6 +94,8 @@ struct ChanEngine {
   int exchange_device(const double* dPm, int ldp, double* dKm, int ldk, cudaStream_t st);
   int coulomb_kernels(int nang, cudaStream_t st);
   const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;
+  std::vector<unsigned char> hPnzJ;  // host copy of the pair flags (host-matrix path)
+  unsigned char *dPnz = nullptr, *dCnz = nullptr, *dOnz = nullptr;  // zero-screening flags of the Coulomb kernels (chan_kernels.cuh)
   // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
   long long last_items = 0;
   long long counts[12] = {0};       // per-pattern list sizes, see hfb200_chan_exchange_counts

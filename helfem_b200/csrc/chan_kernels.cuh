@@ -46,6 +46,11 @@ struct ChanParams {
   double* traces;         // [nchan][nb][nel][2]
   double* jc;             // [nchan][nb][nel][8 MT]
   double* J;              // [nb][npair][nel][np2]
+  // zero screening (exact: a zero term adds nothing): pairs whose density band vanishes are skipped by the ket contraction,
+  // channels whose radial result vanishes by the bra contraction, pairs whose J band vanishes by the unpack
+  const unsigned char* pnz;  // [npair] the density band of the pair has a non-zero entry (nullptr: no screening)
+  unsigned char* cnz;        // [nchan] the channel result jc has a non-zero entry
+  unsigned char* onz;        // [npair] the J band of the pair has a non-zero entry
 };
 
 // grid (nel, nchan, nb), 128 threads
@@ -69,6 +74,7 @@ static __global__ void __launch_bounds__(128) chan_pre_kernel(ChanParams prm) {
       for (int e = e0; e < e1; e++) {
         const double cf = prm.pre_coef[2 * e + h];
         if (cf == 0.0) continue;
+        if (prm.pnz && !prm.pnz[prm.pre_pair[e]]) continue;
         const double* src = gP + (size_t)prm.pre_pair[e] * pstride;
         double p = src[a];
         if (ij.x != ij.y) p += src[at];
@@ -199,51 +205,80 @@ __global__ void __launch_bounds__(256) chan_jmma_kernel(ChanParams prm) {
     }
 }
 
+// [nchan] flags of the channel results (after the all-reduce of a sharded run): grid (nchan), 128 threads
+static __global__ void __launch_bounds__(128) chan_flag_kernel(ChanParams prm) {
+  const int c = blockIdx.x;
+  const double* src = prm.jc + (size_t)c * prm.nb * prm.nel * 8 * prm.MT;
+  int any = 0;
+  for (int k = threadIdx.x; k < prm.nb * prm.nel * 8 * prm.MT; k += blockDim.x) any |= (src[k] != 0.0);
+  any = __syncthreads_or(any);
+  if (threadIdx.x == 0) prm.cnz[c] = any ? 1 : 0;
+}
+
 // grid (nel * npair, 1, nb), 128 threads
 static __global__ void __launch_bounds__(128) chan_post_kernel(ChanParams prm) {
   const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, b = blockIdx.z;
   const int np = prm.np, np2 = prm.np2, MP = 8 * prm.MT;
   const int e0 = prm.post_ptr[pr], e1 = prm.post_ptr[pr + 1];
   double* out = prm.J + (((size_t)b * prm.npair + pr) * prm.nel + el) * np2;
+  int any = 0;
   for (int k = threadIdx.x; k < np2; k += blockDim.x) {
     const int i = k % np, j = k / np;
     const int lo = min(i, j), hi = max(i, j);
     const int m = lo + hi * (hi + 1) / 2;
     double v = 0.0;
     for (int e = e0; e < e1; e++) {
-      const double* src = prm.jc + (((size_t)prm.post_chan[e] * prm.nb + b) * prm.nel + el) * MP;
+      const int c = prm.post_chan[e];
+      if (prm.cnz && !prm.cnz[c]) continue;
+      const double* src = prm.jc + (((size_t)c * prm.nb + b) * prm.nel + el) * MP;
       v = fma(prm.post_coef[2 * e], src[m], v);
       if (prm.stack == 2) v = fma(prm.post_coef[2 * e + 1], src[prm.ntri + m], v);
     }
     out[k] = v;
+    any |= (v != 0.0);
+  }
+  if (prm.onz) {
+    any = __syncthreads_or(any);
+    if (threadIdx.x == 0 && any) prm.onz[pr] = 1;  // preset to zero; every writer stores the same value
   }
 }
 
 // Device-resident operator calls: gather the element-diagonal band of every angular pair out of a dense matrix,
 // grid (nel * npair), and the inverse (a radial index pair lies in at most two common elements), grid-stride.
 static __global__ void __launch_bounds__(128) chan_band_pack_kernel(ChanParams prm, const int* first, const int* npe, int nang, int nrad,
-                                                                    const double* D, int ld, double* band) {
+                                                                    const double* D, int ld, double* band, unsigned char* pnz) {
   const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, k = pr / nang, l = pr % nang;
   const int f = first[el], n = npe[el], np = prm.np;
   double* dst = band + ((size_t)pr * prm.nel + el) * prm.np2;
+  int any = 0;
   for (int q = threadIdx.x; q < prm.np2; q += blockDim.x) {
     const int i = q % np, j = q / np;
-    dst[q] = (i < n && j < n) ? D[(size_t)(k * nrad + f + i) + (size_t)(l * nrad + f + j) * ld] : 0.0;
+    const double v = (i < n && j < n) ? D[(size_t)(k * nrad + f + i) + (size_t)(l * nrad + f + j) * ld] : 0.0;
+    dst[q] = v;
+    any |= (v != 0.0);
   }
+  any = __syncthreads_or(any);
+  if (threadIdx.x == 0 && any) pnz[pr] = 1;  // preset to zero; every writer stores the same value
 }
-static __global__ void chan_band_unpack_kernel(ChanParams prm, const int* first, const int* elem_of, int nang, int nrad,
-                                               const double* band, double* D, int ld) {
-  const size_t per = (size_t)nrad * nrad, total = per * prm.npair;
-  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    const int pr = (int)(idx / per), a = (int)(idx % nrad), b = (int)((idx / nrad) % nrad);
+// grid (npair), 256 threads: the (nrad x nrad) block of one angular pair; zeros without touching the band when the pair's
+// J band vanishes (onz)
+static __global__ void __launch_bounds__(256) chan_band_unpack_kernel(ChanParams prm, const int* first, const int* elem_of, int nang, int nrad,
+                                                                      const double* band, double* D, int ld, const unsigned char* onz) {
+  const int pr = blockIdx.x;
+  double* dst = D + (size_t)(pr / nang) * nrad + (size_t)(pr % nang) * nrad * ld;
+  const bool live = onz == nullptr || onz[pr] != 0;
+  const double* src = band + (size_t)pr * prm.nel * prm.np2;
+  for (int idx = threadIdx.x; idx < nrad * nrad; idx += 256) {
+    const int a = idx % nrad, b = idx / nrad;
     double s = 0.0;
-    for (int x = 0; x < 2; x++) {
-      const int e = elem_of[2 * a + x];
-      if (e < 0) continue;
-      if (e == elem_of[2 * b] || e == elem_of[2 * b + 1])
-        s += band[((size_t)pr * prm.nel + e) * prm.np2 + (a - first[e]) + (b - first[e]) * prm.np];
+    if (live) {
+      for (int x = 0; x < 2; x++) {
+        const int e = elem_of[2 * a + x];
+        if (e < 0) continue;
+        if (e == elem_of[2 * b] || e == elem_of[2 * b + 1]) s += src[(size_t)e * prm.np2 + (a - first[e]) + (b - first[e]) * prm.np];
+      }
     }
-    D[(size_t)((pr / nang) * nrad + a) + (size_t)((pr % nang) * nrad + b) * ld] = s;
+    dst[a + (size_t)b * ld] = s;
   }
 }
 

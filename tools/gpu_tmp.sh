@@ -1,7 +1,2 @@
-set -x
-timeout 300 python bench.py --workload n2_hf_l4m1 --steps 5 > gpurun_out/r02i_bench_l4m1.json 2> gpurun_out/r02i_l4m1.err || tail -n 20 gpurun_out/r02i_l4m1.err
-python -c "import json; d=json.load(open('gpurun_out/r02i_bench_l4m1.json')); print(d['value'], d['e2e']['value'], d['cpu_baseline'])"
-timeout 600 python bench.py --steps 5 > gpurun_out/r02i_bench_cfg4.json 2> gpurun_out/r02i_cfg4.err || tail -n 20 gpurun_out/r02i_cfg4.err
-python -c "import json; d=json.load(open('gpurun_out/r02i_bench_cfg4.json')); print(d['value'], d['ms_per_step'], d['e2e'], d['cpu_baseline']); [print(e) for e in d['roofline']['stages']]"
-timeout 600 python bench.py --impl reference --steps 2 > gpurun_out/r02i_ref_cfg4.json 2> gpurun_out/r02i_ref.err || tail -n 20 gpurun_out/r02i_ref.err
-cat gpurun_out/r02i_ref_cfg4.json
+timeout 900 python -m pytest tests/test_atomic_gpu.py tests/test_diatomic_gpu.py tests/test_shard_gpu.py tests/test_hotpath_goldens.py tests/test_scf_energy_gpu.py tests/test_cfg4_fullsize_gpu.py -m gpu -x -q -s 2>&1 | tail -n 8
+timeout 300 python bench.py --workload n2_hf_cfg4 --steps 3 --warmup 1 --kernels-only 2>&1 | tail -n 2
