@@ -2,6 +2,7 @@
 #include "chan_engine.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -604,78 +605,6 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
   return 0;
 }
 
-// J = coulomb(P) with dense host matrices ((nang*nrad)^2, column-major, block (iang,jang) at rows
-// iang*nrad, cols jang*nrad: atomic/TwoDBasis.cpp:290-300).  Only the element-diagonal radial blocks of
-// each angular pair enter or leave the operator, so that is all that crosses PCIe.
-int ChanEngine::coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map, int nout) {
-  const int nel = prm.nel, np = prm.np, np2 = prm.np2, nang = (int)std::lround(std::sqrt((double)npair));
-  const size_t nband = (size_t)npair * nel * np2;
-  const int KP = 4 * prm.KS, MP = 8 * prm.MT;
-  int rc;
-  if ((rc = hIn.reserve(nband)) || (rc = hOut.reserve(nband)) || (rc = dP.reserve(nband)) || (rc = dJ.reserve(nband)) ||
-      (rc = dPc.reserve((size_t)nchan * nel * KP)) || (rc = dTr.reserve((size_t)nchan * nel * 2)) ||
-      (rc = dJc.reserve((size_t)nchan * nel * MP)))
-    return rc;
-  // pack: [pair = k*nang + l][element][np2]; hPnzJ flags the pairs whose band has a non-zero entry (zero screening)
-  hPnzJ.assign((size_t)npair, 0);
-#pragma omp parallel for collapse(2) schedule(static)
-  for (int k = 0; k < nang; k++)
-    for (int l = 0; l < nang; l++) {
-      double* dst = hIn.p + ((size_t)(k * nang + l) * nel) * np2;
-      unsigned char any = 0;
-      for (int e = 0; e < nel; e++) {
-        const int f = first[e], npe = last[e] - f + 1;
-        double* blk = dst + (size_t)e * np2;
-        if (npe < np) memset(blk, 0, sizeof(double) * np2);
-        if (!map) {
-          for (int j = 0; j < npe; j++)
-            memcpy(blk + (size_t)j * np, P + (size_t)(k * nrad + f) + (size_t)(l * nrad + f + j) * ldp, sizeof(double) * npe);
-        } else {
-          for (int j = 0; j < npe; j++) {
-            const int pc = map[l * nrad + f + j];
-            for (int i = 0; i < npe; i++) {
-              const int pr = map[k * nrad + f + i];
-              blk[(size_t)j * np + i] = (pr < 0 || pc < 0) ? 0.0 : P[(size_t)pr + (size_t)pc * ldp];
-            }
-          }
-        }
-        for (int q = 0; q < np2 && !any; q++) any = blk[q] != 0.0;
-      }
-      hPnzJ[(size_t)k * nang + l] = any;
-    }
-  HFB_CUDA_OK(cudaMemcpyAsync(dPnz, hPnzJ.data(), (size_t)npair, cudaMemcpyHostToDevice, st));
-  HFB_CUDA_OK(cudaMemcpyAsync(dP.p, hIn.p, nband * sizeof(double), cudaMemcpyHostToDevice, st));
-  if ((rc = coulomb_kernels(nang, st))) return rc;
-  HFB_CUDA_OK(cudaMemcpyAsync(hOut.p, dJ.p, nband * sizeof(double), cudaMemcpyDeviceToHost, st));
-  const int ntot = map ? nout : nang * nrad;
-#pragma omp parallel for schedule(static)
-  for (int c = 0; c < ntot; c++) memset(J + (size_t)c * ldj, 0, sizeof(double) * ntot);
-  HFB_CUDA_OK(cudaStreamSynchronize(st));
-#pragma omp parallel for collapse(2) schedule(static)
-  for (int i = 0; i < nang; i++)
-    for (int j = 0; j < nang; j++) {
-      const double* src = hOut.p + ((size_t)(i * nang + j) * nel) * np2;
-      for (int e = 0; e < nel; e++) {
-        const int f = first[e], npe = last[e] - f + 1;
-        if (!map) {
-          for (int b = 0; b < npe; b++)
-            for (int a = 0; a < npe; a++)
-              J[(size_t)(i * nrad + f + a) + (size_t)(j * nrad + f + b) * ldj] += src[(size_t)e * np2 + a + (size_t)b * np];
-        } else {
-          for (int b = 0; b < npe; b++) {
-            const int pc = map[j * nrad + f + b];
-            if (pc < 0) continue;
-            for (int a = 0; a < npe; a++) {
-              const int pr = map[i * nrad + f + a];
-              if (pr >= 0) J[(size_t)pr + (size_t)pc * ldj] += src[(size_t)e * np2 + a + (size_t)b * np];
-            }
-          }
-        }
-      }
-    }
-  return 0;
-}
-
 namespace {
 // the max-dynamic-shared-memory attribute is set per launch: it belongs to the current device's context (one process can
 // hold contexts on several GPUs)
@@ -750,61 +679,113 @@ int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj,
   return 0;
 }
 
-// -K = exchange(P), dense host matrices.  map (optional): operator index -> row/column of the caller's matrices, -1 for
-// rows that are identically zero (the diatomic boundary functions); the caller's matrices are nout x nout.
-// The matrix is staged through one pinned buffer in column chunks so that packing, H2D, D2H and unpacking overlap.
-int ChanEngine::exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map, int nout) {
-  if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
-  const int nang = xprm.nang, ntot = nang * nrad;
-  (void)nout;
+// Host-matrix operators (the reference's interface: dense arma::mat in, dense zero-filled arma::mat out;
+// atomic/TwoDBasis.cpp:817,957, diatomic/basis.cpp:1359,1532 with expand / remove_boundaries :1735-1773 folded in).
+// map (optional): operator index -> row / column of the caller's nout x nout matrices, -1 for the rows that are identically
+// zero (the diatomic boundary functions); an angular function's rows must be consecutive in the caller's matrix.
+// Only what can be non-zero crosses PCIe: the host scans P for its non-zero angular blocks (the same Frobenius-free test
+// "any non-zero entry"; blocks below the reference's 10 eps norm screen are dropped again on the device) and uploads those,
+// packed; the result comes back as the packed blocks (j,k) with m_j - m_k = m_i - m_l for some non-zero P[i,l] -- every other
+// block of J or K vanishes identically -- and is scattered into the caller's matrix, which is zero-filled while the GPU works.
+int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, int ldf, cudaStream_t st, const int* map, int nout) {
+  if (exchange && !have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  const int nang = (int)std::lround(std::sqrt((double)npair)), ntot = nang * nrad;
+  const size_t nrad2 = (size_t)nrad * nrad;
+  if (!map) nout = ntot;
   int rc;
-  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) || (rc = hX.reserve((size_t)ntot * ntot)))
+  const bool verbose = getenv("HFB200_X_VERBOSE") != nullptr;
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_start = now();
+  double t_scan = 0, t_pack = 0, t_dev = 0, t_zero = 0, t_wait = 0;
+  // rows of angular function i in the caller's matrix: r0[i] .. r0[i] + cnt[i] - 1  <->  radial index skip[i] ..
+  std::vector<int> r0(nang), skip(nang), cnt(nang);
+  for (int i = 0; i < nang; i++) {
+    if (!map) { r0[i] = i * nrad; skip[i] = 0; cnt[i] = nrad; continue; }
+    int a0 = 0;
+    while (a0 < nrad && map[i * nrad + a0] < 0) a0++;
+    skip[i] = a0; cnt[i] = nrad - a0; r0[i] = a0 < nrad ? map[i * nrad + a0] : 0;
+    for (int a = a0; a < nrad; a++)
+      if (map[i * nrad + a] != r0[i] + (a - a0)) { set_error("index map: the rows of an angular function must be consecutive"); return HFB200_EINVAL; }
+  }
+  // ---- scan: non-zero angular blocks of P ----
+  std::vector<unsigned char> nz((size_t)npair, 0);
+#pragma omp parallel for collapse(2) schedule(dynamic, 16)
+  for (int i = 0; i < nang; i++)
+    for (int l = 0; l < nang; l++) {
+      unsigned char any = 0;
+      for (int b = 0; b < cnt[l] && !any; b++) {
+        const double* col = P + (size_t)r0[i] + (size_t)(r0[l] + b) * ldp;
+        for (int a = 0; a < cnt[i]; a++) any |= (col[a] != 0.0);
+      }
+      nz[(size_t)i * nang + l] = any;
+    }
+  t_scan = now() - t_start;
+  std::vector<int2> inb;
+  for (int i = 0; i < nang; i++)
+    for (int l = 0; l < nang; l++)
+      if (nz[(size_t)i * nang + l]) inb.push_back(make_int2(i, l));
+  // output blocks that can be non-zero
+  std::vector<int2> outb;
+  {
+    int mlo = 0, mhi = 0;
+    for (int a = 0; a < nang; a++) { mlo = std::min(mlo, ang_m[a]); mhi = std::max(mhi, ang_m[a]); }
+    const int span = mhi - mlo;
+    std::vector<char> dset(2 * span + 1, 0);
+    for (const int2& b : inb) dset[ang_m[b.x] - ang_m[b.y] + span] = 1;
+    for (int j = 0; j < nang; j++)
+      for (int k = 0; k < nang; k++)
+        if (dset[ang_m[j] - ang_m[k] + span]) outb.push_back(make_int2(j, k));
+  }
+  if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) ||
+      (rc = hX.reserve(std::max<size_t>(std::max(inb.size(), outb.size()), 1) * nrad2)) ||
+      (rc = dRed.reserve(std::max<size_t>(std::max(inb.size(), outb.size()), 1) * nrad2)) || (rc = up_list(dIoBlocks, inb)))
     return rc;
-  const int nchunk = ntot >= 4096 ? 16 : 1;
-  std::vector<cudaEvent_t> ev(nchunk);
-  for (auto& e : ev) HFB_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  for (int ch = 0; ch < nchunk; ch++) {
-    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
-#pragma omp parallel for schedule(static)
-    for (int c = c0; c < c1; c++) {
-      double* dst = hX.p + (size_t)c * ntot;
-      if (!map) {
-        memcpy(dst, P + (size_t)c * ldp, sizeof(double) * ntot);
-      } else {
-        const int pc = map[c];
-        if (pc < 0) { memset(dst, 0, sizeof(double) * ntot); continue; }
-        const double* src = P + (size_t)pc * ldp;
-        for (int r = 0; r < ntot; r++) dst[r] = map[r] < 0 ? 0.0 : src[map[r]];
-      }
-    }
-    HFB_CUDA_OK(cudaMemcpyAsync(dPdense.p + (size_t)c0 * ntot, hX.p + (size_t)c0 * ntot, (size_t)(c1 - c0) * ntot * sizeof(double),
-                                cudaMemcpyHostToDevice, st));
-  }
-  if ((rc = exchange_device(dPdense.p, ntot, dKdense.p, ntot, st))) return rc;
-  for (int ch = 0; ch < nchunk; ch++) {
-    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
-    HFB_CUDA_OK(cudaMemcpyAsync(hX.p + (size_t)c0 * ntot, dKdense.p + (size_t)c0 * ntot, (size_t)(c1 - c0) * ntot * sizeof(double),
-                                cudaMemcpyDeviceToHost, st));
-    HFB_CUDA_OK(cudaEventRecord(ev[ch], st));
-  }
-  for (int ch = 0; ch < nchunk; ch++) {
-    const int c0 = (int)((long)ntot * ch / nchunk), c1 = (int)((long)ntot * (ch + 1) / nchunk);
-    HFB_CUDA_OK(cudaEventSynchronize(ev[ch]));
-#pragma omp parallel for schedule(static)
-    for (int c = c0; c < c1; c++) {
-      const double* src = hX.p + (size_t)c * ntot;
-      if (!map) {
-        memcpy(K + (size_t)c * ldk, src, sizeof(double) * ntot);
-      } else {
-        const int pc = map[c];
-        if (pc < 0) continue;
-        double* dst = K + (size_t)pc * ldk;
-        for (int r = 0; r < ntot; r++)
-          if (map[r] >= 0) dst[map[r]] = src[r];
-      }
+  // ---- pack the non-zero blocks (dummy-space layout, zero rows / columns for the removed functions) and upload ----
+#pragma omp parallel for schedule(dynamic, 4)
+  for (long q = 0; q < (long)inb.size(); q++) {
+    const int i = inb[q].x, l = inb[q].y;
+    double* dst = hX.p + (size_t)q * nrad2;
+    for (int b = 0; b < nrad; b++) {
+      double* dc = dst + (size_t)b * nrad;
+      if (b < skip[l]) { memset(dc, 0, sizeof(double) * nrad); continue; }
+      for (int a = 0; a < skip[i]; a++) dc[a] = 0.0;
+      memcpy(dc + skip[i], P + (size_t)r0[i] + (size_t)(r0[l] + b - skip[l]) * ldp, sizeof(double) * cnt[i]);
     }
   }
-  for (auto& e : ev) cudaEventDestroy(e);
+  HFB_CUDA_OK(cudaMemcpyAsync(dRed.p, hX.p, inb.size() * nrad2 * sizeof(double), cudaMemcpyHostToDevice, st));
+  HFB_CUDA_OK(cudaMemsetAsync(dPdense.p, 0, (size_t)ntot * ntot * sizeof(double), st));
+  if (!inb.empty()) {
+    chan_blocks_scatter_kernel<<<(unsigned)inb.size(), 256, 0, st>>>(dPdense.p, ntot, nrad, (const int2*)dIoBlocks.p, dRed.p, 0);
+    HFB_CUDA_OK(cudaGetLastError());
+  }
+  // hX is reused for the download: the upload must have left it
+  HFB_CUDA_OK(cudaStreamSynchronize(st));
+  t_pack = now() - t_start - t_scan;
+  if ((rc = exchange ? exchange_device(dPdense.p, ntot, dKdense.p, ntot, st) : coulomb_device(dPdense.p, ntot, dKdense.p, ntot, st))) return rc;
+  if ((rc = up_list(dIoBlocks, outb))) return rc;  // (synchronous copy: ordered after the kernels that read the input list)
+  if (!outb.empty()) {
+    chan_blocks_gather_kernel<<<(unsigned)outb.size(), 256, 0, st>>>(dKdense.p, ntot, nrad, (const int2*)dIoBlocks.p, dRed.p);
+    HFB_CUDA_OK(cudaGetLastError());
+    HFB_CUDA_OK(cudaMemcpyAsync(hX.p, dRed.p, outb.size() * nrad2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  }
+  t_dev = now() - t_start - t_scan - t_pack;  // host side of the operator call (list upkeep, launches)
+  // zero-fill the caller's matrix while the device works (the reference returns a zero-filled dense matrix)
+  const double t_z0 = now();
+#pragma omp parallel for schedule(static)
+  for (int c = 0; c < nout; c++) memset(F + (size_t)c * ldf, 0, sizeof(double) * nout);
+  t_zero = now() - t_z0;
+  HFB_CUDA_OK(cudaStreamSynchronize(st));
+  t_wait = now() - t_z0 - t_zero;
+#pragma omp parallel for schedule(dynamic, 4)
+  for (long q = 0; q < (long)outb.size(); q++) {
+    const int j = outb[q].x, k = outb[q].y;
+    const double* src = hX.p + (size_t)q * nrad2;
+    for (int b = skip[k]; b < nrad; b++)
+      memcpy(F + (size_t)r0[j] + (size_t)(r0[k] + b - skip[k]) * ldf, src + (size_t)b * nrad + skip[j], sizeof(double) * cnt[j]);
+  }
+  if (verbose)
+    fprintf(stderr, "[hfb200] %s host call: scan %.1f ms, pack+upload %.1f ms (%zu blocks), launches %.1f ms, zero-fill %.1f ms, wait %.1f ms, total %.1f ms (%zu blocks back)\n",
+            exchange ? "exchange" : "coulomb", 1e3 * t_scan, 1e3 * t_pack, inb.size(), 1e3 * t_dev, 1e3 * t_zero, 1e3 * t_wait, 1e3 * (now() - t_start), outb.size());
   return 0;
 }
 
@@ -946,7 +927,7 @@ void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
   for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRed}) b->release();
-  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab, &dRedBlocks}) {
+  for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab, &dRedBlocks, &dIoBlocks}) {
     if (L->p) cudaFree(L->p);
     L->p = nullptr;
     L->cap = 0;

@@ -86,15 +86,16 @@ struct ChanEngine {
   int build(const ChanSpec& spec, bool with_exchange);
   // dense HOST matrices; map (optional, length nang*nrad): operator index -> row/column of the caller's nout x nout
   // matrices, -1 = identically zero row (diatomic boundary functions, diatomic/basis.cpp:1735-1773)
-  int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map = nullptr, int nout = 0);
-  int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map = nullptr, int nout = 0);
+  int dense_apply(bool exchange, const double* P, int ldp, double* F, int ldf, cudaStream_t st, const int* map = nullptr, int nout = 0);
+  int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map = nullptr, int nout = 0) { return dense_apply(false, P, ldp, J, ldj, st, map, nout); }
+  int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map = nullptr, int nout = 0) { return dense_apply(true, P, ldp, K, ldk, st, map, nout); }
+  DevList dIoBlocks;                // block list of the host-matrix calls (input blocks, then output blocks)
   PinBuf hX;
   // device-resident variants: dense (nang*nrad)^2 matrices already in HBM; every kernel of the operator, no PCIe
   int coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st);
   int exchange_device(const double* dPm, int ldp, double* dKm, int ldk, cudaStream_t st);
   int coulomb_kernels(int nang, cudaStream_t st);
   const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;
-  std::vector<unsigned char> hPnzJ;  // host copy of the pair flags (host-matrix path)
   unsigned char *dPnz = nullptr, *dCnz = nullptr, *dOnz = nullptr;  // zero-screening flags of the Coulomb kernels (chan_kernels.cuh)
   // statistics of the last exchange call (bench.py): output blocks summed over families, algorithmic flops of x3
   long long last_items = 0;

@@ -125,6 +125,13 @@ class DiatomicBasis:
         then return the complete J / K on every rank (all-reduce inside the library)."""
         check(lib().hfb200_comm_init(self.context(), ctypes.c_char_p(uid), int(rank), int(nranks)))
 
+    def coulomb_into(self, P, J):
+        """coulomb with a caller-owned output (Fortran-ordered float64, fully overwritten): no allocation per call."""
+        check_host(lib().hfh_diatomic_coulomb(self._h, _p(P), _p(J)))
+
+    def exchange_into(self, P, K):
+        check_host(lib().hfh_diatomic_exchange(self._h, _p(P), _p(K)))
+
     def coulomb(self, P):
         P = np.asfortranarray(P, dtype=np.float64)
         J = np.zeros_like(P, order="F")

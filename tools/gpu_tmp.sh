@@ -1,2 +1,2 @@
-timeout 900 python -m pytest tests/test_atomic_gpu.py tests/test_diatomic_gpu.py tests/test_shard_gpu.py tests/test_hotpath_goldens.py tests/test_scf_energy_gpu.py tests/test_cfg4_fullsize_gpu.py -m gpu -x -q -s 2>&1 | tail -n 8
-timeout 300 python bench.py --workload n2_hf_cfg4 --steps 3 --warmup 1 --kernels-only 2>&1 | tail -n 2
+HFB200_X_VERBOSE=1 timeout 600 python bench.py --steps 3 > gpurun_out/r02k_bench_cfg4.json 2> gpurun_out/r02k_cfg4.err; grep "host call" gpurun_out/r02k_cfg4.err | tail -n 4
+python -c "import json; d=json.load(open('gpurun_out/r02k_bench_cfg4.json')); print(d['value'], d['ms_per_step'], d['e2e'])"
