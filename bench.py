@@ -56,6 +56,9 @@ WORKLOADS = {
                              desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 6, mmax 2, 3 elements, ldft 4 lmax+12, mdft 4 mmax+5"),
     "n2_pbe_grid_l2m1": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=2, mmax=1, nelem=2, nnodes=5, primbas=4, x=101, c=130,
                              desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 2, mmax 1 (oracle-sized)"),
+    # the Z sweep (configs[4]): one shared Kr-type basis, every atom's trial configurations, dynamic queue over the ranks
+    "sweep_z1_86": dict(kind="sweep", zmin=1, zmax=86, primbas=4, nnodes=15, nelem=20, taylor=-1, lmax=3, x=101, c=130,
+                        desc="gensap --Z 1..86 --nelem 20 --nnodes 15 --primbas 4 --method gga_x_pbe-gga_c_pbe (configs[4]), one process group"),
     "ne_pbe_small": dict(Z=10, primbas=4, nnodes=15, nelem=5, taylor=-1, lmax=2, x=101, c=130, nspin=1,
                          desc="small smoke case"),
 }
@@ -783,6 +786,170 @@ def run_chan(args, w, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def sweep_units(b, w):
+    """Units of the Z = 1..86 sweep (BASELINE configs[4]) on ONE shared radial basis (the basis does not depend on Z): for every
+    atom the trial configurations of a gensap-style occupation search (tests/util.trial_configurations), each a mock SCF of
+    niter(Z) Fock builds.  Returns (units, bands): units[u] = dict(Z, occ, niter, first build, ground), bands [nbuilds][2][nsl][blk]
+    of spin densities / 4 pi as FockBuild passes them (sadatom/solver.cpp:784,804), heavy units first."""
+    import scipy.linalg
+    from util import trial_configurations
+    from helfem_b200 import shard
+    lmax, nsl = w["lmax"], w["lmax"] + 1
+    S, T, Tl, V1 = b.overlap(), b.kinetic(), b.kinetic_l(), b.nuclear()  # the basis was built with Z = 1: V(Z) = Z V(1)
+    blk = b.nel * b.np_max ** 2
+    units = []
+    for Z in range(w["zmin"], w["zmax"] + 1):
+        orb = [scipy.linalg.eigh(T + l * (l + 1) * Tl + Z * V1, S)[1] for l in range(nsl)]
+        for ic, occ in enumerate(trial_configurations(Z, lmax)):
+            units.append(dict(Z=Z, occ=occ, niter=8 + Z // 8, ground=(ic == 0), orb=orb))
+    order = shard.heavy_first([u["niter"] for u in units])
+    units = [units[q] for q in order]
+    nbuilds = sum(u["niter"] for u in units)
+    bands = np.zeros((nbuilds, 2, nsl, blk))
+    first = 0
+    for u in units:
+        u["first"] = first
+        P = np.zeros((2, nsl, blk))
+        for si, spin in enumerate("ab"):
+            for l in range(nsl):
+                cap = (2 * l + 1)
+                numl = (u["occ"][l] + (1 if spin == "a" else 0)) // 2
+                D = np.zeros_like(S)
+                io = 0
+                while numl > 0:  # sadatom's fractional shell filling (sadatom/solver.cpp:386-398)
+                    k = min(cap, numl)
+                    D += k * np.outer(u["orb"][l][:, io], u["orb"][l][:, io])
+                    numl -= k
+                    io += 1
+                P[si, l] = b.pack_band(np.asfortranarray(D / (4 * np.pi)))
+        for it in range(u["niter"]):  # the iterations of the mock SCF see slightly different densities
+            bands[first + it] = P * (1.0 + 1e-3 * it)
+        first += u["niter"]
+        del u["orb"]
+    return units, bands
+
+
+def run_sweep(args, w, rank, world, local_rank):
+    """sadatom sweep Z = 1..86 with PBE (BASELINE configs[4]): independent units, no data-path collective; the ranks draw chunks of
+    units from one shared heavy-first queue (helfem_b200/shard.WorkQueue); rank 0 gathers Exc and Nel of every build."""
+    import torch
+    import helfem_b200 as hb
+    from helfem_b200 import shard
+    if not torch.cuda.is_available() or hb.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: helfem_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    b = hb.SadatomBasis(Z=1, nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"], taylor_order=w["taylor"], lmax=w["lmax"], device=local_rank)
+    b.compute_tei(1, False)
+    units, bands = sweep_units(b, w)
+    nsl, blk = w["lmax"] + 1, b.nel * b.np_max ** 2
+    nbuilds = bands.shape[0]
+    hP = torch.from_numpy(bands).pin_memory()
+    dP = hP.cuda()
+    dJ = torch.zeros((nbuilds, blk), dtype=torch.float64, device="cuda")
+    dH = torch.zeros((nbuilds, 2, nsl, blk), dtype=torch.float64, device="cuda")
+    dS = torch.zeros((nbuilds, 4), dtype=torch.float64, device="cuda")
+    hJ = torch.zeros((nbuilds, blk), dtype=torch.float64).pin_memory()
+    hH = torch.zeros((nbuilds, 2, nsl, blk), dtype=torch.float64).pin_memory()
+    hS = torch.zeros((nbuilds, 4), dtype=torch.float64).pin_memory()
+    stream = torch.cuda.current_stream()
+    sh = stream.cuda_stream
+    x, c, thr = w["x"], w["c"], 1e-12
+    chunk = max(1, len(units) // (4 * world))
+    queue = shard.WorkQueue(list(range(len(units))), chunk=chunk)
+    perP, perH = 2 * nsl * blk, 2 * nsl * blk
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_pass(host):
+        """Every rank drains the shared queue once; returns the builds this rank did."""
+        barrier()
+        queue.reset()
+        barrier()
+        done = 0
+        while True:
+            ids = queue.claim()
+            if not ids:
+                break
+            f0 = units[ids[0]]["first"]
+            nb = sum(units[u]["niter"] for u in ids)  # consecutive queue entries are consecutive in memory
+            if host:
+                P_, J_, H_, S_ = (t.numpy().reshape(nbuilds, -1)[f0:f0 + nb] for t in (hP, hJ, hH, hS))
+                b.fock_host(nb, x, c, 2, nsl, thr, P_, J_, H_, S_)
+            else:
+                b.fock_batch(nb, x, c, 2, nsl, thr, dP.data_ptr() + f0 * perP * 8, dJ.data_ptr() + f0 * blk * 8, dH.data_ptr() + f0 * perH * 8,
+                             dS.data_ptr() + f0 * 32, sh)
+            done += nb
+        torch.cuda.synchronize()
+        return done
+
+    for _ in range(max(args.warmup, 3)):
+        one_pass(False)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    mine = 0
+    for _ in range(args.steps):
+        mine += one_pass(False)
+    barrier()
+    t_dev = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    one_pass(True)
+    barrier()
+    t0 = time.perf_counter()
+    ne2e = max(1, args.steps // 2)
+    for _ in range(ne2e):
+        one_pass(True)
+    barrier()
+    t_e2e = (time.perf_counter() - t0) / ne2e
+    share = [mine]
+    if dist is not None:
+        t = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_dev, t_e2e = float(t[0]), float(t[1])
+        share = [None] * world
+        dist.all_gather_object(share, mine)
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    # rank 0: one clean single-rank pass for the gathered table (Exc, Nel of every atom's ground configuration)
+    dS.zero_()
+    b.fock_batch(nbuilds, x, c, 2, nsl, thr, dP.data_ptr(), dJ.data_ptr(), dH.data_ptr(), dS.data_ptr(), sh)
+    torch.cuda.synchronize()
+    sc = dS.cpu().numpy()
+    table = {u["Z"]: (float(sc[u["first"], 0]), float(sc[u["first"], 1])) for u in units if u["ground"]}
+    max_dnel = max(abs(table[Z][1] - Z) for Z in table)
+    hbm_peak, hbm_src = peaks()
+    value = nbuilds * args.steps / t_dev
+    line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "operators": "coulomb + eval_Fxc (unrestricted PBE)", "atoms": len(table),
+                       "units": len(units), "builds_per_step": nbuilds, "queue_chunk_units": chunk,
+                       "partition": "one shared heavy-first queue of (atom, trial configuration) units over the ranks (TCP store counter), no data-path "
+                                    "collective; rank 0 gathers Exc / Nel", "builds_per_rank": share,
+                       "timing": "wall clock around the drained queue (host claims + launches + device), max over ranks",
+                       "l2": "P + J + H bands = %.0f MB per step" % ((bands.nbytes * 2 + nbuilds * blk * 8) / 1e6)},
+            "roofline": None, "cpu_baseline": None,
+            "e2e": {"value": nbuilds / t_e2e, "unit": "builds/s", "h2d_bytes_per_step": int(bands.nbytes), "d2h_bytes_per_step": int(bands.nbytes + nbuilds * (blk + 4) * 8),
+                    "api": "hfb200_sadatom_fock_host per claimed chunk (pinned host bands)"},
+            "checks": {"max_abs_Nel_minus_Z": max_dnel, "Exc_H": table[min(table)][0], "Exc_last": table[max(table)][0]},
+            "gpu_launches": int(args.steps * 3 * ((len(units) + chunk - 1) // chunk)), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def run_grid2d(args, w, rank, world, local_rank):
     """DFTGrid::eval_Fxc of the diatomic program through the host mirror class (dense host matrices in and out)."""
     import torch
@@ -854,6 +1021,13 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     w = WORKLOADS[args.workload]
+    if w.get("kind") == "sweep":
+        if args.impl == "reference":
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "the CPU arm of the sweep is the kr_pbe_cfg2 reference arm (same basis, same operators)"}))
+            return
+        run_sweep(args, w, rank, world, local_rank)
+        return
     if w.get("kind") == "grid2d":
         if rank == 0 and args.impl != "reference":
             run_grid2d(args, w, rank, world, local_rank)

@@ -57,6 +57,42 @@ def allreduce_operator(M, group=None, device=None):
     return np.asfortranarray(out.T) if fortran else out
 
 
+def heavy_first(costs):
+    """Unit order of a sweep: most expensive first (longest-processing-time rule), ties by index."""
+    return sorted(range(len(costs)), key=lambda u: (-costs[u], u))
+
+
+class WorkQueue:
+    """Dynamic queue of independent units (atoms x trial configurations of the sadatom sweep, BASELINE configs[4]) over the
+    ranks of a process group: the reference runs one process per atom (/root/reference/src/sadatom/main.cpp:101); here
+    every rank claims the next `chunk` units of a heavy-first order from ONE shared atomic counter (the process group's
+    key-value store), so a rank that drew cheap atoms simply comes back sooner.  No data-path collective.
+    Without an initialised process group the counter is local."""
+
+    def __init__(self, order, chunk=1, name="hfb200_queue", store=None):
+        import torch.distributed as dist
+        self.order, self.chunk, self.name = list(order), max(1, int(chunk)), name
+        self.store = store
+        if self.store is None and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            self.store = dist.distributed_c10d._get_default_store()
+        self._local = 0
+        self._epoch = 0
+
+    def reset(self):
+        """Start a new pass (collective in spirit: every rank calls it between two barriers)."""
+        self._epoch += 1
+        self._local = 0
+
+    def claim(self):
+        """Next chunk of unit ids, or [] when the queue is drained."""
+        if self.store is None:
+            begin = self._local
+            self._local += self.chunk
+        else:
+            begin = self.store.add("%s/%d" % (self.name, self._epoch), self.chunk) - self.chunk
+        return self.order[begin:begin + self.chunk] if begin < len(self.order) else []
+
+
 _block_cache = {}
 
 

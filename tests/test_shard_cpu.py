@@ -95,11 +95,28 @@ def _worker(rank, world, port, q):
         b, e = shard.partition_units(7, rank, world)
         counts = [None] * world
         dist.all_gather_object(counts, e - b)
+        # dynamic heavy-first queue of the sadatom sweep: two passes; every unit is claimed exactly once per pass
+        costs = [1 + (u * 7) % 11 for u in range(23)]
+        wq = shard.WorkQueue(shard.heavy_first(costs), chunk=3)
+        claimed = []
+        for _ in range(2):
+            dist.barrier()
+            wq.reset()
+            dist.barrier()
+            mine = []
+            while True:
+                c = wq.claim()
+                if not c:
+                    break
+                mine += c
+            allc = [None] * world
+            dist.all_gather_object(allc, mine)
+            claimed.append(allc)
         dist.destroy_process_group()
-        q.put((rank, J, K, float(np.max(np.abs(Jp))), counts))
+        q.put((rank, J, K, float(np.max(np.abs(Jp))), counts, claimed, costs))
     except Exception as ex:  # pragma: no cover
         import traceback
-        q.put((rank, "ERR", traceback.format_exc(), 0, None))
+        q.put((rank, "ERR", traceback.format_exc(), 0, None, None, None))
 
 
 @pytest.mark.timeout(300)
@@ -119,7 +136,13 @@ def test_allreduce_of_family_partials_gloo_world2():
     res.sort(key=lambda r: r[0])
     o, P = _atomic_oracle_partial(0, 1)  # all families
     Jfull, Kfull = o.coulomb(P), o.exchange(P)
-    for rank, J, K, pmax, counts in res:
+    for rank, J, K, pmax, counts, claimed, costs in res:
+        from helfem_b200 import shard
+        for allc in claimed:
+            flat = sum(allc, [])
+            assert sorted(flat) == list(range(len(costs)))          # every unit exactly once
+            for mine in allc:                                        # each rank sees its units heaviest first
+                assert [costs[u] for u in mine] == sorted((costs[u] for u in mine), reverse=True)
         assert np.max(np.abs(J - Jfull)) <= 1e-12 * max(1.0, np.max(np.abs(Jfull)))
         assert np.max(np.abs(K - Kfull)) <= 1e-12 * max(1.0, np.max(np.abs(Kfull)))
         assert pmax > 0  # both ranks own something

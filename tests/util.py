@@ -35,14 +35,15 @@ def aufbau_occs(Z, lmax):
     return occ
 
 
-def sadatom_density(S, T, Tl, Vnuc, Z, lmax, perturb=1e-3, spin=None, seed=SEED):
+def sadatom_density(S, T, Tl, Vnuc, Z, lmax, perturb=1e-3, spin=None, seed=SEED, occs=None):
     """Density cube P_l (nbf x nbf x (lmax+1), Fortran order) from core-Hamiltonian orbitals filled by
     Aufbau with sadatom's fractional shell filling (sadatom/solver.cpp:386-398), plus a seeded symmetric
     perturbation so no block is accidentally zero.  spin: None (total), 'a' or 'b' (b has the last
-    shell of the highest l emptied)."""
+    shell of the highest l emptied).  occs: electrons per l channel (default: Aufbau ground configuration)."""
     n = S.shape[0]
     P = np.zeros((n, n, lmax + 1), order="F")
-    occs = aufbau_occs(Z, lmax)
+    if occs is None:
+        occs = aufbau_occs(Z, lmax)
     for l in range(lmax + 1):
         H = T + l * (l + 1) * Tl + Vnuc
         E, C = scipy.linalg.eigh(H, S)
@@ -176,3 +177,20 @@ def diatomic_orbitals(b, occ_m=(0, 0, 0, 0, 0, 1, -1), seed=100, decay_l=0.35, d
     ev, U = np.linalg.eigh(G)
     C = C @ (U @ np.diag(ev ** -0.5) @ U.T)
     return C.reshape(nang * nrad, len(occ_m))
+
+
+def trial_configurations(Z, lmax):
+    """Occupations (electrons per l channel) a gensap-style configuration search visits for atom Z: the Aufbau ground
+    configuration and its neighbours with one electron moved between adjacent l channels
+    (/root/reference/src/sadatom/main.cpp:268-352 scans such occupation vectors).  Deterministic, ground state first."""
+    base = aufbau_occs(Z, lmax)
+    out = [tuple(base)]
+    for l in range(lmax):
+        for src, dst in ((l, l + 1), (l + 1, l)):
+            if base[src] > 0:
+                occ = list(base)
+                occ[src] -= 1
+                occ[dst] += 1
+                if tuple(occ) not in out:
+                    out.append(tuple(occ))
+    return out

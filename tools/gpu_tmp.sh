@@ -1,2 +1,3 @@
-HFB200_X_VERBOSE=1 timeout 600 python bench.py --steps 3 > gpurun_out/r02k_bench_cfg4.json 2> gpurun_out/r02k_cfg4.err; grep "host call" gpurun_out/r02k_cfg4.err | tail -n 4
-python -c "import json; d=json.load(open('gpurun_out/r02k_bench_cfg4.json')); print(d['value'], d['ms_per_step'], d['e2e'])"
+timeout 600 python -m pytest tests/test_sweep_gpu.py -m gpu -x -q -s 2>&1 | tail -n 6
+timeout 600 python bench.py --workload sweep_z1_86 --steps 10 > gpurun_out/r02l_sweep_n1.json 2> gpurun_out/r02l_sweep_n1.err || tail -n 15 gpurun_out/r02l_sweep_n1.err
+cat gpurun_out/r02l_sweep_n1.json | cut -c1-1800
