@@ -1,0 +1,202 @@
+"""Pins of the XC functionals that need no libxc (CPU; the device source helfem_b200/csrc/xc_*.cuh compiled for the host by the
+test-only shim, tests/xc_host_shim.cpp -- the GPU twin of the golden comparison is tests/test_xc_pins_gpu.py):
+
+  1. golden vectors from the independent 110-digit mpmath restatement (tests/xc_mpmath.py, fixture tests/golden/xc_mpmath.npz written
+     by tests/golden/make_xc_mpmath_goldens.py): 1024 seeded points x 7 functionals x (polarised, unpolarised), every libxc-style
+     output, gate 1e-11 relative (+ 1e-13 of the exchange-energy scale where x/c pieces cancel);
+  2. exact constraints the published functionals satisfy by construction: uniform-gas limits (PBE, r2SCAN -> Slater / PW92 at
+     sigma = 0, alpha = 1), spin scaling of exchange, vanishing r2SCAN correlation for fully polarised one-electron densities, the
+     hydrogen-atom exchange energy -5/16 Eh (the SCAN norm r2SCAN restores to 1e-3), PW92 literature values, the smoothness
+     conditions that fix the low-order coefficients of the two r2SCAN interpolation polynomials, closed forms of the constants.
+
+libxc is not installed in this image nor on the GPU box (no pylibxc, libxc.so or xc.h), and the reference does not pin its version
+(find_library(xc), CMakeLists.txt:83): this is as far as the XC numbers can be pinned here."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FIDS = (1, 12, 13, 101, 130, 497, 498)
+dp = ctypes.POINTER(ctypes.c_double)
+
+
+@pytest.fixture(scope="module")
+def shim():
+    so = os.path.join(HERE, "_xc_host.so")
+    src = os.path.join(HERE, "xc_host_shim.cpp")
+    deps = [src] + [os.path.join(HERE, "..", "helfem_b200", "csrc", f) for f in ("xc_point.cuh", "xc_functionals.cuh", "dual.cuh")]
+    if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-o", so, src])
+    return ctypes.CDLL(so)
+
+
+def host_eval(shim, f, nspin, rho, sigma, tau, thr=1e-12):
+    r_, s_, t_ = (np.ascontiguousarray(a, dtype=np.float64).ravel().copy() for a in (rho, sigma, tau))
+    n = r_.size // nspin
+    exc, vr, vs, vt = np.zeros(n), np.zeros_like(r_), np.zeros_like(s_), np.zeros_like(t_)
+    is_x = f in (1, 101, 497)
+    rc = shim.xc_host_eval(f if is_x else 0, 0 if is_x else f, nspin, n, ctypes.c_double(thr), r_.ctypes.data_as(dp), s_.ctypes.data_as(dp),
+                           t_.ctypes.data_as(dp), exc.ctypes.data_as(dp), vr.ctypes.data_as(dp), vs.ctypes.data_as(dp), vt.ctypes.data_as(dp))
+    assert rc == 0
+    return exc, vr, vs, vt
+
+
+def compare_with_goldens(evaluate):
+    """evaluate(fid, nspin, rho, sigma, tau) -> (exc, vrho, vsigma, vtau); returns the worst relative deviation seen."""
+    g = np.load(os.path.join(HERE, "golden", "xc_mpmath.npz"))
+    rho, sigma, tau = g["rho"], g["sigma"], g["tau"]
+    n = rho.shape[0]
+    worst = 0.0
+    for fid in FIDS:
+        for tag, nspin in (("p", 2), ("u", 1)):
+            if nspin == 2:
+                got = evaluate(fid, 2, rho, sigma, tau)
+                nt, st, tt = rho.sum(axis=1), sigma[:, 0] + 2 * sigma[:, 1] + sigma[:, 2], tau.sum(axis=1)
+            else:
+                got = evaluate(fid, 1, 2 * rho[:, 0], 4 * sigma[:, 0], 2 * tau[:, 0])
+                nt, st, tt = 2 * rho[:, 0], 4 * sigma[:, 0], 2 * tau[:, 0]
+            # scale of a well-conditioned answer at the point: the LDA exchange energy per particle; derivatives by dimension
+            e_scale = 0.7386 * nt ** (1.0 / 3.0)
+            scales = {"exc": e_scale, "vrho": e_scale, "vsigma": e_scale * nt / st, "vtau": e_scale * nt / tt}
+            for name, arr in zip(("exc", "vrho", "vsigma", "vtau"), got):
+                if name == "vsigma" and fid in (1, 12, 13):
+                    continue
+                if name == "vtau" and fid not in (497, 498):
+                    continue
+                ref = g["%s%d_%s" % (tag, fid, name)]
+                a = np.asarray(arr).reshape(ref.shape)
+                sc = scales[name].reshape((n,) + (1,) * (ref.ndim - 1))
+                err = np.abs(a - ref)
+                bad = err > 1e-11 * np.abs(ref) + 1e-13 * sc
+                assert not bad.any(), (fid, tag, name, int(bad.sum()), a[bad][:3], ref[bad][:3])
+                worst = max(worst, float(np.max(err / (np.abs(ref) + 1e-2 * sc))))
+    return worst
+
+
+def test_device_source_matches_mpmath_goldens(shim):
+    worst = compare_with_goldens(lambda f, nspin, r, s, t: host_eval(shim, f, nspin, r, s, t))
+    assert worst < 1e-11
+
+
+# ---------------------------------------------------------------- exact constraints ----
+def _gas(n):
+    """Uniform-gas inputs: sigma = 0, tau = tau_unif (alpha = 1), unpolarised."""
+    n = np.asarray(n, dtype=np.float64)
+    return n, np.zeros_like(n), 0.3 * (3 * np.pi**2) ** (2.0 / 3.0) * n ** (5.0 / 3.0)
+
+
+def test_uniform_gas_limits(shim):
+    n, sg, ta = _gas(10.0 ** np.linspace(-6, 3, 37))
+    ex_lda, vx_lda = host_eval(shim, 1, 1, n, sg, ta)[:2]
+    ec_mod, vc_mod = host_eval(shim, 13, 1, n, sg, ta)[:2]
+    assert np.allclose(ex_lda, -0.75 * (3.0 / np.pi) ** (1.0 / 3.0) * n ** (1.0 / 3.0), rtol=1e-14)  # Dirac
+    # energies coincide; the potentials only for PBE (for a meta-GGA d/dn at FIXED tau moves alpha = tau/tau_unif(n) away from 1)
+    for fx in (101, 497):
+        e, v = host_eval(shim, fx, 1, n, sg, ta)[:2]
+        # (r2SCAN: the paper's 12-digit polynomial has f_x(1) = -1e-12, not 0: 1.7e-13 of the energy)
+        assert np.max(np.abs(e / ex_lda - 1)) < 1e-12, fx
+        if fx == 101:
+            assert np.max(np.abs(v / vx_lda - 1)) < 1e-12
+    for fc in (130, 498):  # both reduce to PW92 with the "modified" parameters
+        e, v = host_eval(shim, fc, 1, n, sg, ta)[:2]
+        assert np.max(np.abs(e / ec_mod - 1)) < 1e-11, fc
+        if fc == 130:
+            assert np.max(np.abs(v / vc_mod - 1)) < 1e-11
+
+
+def test_exchange_spin_scaling(shim):
+    """E_x[rho_a, rho_b] = (E_x[2 rho_a] + E_x[2 rho_b]) / 2 for every exchange functional."""
+    rng = np.random.RandomState(7)
+    n = 64
+    ra, rb = 10.0 ** rng.uniform(-4, 2, n), 10.0 ** rng.uniform(-4, 2, n)
+    kfa, kfb = (6 * np.pi**2 * ra) ** (1 / 3), (6 * np.pi**2 * rb) ** (1 / 3)
+    ga, gb = rng.uniform(0.01, 3, n) * 2 * kfa * ra, rng.uniform(0.01, 3, n) * 2 * kfb * rb
+    ta = ga**2 / (8 * ra) + rng.uniform(0, 3, n) * 0.3 * (6 * np.pi**2) ** (2 / 3) * ra ** (5 / 3)
+    tb = gb**2 / (8 * rb) + rng.uniform(0, 3, n) * 0.3 * (6 * np.pi**2) ** (2 / 3) * rb ** (5 / 3)
+    for fx in (1, 101, 497):
+        rho = np.stack([ra, rb], axis=1)
+        sig = np.stack([ga**2, 0.3 * ga * gb, gb**2], axis=1)
+        tau = np.stack([ta, tb], axis=1)
+        e_pol = host_eval(shim, fx, 2, rho, sig, tau)[0] * (ra + rb)
+        e_a = host_eval(shim, fx, 1, 2 * ra, 4 * ga**2, 2 * ta)[0] * 2 * ra
+        e_b = host_eval(shim, fx, 1, 2 * rb, 4 * gb**2, 2 * tb)[0] * 2 * rb
+        assert np.max(np.abs(e_pol - 0.5 * (e_a + e_b)) / np.abs(e_pol)) < 1e-13, fx
+
+
+def test_r2scan_correlation_vanishes_for_one_electron_densities(shim):
+    """alpha = 0 (tau = tau_W) and zeta = 1: eps_c = eps_c^0 G_c(zeta) with G_c(1) = 0.  The minority density sits at the
+    density threshold (libxc clamps it there), so the result is O(rho_b / rho_a) instead of an exact zero."""
+    n = 32
+    ra = 10.0 ** np.linspace(-3, 2, n)
+    rb = np.full(n, 1e-13)
+    g = np.linspace(0.05, 2.0, n) * 2 * (6 * np.pi**2 * ra) ** (1 / 3) * ra
+    rho = np.stack([ra, rb], axis=1)
+    sig = np.stack([g**2, np.zeros(n), np.zeros(n)], axis=1)
+    tau = np.stack([g**2 / (8 * ra), np.zeros(n)], axis=1)
+    ec = host_eval(shim, 498, 2, rho, sig, tau)[0]
+    ec_pw = host_eval(shim, 13, 2, rho, sig, tau)[0]
+    assert np.max(np.abs(ec)) < 1e-9 and np.max(np.abs(ec / ec_pw)) < 1e-7
+    # the same points with alpha = 1 instead are NOT small: the test above is not vacuous
+    tau1 = tau.copy()
+    tau1[:, 0] += 0.3 * (6 * np.pi**2) ** (2 / 3) * ra ** (5 / 3)
+    assert np.min(np.abs(host_eval(shim, 498, 2, rho, sig, tau1)[0] / ec_pw)) > 1e-2
+
+
+def test_hydrogen_atom_exchange(shim):
+    """E_x[H 1s, fully polarised]: exact -5/16 Eh.  LSDA gives -0.2680, PBE -0.3059; SCAN reproduces the exact value by
+    construction (k1 = 0.065 is fitted to it) and r2SCAN keeps it to better than 1e-3 Eh."""
+    r = np.linspace(1e-4, 40.0, 400001)
+    w = np.full_like(r, r[1] - r[0])
+    w[0] = w[-1] = 0.5 * (r[1] - r[0])
+    rho = np.exp(-2 * r) / np.pi
+    grad2 = 4 * rho**2
+    tau = grad2 / (8 * rho)  # one orbital: tau = tau_W
+    rr = np.stack([rho, np.full_like(rho, 1e-14)], axis=1)
+    ss = np.stack([grad2, np.zeros_like(rho), np.zeros_like(rho)], axis=1)
+    tt = np.stack([tau, np.zeros_like(rho)], axis=1)
+    vol = 4 * np.pi * r**2 * w
+    E = {f: float(np.sum(host_eval(shim, f, 2, rr, ss, tt)[0] * rho * vol)) for f in (1, 101, 497)}
+    assert abs(E[1] + 0.2680) < 2e-4 and abs(E[101] + 0.3059) < 3e-4
+    assert abs(E[497] + 0.3125) < 1e-3, E
+
+
+def test_pw92_literature_values_and_mod_variant(shim):
+    """eps_c of the unpolarised gas (Ha): the Ceperley-Alder values PW92 was fitted to, rs = 1, 2, 5, 10 (to 2e-4);
+    lda_c_pw and lda_c_pw_mod differ only in the digits of their parameters."""
+    rs = np.array([1.0, 2.0, 5.0, 10.0])
+    n = 3.0 / (4 * np.pi * rs**3)
+    e = host_eval(shim, 12, 1, n, np.zeros(4), np.zeros(4))[0]
+    assert np.max(np.abs(e - np.array([-0.0598, -0.0448, -0.0282, -0.0186]))) < 2e-4, e
+    em = host_eval(shim, 13, 1, n, np.zeros(4), np.zeros(4))[0]
+    d = np.abs(em / e - 1)
+    assert np.all(d > 0) and np.max(d) < 1e-5
+
+
+def test_constants_closed_forms_and_polynomial_smoothness():
+    """The typed constants of the device source against their definitions, and the smoothness conditions of the r2SCAN switching
+    functions: f(0) = 1, f'(0) = -c1, f''(0) = c1^2 - 2 c1 (continuity with exp(-c1 a/(1-a)) at alpha = 0), f(1) = 0, continuity
+    with -d exp(c2/(1-a)) at alpha = 2.5 (to the digits the paper prints)."""
+    import re
+    src = open(os.path.join(HERE, "..", "helfem_b200", "csrc", "xc_functionals.cuh")).read()
+    val = lambda name: float(re.search(r"#define %s\s+([0-9.eE+-]+)" % name, src).group(1))
+    assert abs(val("HFB_GAMMA_C") - (1 - np.log(2)) / np.pi**2) < 1e-17
+    assert abs(val("HFB_MU_PBE") - val("HFB_BETA_PBE") * np.pi**2 / 3) < 1e-15
+    assert abs(val("HFB_CBRT_3PI2") - (3 * np.pi**2) ** (1 / 3)) < 1e-15
+    assert abs(val("HFB_RS_FACTOR") - (3 / (4 * np.pi)) ** (1 / 3)) < 1e-15
+    assert abs(val("HFB_TWO43M2") - (2 ** (4 / 3) - 2)) < 1e-15
+    fz20 = float(re.search(r"p\.fz20 = ([0-9.]+); \}\s*\n\s*else", src).group(1))
+    assert abs(fz20 - 8 / (9 * (2 ** (4 / 3) - 2))) < 1e-15
+    chi = float(re.search(r"chi_inf = ([0-9.]+)", src).group(1))
+    cx0 = 3 / (4 * np.pi) * (9 * np.pi / 4) ** (1 / 3)
+    assert abs(chi - (3 * np.pi**2 / 16) ** (2 / 3) * 0.066725 * 0.1 / 0.1778 / (0.9 - cx0)) < 1e-12
+    for arr, c1, c2, d in (("cx", 0.667, 0.8, 1.24), ("cc", 0.64, 1.5, 0.7)):
+        body = re.search(r"const double %s\[8\] = \{([^}]*)\}" % arr, src).group(1)
+        c = np.array([float(x) for x in body.replace("\n", " ").split(",")])
+        p = np.polynomial.Polynomial(c)
+        assert c[0] == 1.0 and c[1] == -c1 and abs(2 * c[2] - (c1 * c1 - 2 * c1)) < 1e-12
+        assert abs(p(1.0)) < 1e-9
+        assert abs(p(2.5) + d * np.exp(c2 / (1 - 2.5))) < 1e-8
+        assert abs(p.deriv()(2.5) + d * np.exp(c2 / (1 - 2.5)) * c2 / (1 - 2.5) ** 2) < 1e-7
