@@ -1,7 +1,9 @@
-# 2-GPU checks: family-sharded diatomic J/K over NCCL vs the oracle, and the weak-scaling bench at N=1,2.
-set -x
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 tools/shard_nccl_check.py --lmax 4 --mmax 2 --nelem 4 --nnodes 8 > gpurun_out/r01f_shard_n2.json 2> gpurun_out/r01f_shard_n2.err; tail -c 400 gpurun_out/r01f_shard_n2.err
-python tools/shard_nccl_check.py --lmax 4 --mmax 2 --nelem 4 --nnodes 8 --no-oracle > gpurun_out/r01f_shard_n1.json 2> gpurun_out/r01f_shard_n1.err
-python bench.py --gpus 1 > gpurun_out/r01f_bench_n1.json 2> gpurun_out/r01f_bench_n1.err; tail -c 300 gpurun_out/r01f_bench_n1.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus 2 > gpurun_out/r01f_bench_n2.json 2> gpurun_out/r01f_bench_n2.err; tail -c 300 gpurun_out/r01f_bench_n2.err
-cat gpurun_out/r01f_shard_n2.json gpurun_out/r01f_shard_n1.json gpurun_out/r01f_bench_n1.json gpurun_out/r01f_bench_n2.json
+# N-GPU checks ($1 = N, $2 = tag): XC golden test on the device, in-library NCCL parity, default bench sharded, the Z sweep over N ranks
+N=${1:-2}; TAG=${2:-r02}
+export OMP_NUM_THREADS=6
+timeout 300 python -m pytest tests/test_xc_pins_gpu.py -m gpu -q -s 2>&1 | tail -n 3
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 tools/shard_nccl_check.py > gpurun_out/${TAG}_shard_check_n$N.json 2> gpurun_out/${TAG}_shard_check_n$N.err; tail -n 3 gpurun_out/${TAG}_shard_check_n$N.err; cat gpurun_out/${TAG}_shard_check_n$N.json
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29522 bench.py --gpus $N --steps 10 > gpurun_out/${TAG}_cfg4_n$N.json 2> gpurun_out/${TAG}_cfg4_n$N.err; tail -n 3 gpurun_out/${TAG}_cfg4_n$N.err
+python -c "import json; d=json.load(open('gpurun_out/${TAG}_cfg4_n$N.json')); print('cfg4 N=$N', d['value'], d['ms_per_step'], d['scaling'], 'e2e', d['e2e']['value']); [print(' ', e['stage'], round(e['ms'],3)) for e in d['roofline']['stages']]"
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29523 bench.py --gpus $N --workload sweep_z1_86 --steps 10 > gpurun_out/${TAG}_sweep_n$N.json 2> gpurun_out/${TAG}_sweep_n$N.err; tail -n 3 gpurun_out/${TAG}_sweep_n$N.err
+python -c "import json; d=json.load(open('gpurun_out/${TAG}_sweep_n$N.json')); print('sweep N=$N', d['value'], d['ms_per_step'], d['config']['builds_per_rank'], 'e2e', d['e2e']['value'], d['checks'])"
