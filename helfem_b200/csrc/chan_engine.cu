@@ -348,6 +348,19 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
   std::vector<unsigned long long> wbits((size_t)nchan * nang * nw, 0);
   std::vector<int> wcount((size_t)nchan * nang, 0);
   std::vector<std::vector<int2>> fam_items(nr);
+  // Symmetric P: of every pair of output blocks (j,k), (k,j) only ONE is contracted (x4 writes the other as its transpose).  Which
+  // one is chosen CIRCULARLY inside an m class -- (j,k) is kept when k follows j by at most half the class size -- so that every row
+  // j keeps about half of its partners (a triangle j <= k would leave rows with 1 .. n partners and half-empty tiles of 8).
+  std::vector<int> mpos(nang, 0), mcnt(nang, 0);
+  for (int a = 0; a < nang; a++)
+    for (int b = 0; b < nang; b++)
+      if (ang_m[b] == ang_m[a]) { mcnt[a]++; if (b < a) mpos[a]++; }
+  auto keep = [&](int j, int k) {
+    if (j == k) return true;
+    if (ang_m[j] != ang_m[k]) return j < k;
+    const int n = mcnt[j], d = (mpos[k] - mpos[j] + n) % n;
+    return 2 * d < n || (2 * d == n && mpos[j] < mpos[k]);
+  };
 #pragma omp parallel
   {
     std::vector<uint64_t> rowset((size_t)nang * nw);
@@ -378,7 +391,7 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
         for (int j : js) {
           const unsigned long long* ls = &wbits[((size_t)c * nang + j) * nw];
           for (int k : js) {
-            if (sym && k < j) continue;
+            if (sym && !keep(j, k)) continue;
             if (hit[(size_t)j * nang + k]) continue;
             uint64_t any = 0;
             for (int w = 0; w < nw; w++) any |= ls[w] & rowset[(size_t)k * nw + w];
@@ -394,12 +407,12 @@ int ChanEngine::build_items(const unsigned char* nz, bool sym) {
         std::stable_sort(fam_items[r].begin() + b0, fam_items[r].end(),
                          [&](const int2& a, const int2& b) { return ang_group[a.y] < ang_group[b.y]; });
       }
-      if (sym) {  // rows (c, j) that no item j <= k uses produce nothing that is read: drop their W blocks
+      if (sym) {  // rows (c, j) that no kept item (j, k) uses produce nothing that is read: drop their W blocks
         for (int c = fam_c0_host[r]; c < fam_c0_host[r + 1]; c++)
           for (int j = 0; j < nang; j++) {
             if (!wcount[(size_t)c * nang + j]) continue;
             bool used = false;
-            for (int k = j; k < nang && !used; k++) used = hit[(size_t)j * nang + k] != 0;
+            for (int k = 0; k < nang && !used; k++) used = hit[(size_t)j * nang + k] != 0;
             if (!used) {
               wcount[(size_t)c * nang + j] = 0;
               for (int w = 0; w < nw; w++) wbits[((size_t)c * nang + j) * nw + w] = 0;
