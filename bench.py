@@ -190,10 +190,10 @@ def oracle_from_basis(b):
     return o
 
 
-def cpu_builds(o, w, dens, nbuilds):
-    """nbuilds Fock builds on the host cores; returns seconds."""
-    t0 = time.perf_counter()
-    for i in range(nbuilds):
+def cpu_builds(o, w, dens, nbuilds, nthreads=1):
+    """nbuilds Fock builds on the host cores; returns seconds.  nthreads > 1: ONE BUILD PER THREAD (the reference runs the sweep /
+    configuration search as independent processes, one per core), each build single-threaded inside (ctypes releases the GIL)."""
+    def one(i):
         s = 1.0 + 0.01 * i
         if w["nspin"] == 1:
             P = dens[0] * s
@@ -203,42 +203,58 @@ def cpu_builds(o, w, dens, nbuilds):
             Pa, Pb = dens[0] * s, dens[1] * s
             o.coulomb(np.asfortranarray((Pa + Pb).sum(axis=2)))
             o.eval_fxc(w["x"], w["c"], Pa, Pb)
+    t0 = time.perf_counter()
+    if nthreads <= 1:
+        for i in range(nbuilds):
+            one(i)
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=nthreads) as ex:
+            list(ex.map(one, range(nbuilds)))
     return time.perf_counter() - t0
+
+
+def sadatom_cpu_setup(w):
+    """Oracle + densities of a sadatom workload from the numpy setup (oracle/fem_oracle.py): the CPU arm never maps the product library."""
+    import oracle
+    from oracle import fem_oracle as fo
+    from util import sadatom_density
+    rs = fo.RadialSetup(w["primbas"], w["nnodes"], fo.get_grid(40.0, w["nelem"]), taylor_order=w["taylor"])
+    o = oracle.sadatom_from_setup(rs, w["lmax"], nL=1, exchange=False)
+    S, T, Tl, V = rs.overlap(), rs.kinetic(), rs.kinetic_l(), rs.nuclear(w["Z"])
+    if w["nspin"] == 1:
+        dens = [sadatom_density(S, T, Tl, V, w["Z"], w["lmax"]) / (4 * np.pi)]
+    else:
+        dens = [sadatom_density(S, T, Tl, V, w["Z"], w["lmax"], spin=sp) / (4 * np.pi) for sp in ("a", "b")]
+    return o, dens
 
 
 def run_reference(args, w, rank):
     if rank != 0:
         return
     import oracle
-    b = make_basis_host_only(w)
-    o = oracle_from_basis(b)
-    dens = make_densities(b, w)
-    oracle.lib().oracle_set_num_threads(host_threads())  # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every core
-    nthreads = oracle.lib().oracle_num_threads()
+    o, dens = sadatom_cpu_setup(w)
+    nthreads = host_threads()
+    oracle.lib().oracle_set_num_threads(1)  # one build per thread, every build single-threaded inside
     one = cpu_builds(o, w, dens, 1)
-    per_step = max(1, min(args.batch, int(2.0 / max(one, 1e-6))))  # ~2 s of CPU work per step
+    per_step = max(nthreads, min(args.batch, int(2.0 * nthreads / max(one, 1e-6))))  # ~2 s of CPU work per step
     for _ in range(args.warmup):
-        cpu_builds(o, w, dens, max(1, per_step // 4))
+        cpu_builds(o, w, dens, max(nthreads, per_step // 4), nthreads)
     t = 0.0
     for _ in range(args.steps):
-        t += cpu_builds(o, w, dens, per_step)
+        t += cpu_builds(o, w, dens, per_step, nthreads)
     value = per_step * args.steps / t
     line = {"impl": "reference", "metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "desc": w["desc"], "builds_per_step": per_step,
-                       "note": "CPU restatement of the reference loops (oracle/hotpath_oracle.cpp, -O3 -fopenmp); the "
-                               "reference itself cannot be compiled here (no Armadillo/GSL/libxc/HDF5/gfortran)"},
+                       "note": "CPU restatement of the reference loops (oracle/hotpath_oracle.cpp, -O3), tables from oracle/fem_oracle.py, one build "
+                               "per host thread; the reference itself cannot be compiled here (no Armadillo/GSL/libxc/HDF5/gfortran)"},
             "cpu_baseline": {"value": value, "unit": "builds/s", "cores": nthreads, "kind": "port",
-                             "sample": "%d builds per step x %d steps" % (per_step, args.steps)},
+                             "sample": "%d builds per step x %d steps, one build per thread" % (per_step, args.steps)},
             "e2e": {"value": value, "unit": "builds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
-
-
-def make_basis_host_only(w):
-    """Tables + stored integrals from the host library only (no device context is created)."""
-    return make_basis(w)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -411,13 +427,14 @@ def run_gpu(args, w, rank, world, local_rank):
     cpu = None
     if world == 1:  # reported at N = 1 only
         import oracle
-        oracle.lib().oracle_set_num_threads(host_threads())
+        nthr = host_threads()
+        oracle.lib().oracle_set_num_threads(1)  # one build per thread, every build single-threaded inside
         o = oracle_from_basis(b)
         one = cpu_builds(o, w, dens, 1)
-        nsample = max(2, min(200, int(10.0 / max(one, 1e-6))))
-        tc = cpu_builds(o, w, dens, nsample)
-        cpu = {"value": nsample / tc, "unit": "builds/s", "cores": oracle.lib().oracle_num_threads(), "kind": "port",
-               "sample": "%d Fock builds (coulomb + eval_Fxc) of the same workload" % nsample}
+        nsample = max(nthr, min(200 * nthr, int(10.0 * nthr / max(one, 1e-6))))
+        tc = cpu_builds(o, w, dens, nsample, nthr)
+        cpu = {"value": nsample / tc, "unit": "builds/s", "cores": nthr, "kind": "port",
+               "sample": "%d Fock builds (coulomb + eval_Fxc) of the same workload, one build per thread" % nsample}
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",

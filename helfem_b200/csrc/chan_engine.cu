@@ -649,7 +649,8 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
   ChanParams q = prm;
   q.nb = 1; q.P = dP.p; q.pc = dPc.p; q.traces = dTr.p; q.jc = dJc.p; q.J = dJ.p;
   q.pnz = dPnz; q.cnz = dCnz; q.onz = dOnz;  // dPnz was filled by the caller's pack pass
-  chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
+  if (4 * prm.KS <= 512) chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
+  else chan_pre_generic_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   int maxcol = 1;
   for (int r = 0; r < prm.nr; r++) maxcol = std::max(maxcol, fam_c0_host[r + 1] - fam_c0_host[r]);
@@ -670,7 +671,7 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
   chan_flag_kernel<<<nchan, 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   HFB_CUDA_OK(cudaMemsetAsync(dOnz, 0, (size_t)npair, st));
-  chan_post_kernel<<<dim3(nel * npair, 1, 1), 128, 0, st>>>(q);
+  chan_post_kernel<<<dim3(npair, 1, 1), 256, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
   return 0;
 }

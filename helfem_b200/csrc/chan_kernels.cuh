@@ -53,8 +53,117 @@ struct ChanParams {
   unsigned char* onz;        // [npair] the J band of the pair has a non-zero entry
 };
 
-// grid (nel, nchan, nb), 128 threads
+// grid (nel, nchan, nb), 128 threads.  The couplings of the channel whose pair band is non-zero (pnz) are first compacted, IN ORDER,
+// into shared memory segment by segment (a linear molecule populates 2 % of the pairs), then every thread accumulates its entries
+// over the compacted list only: the summation order is that of the full list with the zero terms left out.
+constexpr int CHAN_PRE_SEG = 512;
 static __global__ void __launch_bounds__(128) chan_pre_kernel(ChanParams prm) {
+  __shared__ double red[8];
+  __shared__ int s_pair[CHAN_PRE_SEG];
+  __shared__ double s_cf[CHAN_PRE_SEG][2];
+  __shared__ int s_wcnt[4], s_n;
+  const int el = blockIdx.x, c = blockIdx.y, b = blockIdx.z, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int np = prm.np, np2 = prm.np2, KP = 4 * prm.KS, MP = 8 * prm.MT, r = prm.chan_r[c];
+  const int e0 = prm.pre_ptr[c], e1 = prm.pre_ptr[c + 1];
+  const double* gP = prm.P + ((size_t)b * prm.npair * prm.nel + el) * np2;
+  const size_t pstride = (size_t)prm.nel * np2;
+  const double* sv = prm.svec + ((size_t)r * prm.nel + el) * MP;
+  const double* bv = prm.bvec + ((size_t)r * prm.nel + el) * MP;
+  double* out = prm.pc + (((size_t)c * prm.nb + b) * prm.nel + el) * KP;
+  // this thread's entries m = tid, tid + 128, ... (KP <= 4 * 128 is checked by the engine: at most 4 per thread)
+  double v[4] = {0.0, 0.0, 0.0, 0.0};
+  int ia[4], iat[4], hh[4];
+  bool diag[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int m = tid + 128 * q;
+    ia[q] = -1; iat[q] = 0; hh[q] = 0; diag[q] = true;
+    if (m < prm.stack * prm.ntri) {
+      hh[q] = m >= prm.ntri ? 1 : 0;
+      const int2 ij = prm.tri[m - hh[q] * prm.ntri];
+      ia[q] = ij.x + ij.y * np;
+      iat[q] = ij.y + ij.x * np;
+      diag[q] = ij.x == ij.y;
+    }
+  }
+  for (int base = e0; base < e1;) {
+    // ---- ordered compaction of up to CHAN_PRE_SEG active couplings starting at `base` ----
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    int consumed = base;
+    while (consumed < e1) {
+      const int e = consumed + tid;
+      bool act = false;
+      int pr = 0;
+      if (e < e1) {
+        pr = prm.pre_pair[e];
+        act = (prm.pnz == nullptr || prm.pnz[pr]) && (prm.pre_coef[2 * e] != 0.0 || prm.pre_coef[2 * e + 1] != 0.0);
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, act);
+      if (lane == 0) s_wcnt[warp] = __popc(bal);
+      __syncthreads();
+      const int n0 = s_n;
+      const int tot = s_wcnt[0] + s_wcnt[1] + s_wcnt[2] + s_wcnt[3];
+      if (n0 + tot > CHAN_PRE_SEG) break;  // block-uniform: this chunk goes into the next segment
+      int off = n0;
+      for (int w = 0; w < warp; w++) off += s_wcnt[w];
+      if (act) {
+        const int pos = off + __popc(bal & ((1u << lane) - 1u));
+        s_pair[pos] = pr;
+        s_cf[pos][0] = prm.pre_coef[2 * e];
+        s_cf[pos][1] = prm.pre_coef[2 * e + 1];
+      }
+      __syncthreads();
+      if (tid == 0) s_n = n0 + tot;
+      consumed += 128;
+      __syncthreads();
+    }
+    const int nact = s_n;
+    // ---- accumulate over the compacted segment ----
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      if (ia[q] < 0) continue;
+      double acc = v[q];
+      for (int x = 0; x < nact; x++) {
+        const double cf = s_cf[x][hh[q]];
+        if (cf == 0.0) continue;
+        const double* src = gP + (size_t)s_pair[x] * pstride;
+        double pv = src[ia[q]];
+        if (!diag[q]) pv += src[iat[q]];
+        acc = fma(cf, pv, acc);
+      }
+      v[q] = acc;
+    }
+    __syncthreads();
+    base = consumed;
+  }
+  double ts = 0.0, tb = 0.0;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int m = tid + 128 * q;
+    if (m >= KP) continue;
+    if (ia[q] >= 0) {
+      ts = fma(sv[m], v[q], ts);
+      tb = fma(bv[m], v[q], tb);
+    }
+    out[m] = v[q];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ts += __shfl_xor_sync(0xffffffffu, ts, o);
+    tb += __shfl_xor_sync(0xffffffffu, tb, o);
+  }
+  if ((tid & 31) == 0) { red[tid >> 5] = ts; red[4 + (tid >> 5)] = tb; }
+  __syncthreads();
+  if (tid == 0) {
+    double* tr = prm.traces + (((size_t)c * prm.nb + b) * prm.nel + el) * 2;
+    tr[0] = (red[0] + red[1]) + (red[2] + red[3]);
+    tr[1] = (red[4] + red[5]) + (red[6] + red[7]);
+  }
+}
+
+// grid (nel, nchan, nb), 128 threads.  Any vector length (used when the stacked triangle exceeds 512 entries: np > 21).
+static __global__ void __launch_bounds__(128) chan_pre_generic_kernel(ChanParams prm) {
   __shared__ double red[8];
   const int el = blockIdx.x, c = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
   const int np = prm.np, np2 = prm.np2, KP = 4 * prm.KS, MP = 8 * prm.MT, r = prm.chan_r[c];
@@ -215,31 +324,92 @@ static __global__ void __launch_bounds__(128) chan_flag_kernel(ChanParams prm) {
   if (threadIdx.x == 0) prm.cnz[c] = any ? 1 : 0;
 }
 
-// grid (nel * npair, 1, nb), 128 threads
-static __global__ void __launch_bounds__(128) chan_post_kernel(ChanParams prm) {
-  const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, b = blockIdx.z;
-  const int np = prm.np, np2 = prm.np2, MP = 8 * prm.MT;
+// grid (npair, 1, nb), 256 threads: all elements of one angular pair.  The couplings to channels with a non-zero result (cnz) are
+// compacted in order into shared memory; a pair without any leaves its band untouched and its onz flag clear (the unpack then
+// writes zeros without reading the band).
+constexpr int CHAN_POST_SEG = 256;
+static __global__ void __launch_bounds__(256) chan_post_kernel(ChanParams prm) {
+  __shared__ int s_chan[CHAN_POST_SEG];
+  __shared__ double s_cf[CHAN_POST_SEG][2];
+  __shared__ int s_wcnt[8], s_n;
+  const int pr = blockIdx.x, b = blockIdx.z, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int np = prm.np, np2 = prm.np2, MP = 8 * prm.MT, nel = prm.nel;
   const int e0 = prm.post_ptr[pr], e1 = prm.post_ptr[pr + 1];
-  double* out = prm.J + (((size_t)b * prm.npair + pr) * prm.nel + el) * np2;
+  int any_act = 0;
+  for (int e = e0 + tid; e < e1; e += 256) any_act |= (prm.cnz == nullptr || prm.cnz[prm.post_chan[e]]);
+  if (!__syncthreads_or(any_act)) return;
+  double* out = prm.J + ((size_t)b * prm.npair + pr) * nel * np2;
+  const int total = nel * np2;
   int any = 0;
-  for (int k = threadIdx.x; k < np2; k += blockDim.x) {
-    const int i = k % np, j = k / np;
-    const int lo = min(i, j), hi = max(i, j);
-    const int m = lo + hi * (hi + 1) / 2;
-    double v = 0.0;
-    for (int e = e0; e < e1; e++) {
-      const int c = prm.post_chan[e];
-      if (prm.cnz && !prm.cnz[c]) continue;
-      const double* src = prm.jc + (((size_t)c * prm.nb + b) * prm.nel + el) * MP;
-      v = fma(prm.post_coef[2 * e], src[m], v);
-      if (prm.stack == 2) v = fma(prm.post_coef[2 * e + 1], src[prm.ntri + m], v);
+  for (int k0 = 0; k0 < total; k0 += 2048) {  // sweeps of 2048 band entries (8 per thread); one sweep unless nel np^2 > 2048
+  // this thread's entries k = k0 + tid, + 256, ... of the pair's band [element][np2]
+  double v[8];
+  int mm[8], ee[8];
+#pragma unroll
+  for (int q = 0; q < 8; q++) {
+    const int k = k0 + tid + 256 * q;
+    v[q] = 0.0; mm[q] = -1; ee[q] = 0;
+    if (k < total) {
+      const int el = k / np2, kk = k - el * np2, i = kk % np, j = kk / np;
+      const int lo = min(i, j), hi = max(i, j);
+      mm[q] = lo + hi * (hi + 1) / 2;
+      ee[q] = el;
     }
-    out[k] = v;
-    any |= (v != 0.0);
   }
+  for (int base = e0; base < e1;) {
+    __syncthreads();
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    int consumed = base;
+    while (consumed < e1) {
+      const int e = consumed + tid;
+      bool act = false;
+      int c = 0;
+      if (e < e1) {
+        c = prm.post_chan[e];
+        act = prm.cnz == nullptr || prm.cnz[c];
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, act);
+      if (lane == 0) s_wcnt[warp] = __popc(bal);
+      __syncthreads();
+      const int n0 = s_n;
+      int tot = 0, off = n0;
+      for (int w = 0; w < 8; w++) { if (w < warp) off += s_wcnt[w]; tot += s_wcnt[w]; }
+      if (n0 + tot > CHAN_POST_SEG) break;  // block-uniform
+      if (act) {
+        const int pos = off + __popc(bal & ((1u << lane) - 1u));
+        s_chan[pos] = c;
+        s_cf[pos][0] = prm.post_coef[2 * e];
+        s_cf[pos][1] = prm.post_coef[2 * e + 1];
+      }
+      __syncthreads();
+      if (tid == 0) s_n = n0 + tot;
+      consumed += 256;
+      __syncthreads();
+    }
+    const int nact = s_n;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      if (mm[q] < 0) continue;
+      double acc = v[q];
+      for (int x = 0; x < nact; x++) {
+        const double* src = prm.jc + (((size_t)s_chan[x] * prm.nb + b) * nel + ee[q]) * MP;
+        acc = fma(s_cf[x][0], src[mm[q]], acc);
+        if (prm.stack == 2) acc = fma(s_cf[x][1], src[prm.ntri + mm[q]], acc);
+      }
+      v[q] = acc;
+    }
+    base = consumed;
+  }
+#pragma unroll
+  for (int q = 0; q < 8; q++) {
+    const int k = k0 + tid + 256 * q;
+    if (k < total) { out[k] = v[q]; any |= (v[q] != 0.0); }
+  }
+  }  // sweeps
   if (prm.onz) {
     any = __syncthreads_or(any);
-    if (threadIdx.x == 0 && any) prm.onz[pr] = 1;  // preset to zero; every writer stores the same value
+    if (tid == 0 && any) prm.onz[pr] = 1;
   }
 }
 
