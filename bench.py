@@ -53,7 +53,10 @@ WORKLOADS = {
                        desc="diatomic N2, lmax 4, mmax 1, 3 elements (small case the CPU oracle finishes in seconds)"),
     # product-grid DFT of the diatomic program (configs[3]b in SURVEY 8: the 2-D prolate grid), first correct version
     "n2_pbe_grid_l6m2": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=6, mmax=2, nelem=3, nnodes=10, primbas=4, x=101, c=130,
-                             desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 6, mmax 2, 3 elements, ldft 4 lmax+12, mdft 4 mmax+5"),
+                             desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 6, mmax 2, 3 elements, ldft 4 lmax+12, mdft 4 (mmax+1)+5"),
+    "n2_pbe_cfg4b": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=24, mmax=6, nelem=5, nnodes=15, primbas=4, x=101, c=130,
+                         desc="diatomic --Z1 N --Z2 N --Rbond 2.068 --lmax 24 --mmax 6 --nelem 5 --nnodes 15 --primbas 4 --method gga_x_pbe-gga_c_pbe: "
+                              "eval_Fxc on the product grid, ldft 108 x mdft 33 = 3 564 angular x 375 mu points (configs[3]b of SURVEY 8)"),
     "n2_pbe_grid_l2m1": dict(kind="grid2d", Z1=7, Z2=7, Rbond=2.068, lmax=2, mmax=1, nelem=2, nnodes=5, primbas=4, x=101, c=130,
                              desc="diatomic N2 PBE eval_Fxc on the product grid, lmax 2, mmax 1 (oracle-sized)"),
     # the Z sweep (configs[4]): one shared Kr-type basis, every atom's trial configurations, dynamic queue over the ranks
@@ -976,7 +979,7 @@ def run_grid2d(args, w, rank, world, local_rank):
     from grid2d_cases import diatomic_density
     b = hb.DiatomicBasis(w["Z1"], w["Z2"], w["Rbond"], nelem=w["nelem"], nnodes=w["nnodes"], primbas=w["primbas"],
                          lmax=w["lmax"], mmax=w["mmax"], device=local_rank)
-    lang, mang = 4 * w["lmax"] + 12, 4 * w["mmax"] + 5  # diatomic/main.cpp:417,425
+    lang, mang = 4 * w["lmax"] + 12, 4 * (w["mmax"] + 1) + 5  # diatomic/main.cpp:417,425 (lmmax.n_elem = mmax + 1)
     g = hb.DiatomicDFTGrid(b, lang, mang)
     n = b.nbf
     C = chan_orbitals(b, "diatomic", rank)
