@@ -164,22 +164,35 @@ class _ProductGrid:
         except Exception:
             pass
 
-    def eval_Fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True):
-        """returns (H, Exc, Nel, Ekin) or (Ha, Hb, Exc, Nel, Ekin)"""
+    def eval_Fxc(self, x_func, c_func, P, Pb=None, thr=1e-12, beta=True, out=None):
+        """returns (H, Exc, Nel, Ekin) or (Ha, Hb, Exc, Nel, Ekin); out: optional caller-owned Fortran-ordered float64 H (restricted
+        call), fully overwritten -- no allocation per call"""
         P = np.asfortranarray(P, dtype=np.float64)
         if P.ndim != 2 or P.shape[0] != P.shape[1] or (Pb is not None and np.shape(Pb) != P.shape):
             raise ValueError("density matrices must be square and of equal shape")
-        H = np.zeros_like(P, order="F")
+        if out is not None and (Pb is not None or out.shape != P.shape or not out.flags.f_contiguous or out.dtype != np.float64):
+            raise ValueError("out must be a Fortran-ordered float64 matrix of the shape of P (restricted call)")
+        H = out if out is not None else np.empty_like(P, order="F")
         sc = np.zeros(3)
         fn = getattr(lib(), self._prefix + "_grid_eval")
         if Pb is None:
             check_host(fn(self._h, self._basis._h, int(P.shape[0]), int(x_func), int(c_func), 1, _p(P), None, ctypes.c_double(thr), _p(H), None, 0, _p(sc)))
             return H, sc[0], sc[1], sc[2]
         Pb = np.asfortranarray(Pb, dtype=np.float64)
-        Hb = np.zeros_like(P, order="F")
+        Hb = np.zeros_like(P, order="F")  # left at zero when beta is false
         check_host(fn(self._h, self._basis._h, int(P.shape[0]), int(x_func), int(c_func), 2, _p(P), _p(Pb), ctypes.c_double(thr), _p(H), _p(Hb),
                       int(bool(beta)), _p(sc)))
         return H, Hb, sc[0], sc[1], sc[2]
+
+
+    def last_call(self):
+        """accounting of the last eval_Fxc: device milliseconds of its kernels (CUDA events), packed bytes up / down, kernel launches"""
+        out = np.zeros(3)
+        ctx = self._basis.context()
+        lib().hfb200_grid_last_call.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        lib().hfb200_grid_launches.argtypes = [ctypes.c_void_p]
+        check(lib().hfb200_grid_last_call(ctx, _p(out)))
+        return {"device_ms": float(out[0]), "h2d_bytes": int(out[1]), "d2h_bytes": int(out[2]), "launches": int(lib().hfb200_grid_launches(ctx))}
 
 
 class AtomicDFTGrid(_ProductGrid):

@@ -22,7 +22,7 @@ NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-fop
 CU_SOURCES = ["csrc/capi_common.cu", "csrc/capi_sadatom.cu", "csrc/sadatom_grid_lda.cu", "csrc/sadatom_grid_gga.cu", "csrc/sadatom_grid_mgga.cu",
               "csrc/capi_sadatom_exchange.cu", "csrc/capi_xc.cu",
               "csrc/chan_engine.cu", "csrc/comm.cu", "csrc/capi_atomic.cu", "csrc/capi_diatomic.cu", "csrc/grid2d.cu", "csrc/capi_grid2d.cu"]
-CPP_SOURCES = ["host/fem.cpp", "host/angular.cpp", "host/sadatom.cpp", "host/atomic.cpp", "host/legendre.cpp", "host/diatomic.cpp", "host/dftgrid.cpp", "host/hostapi.cpp"]
+CPP_SOURCES = ["host/fem.cpp", "host/angular.cpp", "host/sadatom.cpp", "host/atomic.cpp", "host/legendre.cpp", "host/diatomic.cpp", "host/dftgrid.cpp", "host/hostapi.cpp", "host/blockscan.cpp"]
 
 
 def _headers():

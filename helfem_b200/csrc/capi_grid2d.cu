@@ -21,7 +21,7 @@ bool valid_pair(int x_func, int c_func, int* fam) {
 }
 
 int eval_common(hfb200_ctx* c, const char* who, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, int ldp,
-                double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin) {
+                double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin, const int* skip) {
   if (!Pa || !Ha || (nspin != 1 && nspin != 2) || (nspin == 2 && (!Pb || (beta && !Hb)))) {
     set_error("%s: invalid argument / empty density matrix", who);
     return HFB200_EINVAL;
@@ -34,7 +34,7 @@ int eval_common(hfb200_ctx* c, const char* who, int x_func, int c_func, int nspi
   }
   HFB_CUDA_OK(cudaSetDevice(c->device));
   double sc[3] = {0, 0, 0};
-  const int rc = c->g2d->eval_fxc(fam, x_func, c_func, nspin, Pa, Pb, ldp, dens_thr, Ha, Hb, ldh, beta, sc, c->stream);
+  const int rc = c->g2d->eval_fxc(fam, x_func, c_func, nspin, Pa, Pb, ldp, dens_thr, Ha, Hb, ldh, beta, sc, c->stream, skip);
   if (rc) return rc;
   if (Exc) *Exc = sc[0];
   if (Nel) *Nel = sc[1];
@@ -64,42 +64,28 @@ int hfb200_atomic_eval_fxc(hfb200_ctx* c, int x_func, int c_func, int nspin, con
   if (!c || c->kind != CTX_ATOMIC) { set_error("hfb200_atomic_eval_fxc: invalid argument"); return HFB200_EINVAL; }
   const int ntot = (int)c->lval.size() * c->nrad;
   if (ldp < ntot || ldh < ntot) { set_error("Density matrix does not match basis set!"); return HFB200_EINVAL; }
-  return eval_common(c, "hfb200_atomic_eval_fxc", x_func, c_func, nspin, Pa, Pb, ldp, dens_thr, Ha, Hb, ldh, beta, Exc, Nel, Ekin);
+  return eval_common(c, "hfb200_atomic_eval_fxc", x_func, c_func, nspin, Pa, Pb, ldp, dens_thr, Ha, Hb, ldh, beta, Exc, Nel, Ekin, nullptr);
 }
 
 int hfb200_diatomic_eval_fxc(hfb200_ctx* c, int x_func, int c_func, int nspin, const double* Pa, const double* Pb, int ldp,
                              double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin) {
   if (!c || c->kind != CTX_DIATOMIC) { set_error("hfb200_diatomic_eval_fxc: invalid argument"); return HFB200_EINVAL; }
-  // pure <-> dummy index map (diatomic/basis.cpp:482-499)
-  std::vector<int> idx;
-  for (size_t i = 0; i < c->mval.size(); i++)
-    for (int a = (c->mval[i] != 0 ? 1 : 0); a < c->nrad; a++) idx.push_back((int)i * c->nrad + a);
-  const int npure = (int)idx.size(), nd = (int)c->lval.size() * c->nrad;
+  // pure <-> dummy index map (diatomic/basis.cpp:482-499): the first radial function of every m != 0 angular function is absent
+  // from the caller's matrices.  expand_boundaries (diatomic/basis.cpp:1754-1773) and remove_boundaries (dftgrid.cpp:809,854-855)
+  // happen while the angular blocks are packed / unpacked (grid2d.cu).
+  std::vector<int> skip(c->mval.size());
+  int npure = 0;
+  for (size_t i = 0; i < c->mval.size(); i++) { skip[i] = c->mval[i] != 0 ? 1 : 0; npure += c->nrad - skip[i]; }
   if (ldp < npure || ldh < npure) { set_error("Matrix does not have expected size!"); return HFB200_EINVAL; }
   if (!Pa || !Ha || (nspin == 2 && (!Pb || (beta && !Hb)))) { set_error("hfb200_diatomic_eval_fxc: empty density matrix"); return HFB200_EINVAL; }
-  // expand_boundaries (diatomic/basis.cpp:1754-1773), H in the dummy space, remove_boundaries (dftgrid.cpp:809,854-855)
-  std::vector<double> Pd((size_t)nd * nd * nspin, 0.0), Hd((size_t)nd * nd * nspin, 0.0);
-  for (int s = 0; s < nspin; s++) {
-    const double* P = s ? Pb : Pa;
-    double* D = Pd.data() + (size_t)s * nd * nd;
-#pragma omp parallel for schedule(static)
-    for (int j = 0; j < npure; j++)
-      for (int i = 0; i < npure; i++) D[(size_t)idx[i] + (size_t)idx[j] * nd] = P[(size_t)i + (size_t)j * ldp];
-  }
-  const int rc = eval_common(c, "hfb200_diatomic_eval_fxc", x_func, c_func, nspin, Pd.data(), nspin == 2 ? Pd.data() + (size_t)nd * nd : nullptr,
-                             nd, dens_thr, Hd.data(), nspin == 2 ? Hd.data() + (size_t)nd * nd : nullptr, nd, beta, Exc, Nel, Ekin);
-  if (rc) return rc;
-  for (int s = 0; s < nspin; s++) {
-    if (s == 1 && !beta) continue;
-    double* H = s ? Hb : Ha;
-    const double* D = Hd.data() + (size_t)s * nd * nd;
-#pragma omp parallel for schedule(static)
-    for (int j = 0; j < npure; j++)
-      for (int i = 0; i < npure; i++) H[(size_t)i + (size_t)j * ldh] = D[(size_t)idx[i] + (size_t)idx[j] * nd];
-  }
-  return HFB200_OK;
+  return eval_common(c, "hfb200_diatomic_eval_fxc", x_func, c_func, nspin, Pa, Pb, ldp, dens_thr, Ha, Hb, ldh, beta, Exc, Nel, Ekin, skip.data());
 }
 
 int hfb200_grid_launches(hfb200_ctx* c) { return (c && c->g2d) ? c->g2d->launches : 0; }
+int hfb200_grid_last_call(hfb200_ctx* c, double* out3) {
+  if (!c || !c->g2d || !out3) { set_error("hfb200_grid_last_call: invalid argument"); return HFB200_EINVAL; }
+  out3[0] = (double)c->g2d->device_ms; out3[1] = c->g2d->h2d_bytes; out3[2] = c->g2d->d2h_bytes;
+  return HFB200_OK;
+}
 
 }  // extern "C"

@@ -1,5 +1,6 @@
 // Host-side driver of the channel-coupled Coulomb / exchange kernels; see chan_engine.h.
 #include "chan_engine.h"
+#include "../host/blockscan.h"
 
 #include <algorithm>
 #include <chrono>
@@ -151,6 +152,13 @@ int ChanEngine::build(const ChanSpec& S, bool with_exchange) {
     const size_t nbytes = (f == &dCnz) ? (size_t)nchan : (size_t)npair;
     HFB_CUDA_OK(cudaMalloc(f, std::max<size_t>(nbytes, 1)));
     owned.push_back(*f);
+  }
+  {  // per-family ownership for the radial product: a rank of a sharded build skips the other ranks' families
+    unsigned char* f = nullptr;
+    HFB_CUDA_OK(cudaMalloc(&f, std::max<size_t>((size_t)nr, 1)));
+    owned.push_back(f);
+    HFB_CUDA_OK(cudaMemcpy(f, fam_owned.data(), (size_t)nr, cudaMemcpyHostToDevice));
+    prm.fam_own = f;
   }
   have_k = false;
   if (with_exchange && S.ktei) return build_exchange(S);
@@ -652,6 +660,7 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
   if (4 * prm.KS <= 512) chan_pre_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
   else chan_pre_generic_kernel<<<dim3(nel, nchan, 1), 128, 0, st>>>(q);
   HFB_CUDA_OK(cudaGetLastError());
+  if (comm) HFB_CUDA_OK(cudaMemsetAsync(dJc.p, 0, (size_t)nchan * nel * 8 * prm.MT * sizeof(double), st));  // skipped families sum as zeros
   int maxcol = 1;
   for (int r = 0; r < prm.nr; r++) maxcol = std::max(maxcol, fam_c0_host[r + 1] - fam_c0_host[r]);
   const int rts = (prm.MT + 3) / 4;
@@ -723,16 +732,7 @@ int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, 
   }
   // ---- scan: non-zero angular blocks of P ----
   std::vector<unsigned char> nz((size_t)npair, 0);
-#pragma omp parallel for collapse(2) schedule(dynamic, 16)
-  for (int i = 0; i < nang; i++)
-    for (int l = 0; l < nang; l++) {
-      unsigned char any = 0;
-      for (int b = 0; b < cnt[l] && !any; b++) {
-        const double* col = P + (size_t)r0[i] + (size_t)(r0[l] + b) * ldp;
-        for (int a = 0; a < cnt[i]; a++) any |= (col[a] != 0.0);
-      }
-      nz[(size_t)i * nang + l] = any;
-    }
+  scan_nonzero_blocks(&P, 1, ldp, nang, r0.data(), cnt.data(), nz.data());
   t_scan = now() - t_start;
   std::vector<int2> inb;
   for (int i = 0; i < nang; i++)
@@ -785,8 +785,7 @@ int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, 
   t_dev = now() - t_start - t_scan - t_pack;  // host side of the operator call (list upkeep, launches)
   // zero-fill the caller's matrix while the device works (the reference returns a zero-filled dense matrix)
   const double t_z0 = now();
-#pragma omp parallel for schedule(static)
-  for (int c = 0; c < nout; c++) memset(F + (size_t)c * ldf, 0, sizeof(double) * nout);
+  zero_fill(F, ldf, nout);
   t_zero = now() - t_z0;
   HFB_CUDA_OK(cudaStreamSynchronize(st));
   t_wait = now() - t_z0 - t_zero;

@@ -51,6 +51,7 @@ struct ChanParams {
   const unsigned char* pnz;  // [npair] the density band of the pair has a non-zero entry (nullptr: no screening)
   unsigned char* cnz;        // [nchan] the channel result jc has a non-zero entry
   unsigned char* onz;        // [npair] the J band of the pair has a non-zero entry
+  const unsigned char* fam_own;  // [nr] this rank computes the family (sharded builds; the results are summed over ranks)
 };
 
 // grid (nel, nchan, nb), 128 threads.  The couplings of the channel whose pair band is non-zero (pnz) are first compacted, IN ORDER,
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(256) chan_jmma_kernel(ChanParams prm) {
   const int gid = lane >> 2, t4 = lane & 3;
   const int KS = prm.KS, KP = 4 * KS, MP = 8 * prm.MT;
   const int mt0 = 4 * rt, nmt = min(4, prm.MT - mt0);
+  if (prm.fam_own && !prm.fam_own[r]) return;  // block-uniform: another rank's family (the launcher zeroed jc)
   const int c0 = prm.fam_c0[r];
   const int ncol = (prm.fam_c0[r + 1] - c0) * prm.nb;
   const int chunk = SPLITK ? 8 * NTW : 8 * 8 * NTW;

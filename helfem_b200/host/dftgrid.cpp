@@ -95,6 +95,15 @@ void DFTGrid::eval_Fxc(int x_func, const Vec& x_pars, int c_func, const Vec& c_p
                                       (int)Ha.nr, beta ? 1 : 0, &Exc, &Nel, &Ekin));
 }
 
+void DFTGrid::eval_Fxc(int x_func, int c_func, int nspin, size_t n, const double* Pa, const double* Pb, double* Ha, double* Hb, double& Exc,
+                       double& Nel, double& Ekin, bool beta, double thr) {
+  if (!Pa || (nspin == 2 && !Pb)) throw std::runtime_error("Error - density matrix is empty!\n");
+  if (n != basp->Nbf()) throw std::logic_error("Density matrix does not match basis set!\n");
+  upload();
+  throw_status(hfb200_atomic_eval_fxc(basp->context(), x_func, c_func, nspin, Pa, Pb, (int)n, thr, Ha, Hb, (int)n, beta ? 1 : 0, &Exc, &Nel, &Ekin));
+}
+
+
 }  // namespace atomic
 
 namespace diatomic {
@@ -128,6 +137,15 @@ void DFTGrid::eval_Fxc(int x_func, const Vec& x_pars, int c_func, const Vec& c_p
   throw_status(hfb200_diatomic_eval_fxc(basp->context(), x_func, c_func, 2, Pa.ptr(), Pb.ptr(), (int)Pa.nr, thr, Ha.ptr(), Hb.ptr(),
                                         (int)Ha.nr, beta ? 1 : 0, &Exc, &Nel, &Ekin));
 }
+
+void DFTGrid::eval_Fxc(int x_func, int c_func, int nspin, size_t n, const double* Pa, const double* Pb, double* Ha, double* Hb, double& Exc,
+                       double& Nel, double& Ekin, bool beta, double thr) {
+  if (!Pa || (nspin == 2 && !Pb)) throw std::runtime_error("Error - density matrix is empty!\n");
+  if (n != basp->Nbf()) throw std::logic_error("Matrix does not have expected size!\n");
+  upload();
+  throw_status(hfb200_diatomic_eval_fxc(basp->context(), x_func, c_func, nspin, Pa, Pb, (int)n, thr, Ha, Hb, (int)n, beta ? 1 : 0, &Exc, &Nel, &Ekin));
+}
+
 
 }  // namespace diatomic
 }  // namespace hfb

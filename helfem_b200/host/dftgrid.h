@@ -25,6 +25,10 @@ class DFTGrid {
   /// atomic/dftgrid.cpp:872-928
   void eval_Fxc(int x_func, const Vec& x_pars, int c_func, const Vec& c_pars, const Mat& Pa, const Mat& Pb, Mat& Ha, Mat& Hb,
                 double& Exc, double& Nel, double& Ekin, bool beta, double thr);
+  /// the same two operators on caller-owned column-major storage of order n (what arma::mat(ptr, n, n, false) wraps): no copies,
+  /// H fully overwritten
+  void eval_Fxc(int x_func, int c_func, int nspin, size_t n, const double* Pa, const double* Pb, double* Ha, double* Hb, double& Exc,
+                double& Nel, double& Ekin, bool beta, double thr);
   int n_angular_points() const { return lang * mang; }
 
  private:
@@ -48,6 +52,10 @@ class DFTGrid {
   /// diatomic/dftgrid.cpp:812-856
   void eval_Fxc(int x_func, const Vec& x_pars, int c_func, const Vec& c_pars, const Mat& Pa, const Mat& Pb, Mat& Ha, Mat& Hb,
                 double& Exc, double& Nel, double& Ekin, bool beta, double thr);
+  /// the same two operators on caller-owned column-major storage of order n (what arma::mat(ptr, n, n, false) wraps): no copies,
+  /// H fully overwritten
+  void eval_Fxc(int x_func, int c_func, int nspin, size_t n, const double* Pa, const double* Pb, double* Ha, double* Hb, double& Exc,
+                double& Nel, double& Ekin, bool beta, double thr);
   int n_angular_points() const { return lang * mang; }
 
  private:

@@ -30,19 +30,9 @@ static int grid_eval(void* g, void* b, int nrows, int x_func, int c_func, int ns
                      double* Ha, double* Hb, int beta, double* scal3) {
   HFH_TRY
   (void)b;
-  const size_t n = (size_t)nrows;  // the mirror class checks it against the basis like the reference does
-  Mat P1(n, n), P2, H1, H2;
-  memcpy(P1.ptr(), Pa, n * n * sizeof(double));
   double exc = 0, nel = 0, ekin = 0;
-  if (nspin == 1) {
-    ((Grid*)g)->eval_Fxc(x_func, Vec(), c_func, Vec(), P1, H1, exc, nel, ekin, thr);
-  } else {
-    P2 = Mat(n, n);
-    memcpy(P2.ptr(), Pb, n * n * sizeof(double));
-    ((Grid*)g)->eval_Fxc(x_func, Vec(), c_func, Vec(), P1, P2, H1, H2, exc, nel, ekin, beta != 0, thr);
-    if (Hb) memcpy(Hb, H2.ptr(), n * n * sizeof(double));
-  }
-  memcpy(Ha, H1.ptr(), n * n * sizeof(double));
+  // caller-owned storage, no copies; the mirror class checks the order against the basis like the reference does
+  ((Grid*)g)->eval_Fxc(x_func, c_func, nspin, (size_t)nrows, Pa, Pb, Ha, Hb, exc, nel, ekin, beta != 0, thr);
   scal3[0] = exc; scal3[1] = nel; scal3[2] = ekin;
   HFH_CATCH
 }

@@ -219,6 +219,10 @@ int hfb200_diatomic_eval_fxc(hfb200_ctx* ctx, int x_func, int c_func, int nspin,
                              double dens_thr, double* Ha, double* Hb, int ldh, int beta, double* Exc, double* Nel, double* Ekin);
 /* number of kernels the last product-grid eval_fxc launched (bench accounting) */
 int hfb200_grid_launches(hfb200_ctx* ctx);
+/* accounting of the last product-grid eval_fxc (no reference counterpart): out3 = { device milliseconds between the end of the
+ * upload and the end of the last kernel (CUDA events on the context's stream), bytes uploaded, bytes downloaded } -- the packed
+ * angular blocks, see DESIGN.md section 7 */
+int hfb200_grid_last_call(hfb200_ctx* ctx, double* out3);
 
 /* Pointwise XC on the device for validation (libxc array conventions, n points, host arrays;
  * outputs are overwritten with exchange + correlation). */

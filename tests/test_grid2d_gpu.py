@@ -144,3 +144,39 @@ def test_diatomic_grid_restricted_parity(native, case, fn):
 def test_diatomic_grid_unrestricted_parity(native, case, fn):
     b, g, o, P, Pa, Pb = diatomic_case(case)
     check_unrestricted(g, o, Pa, Pb, FUNCS[fn])
+
+
+@pytest.mark.parametrize("fn", ["pbe", "r2scan"])
+def test_diatomic_grid_m_diagonal_density(native, fn):
+    """Density with m_a = m_b blocks only (what an SCF on a linear molecule produces): rho and every field are independent of
+    phi, the product returns the m_a = m_b blocks of H and exact zeros elsewhere (the reference: round-off noise there)."""
+    b, g, o, P, Pa, Pb = diatomic_case("n2_l2m1")
+    pure = b.pure_indices()
+    m_of = np.repeat(np.asarray(b.mval), b.nrad)[pure]
+    Pm = np.asfortranarray(np.where(m_of[:, None] == m_of[None, :], P, 0.0))
+    H = check_restricted(g, o, Pm, FUNCS[fn])
+    assert float(np.max(np.abs(H[m_of[:, None] != m_of[None, :]]))) == 0.0
+    assert float(np.max(np.abs(H))) > 1e-3
+
+
+@pytest.mark.parametrize("fn", ["pbe", "r2scan"])
+def test_general_angular_rule_kernels(native, fn, monkeypatch):
+    """HFB200_G2D_GENERAL=1 at set_grid time keeps the pair-table kernels that serve an angular rule without the theta x phi
+    product structure; they must agree with the oracle (and hence with the factorised kernels) on the same inputs."""
+    import helfem_b200 as hb
+    monkeypatch.setenv("HFB200_G2D_GENERAL", "1")
+    Z1, Z2, Rb, primbas, nnodes, nelem, lmax, mmax, lang, mang = DIATOMIC["n2_l2m1"]
+    bd = hb.DiatomicBasis(Z1, Z2, Rb, nelem=nelem, nnodes=nnodes, primbas=primbas, lmax=lmax, mmax=mmax)
+    gd = hb.DiatomicDFTGrid(bd, lang, mang)
+    monkeypatch.delenv("HFB200_G2D_GENERAL")
+    b, g, o, P, Pa, Pb = diatomic_case("n2_l2m1")
+    check_restricted(gd, o, P, FUNCS[fn])
+    check_unrestricted(gd, o, Pa, Pb, FUNCS[fn])
+    name = "ne_l2m2"
+    Z, primbas, nnodes, nelem, lmax, mmax, nocc, lang, mang = ATOMIC[name]
+    monkeypatch.setenv("HFB200_G2D_GENERAL", "1")
+    ba = hb.AtomicBasis(Z=Z, nelem=nelem, nnodes=nnodes, primbas=primbas, lmax=lmax, mmax=mmax)
+    ga = hb.AtomicDFTGrid(ba, lang, mang)
+    monkeypatch.delenv("HFB200_G2D_GENERAL")
+    b, g, o, P, Pa, Pb = atomic_case(name)
+    check_restricted(ga, o, P, FUNCS[fn])
