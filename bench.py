@@ -20,10 +20,18 @@ independent Fock builds (coulomb + eval_Fxc) on one basis, ranks process their o
 ne_hf_cfg1 (configs[0]); smaller diatomic cases; the product-grid XC cases.
 """
 import os as _os
+import sys as _sys
 if int(_os.environ.get("WORLD_SIZE", "1")) > 1 and _os.environ.get("OMP_NUM_THREADS", "1") == "1":
-    # torchrun exports OMP_NUM_THREADS=1; the host side of the operator calls (block scan, pack, zero-fill) is OpenMP code and each
-    # rank gets its share of the cores instead (set before the native library and its OpenMP runtime are loaded)
-    _os.environ["OMP_NUM_THREADS"] = str(max(1, len(_os.sched_getaffinity(0)) // int(_os.environ.get("LOCAL_WORLD_SIZE", _os.environ["WORLD_SIZE"]))))
+    # torchrun exports OMP_NUM_THREADS=1, but the host side of the operator calls (block scan, pack, zero-fill) is OpenMP code.
+    # Set before the native library and its OpenMP runtime are loaded: the sharded atomic / diatomic build is driven by rank 0
+    # alone (the other ranks serve and do no host work), every other workload gives each rank its share of the cores.
+    _wl = _sys.argv[_sys.argv.index("--workload") + 1] if "--workload" in _sys.argv[:-1] else "n2_hf_cfg4"
+    _cores = len(_os.sched_getaffinity(0))
+    _local = int(_os.environ.get("LOCAL_WORLD_SIZE", _os.environ["WORLD_SIZE"]))
+    if "_hf_" in _wl and "--replicas" not in _sys.argv:
+        _os.environ["OMP_NUM_THREADS"] = str(max(1, _cores - _local + 1) if int(_os.environ.get("RANK", "0")) == 0 else 1)
+    else:
+        _os.environ["OMP_NUM_THREADS"] = str(max(1, _cores // _local))
 import argparse
 import ctypes
 import json
@@ -702,16 +710,32 @@ def run_chan(args, w, rank, world, local_rank):
     else:
         Ph = np.asfortranarray(Ph)
     ne2e = 2 if n > 8000 else 5
-    Jh, Kh = np.zeros_like(Ph, order="F"), np.zeros_like(Ph, order="F")  # caller-owned outputs, reused like an SCF loop's matrices
-    b.coulomb_into(Ph, Jh)
-    b.exchange_into(Ph, Kh)
+    driven = world > 1 and not args.replicas
+    if driven:
+        # N > 1: ONE process (rank 0) holds the host matrices and makes the reference-facing calls, like the reference's
+        # single-process SCF driver would; the other ranks serve (hfb200_comm_set_root / hfb200_chan_serve): the non-zero blocks
+        # of P reach them over NCCL, not through their own host memory
+        b.comm_set_root(0)
+    if rank == 0 or not driven:
+        Jh, Kh = np.zeros_like(Ph, order="F"), np.zeros_like(Ph, order="F")  # caller-owned outputs, reused like an SCF loop's matrices
+
+    def host_build():
+        if rank == 0 or not driven:
+            b.coulomb_into(Ph, Jh)
+            b.exchange_into(Ph, Kh)
+        else:
+            b.serve(False)
+            b.serve(True)
+
+    host_build()
     barrier()
     t0 = time.perf_counter()
     for _ in range(ne2e):
-        b.coulomb_into(Ph, Jh)
-        b.exchange_into(Ph, Kh)
+        host_build()
     torch.cuda.synchronize()
     t_e2e = (time.perf_counter() - t0) / ne2e
+    if driven:
+        b.comm_set_root(-1)
     if dist is not None:
         t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -802,7 +826,7 @@ def run_chan(args, w, rank, world, local_rank):
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": units / t_e2e, "unit": "builds/s", "h2d_bytes_per_step": 2 * nz_in * nrad * nrad * 8, "d2h_bytes_per_step": 2 * nz_out * nrad * nrad * 8,
                     "host_matrix_bytes_per_step": 4 * nb * nb * 8,
-                    "api": "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis, caller-owned outputs), every rank; only the "
+                    "api": "TwoDBasis::coulomb + TwoDBasis::exchange on dense host matrices (pure basis, caller-owned outputs)" + (", called by rank 0 alone, the other ranks serve (root-driven communicator: the blocks of P are broadcast over NCCL)" if driven else "") + "; only the "
                            "non-zero angular blocks of P and the blocks of J / K that can be non-zero cross PCIe (packed), the dense host "
                            "matrices are scanned / zero-filled on the host inside the timed region"},
             "gpu_launches": int(args.steps * nlaunch), "clocks": clocks}

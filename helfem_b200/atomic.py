@@ -121,6 +121,15 @@ class AtomicBasis:
         then return the complete J / K on every rank (all-reduce inside the library)."""
         check(lib().hfb200_comm_init(self.context(), ctypes.c_char_p(uid), int(rank), int(nranks)))
 
+    def comm_set_root(self, root):
+        """Root-driven host-matrix calls: after this (on every rank) only rank `root` calls coulomb / exchange; the others call
+        serve(exchange) once per root call.  root < 0: back to the default (every rank passes the matrices)."""
+        check(lib().hfb200_comm_set_root(self.context(), int(root)))
+
+    def serve(self, exchange):
+        """worker side of one root-driven coulomb (False) / exchange (True) call"""
+        check(lib().hfb200_chan_serve(self.context(), int(bool(exchange))))
+
     def coulomb_into(self, P, J):
         """coulomb with a caller-owned output (Fortran-ordered float64, fully overwritten): no allocation per call."""
         check_host(lib().hfh_atomic_coulomb(self._h, _p(P), _p(J)))

@@ -15,6 +15,7 @@
 namespace hfb {
 
 int comm_allreduce_sum(void* comm, double* buf, size_t n, cudaStream_t st);  // comm.cu
+int comm_broadcast(void* comm, double* buf, size_t n, int root, cudaStream_t st);
 
 namespace {
 template <class T>
@@ -716,6 +717,36 @@ int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, 
   const size_t nrad2 = (size_t)nrad * nrad;
   if (!map) nout = ntot;
   int rc;
+  // root-driven communicator (hfb200_comm_set_root): only the root passes host matrices; it broadcasts the list of non-zero
+  // blocks and their packed contents over NVLink, the other ranks take part through serve() with P = F = nullptr
+  const bool driven = comm && comm_root >= 0;
+  const bool worker = driven && comm_rank != comm_root;
+  if (worker != (P == nullptr)) {
+    set_error(worker ? "this rank is a worker of a root-driven communicator: call hfb200_chan_serve" : "dense_apply: null matrix");
+    return HFB200_EINVAL;
+  }
+  const size_t nhdr = 2 * (size_t)npair + 2;
+  if (worker) {
+    if ((rc = dHdr.reserve(nhdr)) || (rc = comm_broadcast(comm, dHdr.p, nhdr, comm_root, st))) return rc;
+    std::vector<double> hdr(nhdr);
+    HFB_CUDA_OK(cudaMemcpyAsync(hdr.data(), dHdr.p, nhdr * sizeof(double), cudaMemcpyDeviceToHost, st));
+    HFB_CUDA_OK(cudaStreamSynchronize(st));
+    const size_t nin = (size_t)hdr[0];
+    std::vector<int2> inb(nin);
+    for (size_t q = 0; q < nin; q++) inb[q] = make_int2((int)hdr[1 + 2 * q], (int)hdr[2 + 2 * q]);
+    if ((rc = dPdense.reserve((size_t)ntot * ntot)) || (rc = dKdense.reserve((size_t)ntot * ntot)) ||
+        (rc = dRed.reserve(std::max<size_t>(nin, 1) * nrad2)) || (rc = up_list(dIoBlocks, inb)))
+      return rc;
+    if ((rc = comm_broadcast(comm, dRed.p, nin * nrad2, comm_root, st))) return rc;
+    HFB_CUDA_OK(cudaMemsetAsync(dPdense.p, 0, (size_t)ntot * ntot * sizeof(double), st));
+    if (nin) {
+      chan_blocks_scatter_kernel<<<(unsigned)nin, 256, 0, st>>>(dPdense.p, ntot, nrad, (const int2*)dIoBlocks.p, dRed.p, 0);
+      HFB_CUDA_OK(cudaGetLastError());
+    }
+    if ((rc = exchange ? exchange_device(dPdense.p, ntot, dKdense.p, ntot, st) : coulomb_device(dPdense.p, ntot, dKdense.p, ntot, st))) return rc;
+    HFB_CUDA_OK(cudaStreamSynchronize(st));
+    return 0;
+  }
   const bool verbose = getenv("HFB200_X_VERBOSE") != nullptr;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double t_start = now();
@@ -767,6 +798,14 @@ int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, 
     }
   }
   HFB_CUDA_OK(cudaMemcpyAsync(dRed.p, hX.p, inb.size() * nrad2 * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (driven) {
+    if ((rc = dHdr.reserve(nhdr))) return rc;
+    hdr_host.assign(nhdr, 0.0);
+    hdr_host[0] = (double)inb.size();
+    for (size_t q = 0; q < inb.size(); q++) { hdr_host[1 + 2 * q] = inb[q].x; hdr_host[2 + 2 * q] = inb[q].y; }
+    HFB_CUDA_OK(cudaMemcpyAsync(dHdr.p, hdr_host.data(), nhdr * sizeof(double), cudaMemcpyHostToDevice, st));
+    if ((rc = comm_broadcast(comm, dHdr.p, nhdr, comm_root, st)) || (rc = comm_broadcast(comm, dRed.p, inb.size() * nrad2, comm_root, st))) return rc;
+  }
   HFB_CUDA_OK(cudaMemsetAsync(dPdense.p, 0, (size_t)ntot * ntot * sizeof(double), st));
   if (!inb.empty()) {
     chan_blocks_scatter_kernel<<<(unsigned)inb.size(), 256, 0, st>>>(dPdense.p, ntot, nrad, (const int2*)dIoBlocks.p, dRed.p, 0);
@@ -939,7 +978,7 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
 void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
-  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRed}) b->release();
+  for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRed, &dHdr}) b->release();
   for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab, &dRedBlocks, &dIoBlocks}) {
     if (L->p) cudaFree(L->p);
     L->p = nullptr;
@@ -985,6 +1024,18 @@ int hfb200_chan_exchange_counts(hfb200_ctx* c, long long* out, int n) {
   if (!c || !c->chan || !out || n < 1) { hfb::set_error("hfb200_chan_exchange_counts: invalid argument"); return HFB200_EINVAL; }
   for (int q = 0; q < n; q++) out[q] = q < 12 ? c->chan->counts[q] : 0;
   return HFB200_OK;
+}
+int hfb200_comm_set_root(hfb200_ctx* c, int root) {
+  if (!c || !c->chan || !c->comm || root >= c->shard_n) { hfb::set_error("hfb200_comm_set_root: needs a context with a communicator (hfb200_comm_init) and root < nranks"); return HFB200_EINVAL; }
+  c->chan->comm_root = root < 0 ? -1 : root;
+  c->chan->comm_rank = c->shard_rank;
+  return HFB200_OK;
+}
+int hfb200_chan_serve(hfb200_ctx* c, int exchange) {
+  if (!c || !c->chan || !c->comm) { hfb::set_error("hfb200_chan_serve: needs a context with a communicator"); return HFB200_EINVAL; }
+  if (c->chan->comm_root < 0 || c->chan->comm_rank == c->chan->comm_root) { hfb::set_error("hfb200_chan_serve: only the workers of a root-driven communicator (hfb200_comm_set_root) serve"); return HFB200_EINVAL; }
+  if (cudaSetDevice(c->device) != cudaSuccess) { hfb::set_error("cudaSetDevice failed"); return HFB200_ECUDA; }
+  return c->chan->dense_apply(exchange != 0, nullptr, 0, nullptr, 0, c->stream);
 }
 int hfb200_chan_allreduce_ms(hfb200_ctx* c, double* ms) {
   if (!c || !c->chan || !ms) { hfb::set_error("hfb200_chan_allreduce_ms: invalid argument"); return HFB200_EINVAL; }

@@ -47,6 +47,9 @@ struct ChanEngine {
   PinBuf hIn, hOut;
   std::vector<int> fam_c0_host;
   void* comm = nullptr;             // ncclComm_t (comm.cu) or null
+  int comm_root = -1, comm_rank = 0; // root-driven host-matrix calls (hfb200_comm_set_root); -1: every rank passes the matrices
+  DevBuf dHdr;                      // broadcast header of a root-driven call: [count, (i, l) ...]
+  std::vector<double> hdr_host;
   std::vector<char> fam_owned;      // [nr]
   std::vector<int> ang_m;           // [nang]
   // bra-contraction CSR over the couplings of ALL families (prm.post_* covers the owned ones only)

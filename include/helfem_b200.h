@@ -93,6 +93,14 @@ int hfb200_set_shard(hfb200_ctx* ctx, int rank, int nranks);
 int hfb200_comm_unique_id(void* id, int nbytes);
 int hfb200_comm_init(hfb200_ctx* ctx, const void* id, int rank, int nranks);
 int hfb200_comm_destroy(hfb200_ctx* ctx);
+/* Root-driven host-matrix calls (no reference counterpart: the reference is a single-process program).  After
+ * hfb200_comm_set_root(ctx, root) on EVERY rank, only rank `root` calls hfb200_{atomic,diatomic}_coulomb / _exchange with host
+ * matrices -- one SCF process driving all GPUs; it broadcasts the non-zero angular blocks of P to the other ranks over
+ * NCCL/NVLink, every rank computes its integral families, the all-reduce runs as before and the root returns the complete J / K.
+ * The other ranks call hfb200_chan_serve(ctx, exchange) once per root call (0: coulomb, 1: exchange), in the same order.
+ * root < 0 switches back to the default (every rank passes the same host matrix and gets the complete result). */
+int hfb200_comm_set_root(hfb200_ctx* ctx, int root);
+int hfb200_chan_serve(hfb200_ctx* ctx, int exchange);
 
 /* J = coulomb(P): P, J are nrad x nrad (host). */
 int hfb200_sadatom_coulomb(hfb200_ctx* ctx, const double* P, int ldp, double* J, int ldj);

@@ -63,6 +63,25 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)  # worst rank: every rank must hold the complete operator
         out["max_dJ_" + name], out["max_dK_" + name] = float(t[0]), float(t[1])
         ok = ok and float(t[0]) <= max(1e-9, 5e-14 * np.max(np.abs(Jo))) and float(t[1]) <= max(1e-9, 5e-14 * np.max(np.abs(Ko)))
+    # root-driven calls (hfb200_comm_set_root): only rank 0 passes host matrices, the others serve; rank 0 must get the same
+    # complete operators (the workers' densities are deliberately garbage-free: they pass nothing)
+    b.comm_set_root(0)
+    for name, P in (("sym", Psym), ("nonsym", Pns)):
+        if rank == 0:
+            J, K = b.coulomb(P), b.exchange(P)
+            Jo, Ko = o.coulomb(P), o.exchange(P)
+            dJ, dK = float(np.max(np.abs(J - Jo))), float(np.max(np.abs(K - Ko)))
+            good = dJ <= max(1e-9, 5e-14 * np.max(np.abs(Jo))) and dK <= max(1e-9, 5e-14 * np.max(np.abs(Ko)))
+        else:
+            b.serve(False)
+            b.serve(True)
+            dJ = dK = 0.0
+            good = True
+        t = torch.tensor([dJ, dK, 0.0 if good else 1.0], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["root_driven_max_dJ_" + name], out["root_driven_max_dK_" + name] = float(t[0]), float(t[1])
+        ok = ok and float(t[2]) == 0.0
+    b.comm_set_root(-1)
     out["parity_ok"] = bool(ok)
     if rank == 0:
         print(json.dumps(out), flush=True)
