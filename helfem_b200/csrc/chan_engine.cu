@@ -642,7 +642,7 @@ int launch_xf_same(const ChanXParams& q, const int4* groups, int ngroups, const 
 template <int NI, int NTL>
 int launch_xf_pair(const ChanXParams& q, const int4* groups, int ngroups, const int2* tiles, int nsm, cudaStream_t st) {
   if (q.nel < 2) return 0;
-  const size_t smem = ((size_t)NI * q.stack * ChxfPair<NTL>::RS + (size_t)8 * ChxfPair<NTL>::YS + chxf_ring_doubles(q.PB)) * sizeof(double);
+  const size_t smem = ((size_t)NI * q.stack * ChxfPair<NTL>::RS + (size_t)8 * ChxfPair<NTL>::YS + chxf_ring_doubles(q.PB) + chxf_pair_table_doubles(q.np2, q.stack)) * sizeof(double);
   HFB_CUDA_OK(cudaFuncSetAttribute(chan_xf_pair_kernel<NI, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long units = (long long)ngroups * q.nel * (q.nel - 1);
   chan_xf_pair_kernel<NI, NTL><<<(unsigned)std::min<long long>(units, (NTL <= 2 ? 2LL : 1LL) * nsm), CHXF_THREADS, smem, st>>>(q, groups, ngroups, tiles);

@@ -42,8 +42,15 @@ constexpr int CHXF_THREADS = 288;           // 8 consumer warps + 1 producer war
 // bank-conflict free (and 16-byte aligned, as a bulk-copy destination must be).
 __host__ __device__ inline int chxf_rows(int PB) { return PB < 256 ? PB : 256; }
 __host__ __device__ inline int chxf_pbs(int PB) { return (chxf_rows(PB) - 4 + 15) / 16 * 16 + 4; }
-__host__ __device__ inline size_t chxf_ring_doubles(int PB) { return (size_t)CHXF_STAGES * CHXF_SLOTS * chxf_pbs(PB); }
-__host__ __device__ inline size_t chxf_inline_ring_doubles(int PB) { return chxf_ring_doubles(PB); }
+// A stage = CHXF_SLOTS sub-blocks of PBS doubles + the stage's coupling coefficients (CHXF_SLOTS x [2 stack halves][8 items]):
+// both arrive by bulk copy and complete the same `full` barrier, so no consumer ever waits on a global load of its own.
+#ifndef HFB_XF_PSTAGES
+#define HFB_XF_PSTAGES 5
+#endif
+constexpr int CHXF_PSTAGES = HFB_XF_PSTAGES;  // ring depth of the pair kernel (its shared memory also holds the unit's integral tables)
+__host__ __device__ inline int chxf_stage_doubles(int PB) { return CHXF_SLOTS * (chxf_pbs(PB) + 16); }
+__host__ __device__ inline size_t chxf_ring_doubles(int PB) { return (size_t)CHXF_PSTAGES * chxf_stage_doubles(PB); }
+__host__ __device__ inline size_t chxf_inline_ring_doubles(int PB) { return (size_t)CHXF_STAGES * chxf_stage_doubles(PB); }
 
 // ---- mbarrier / bulk-copy primitives (PTX) ----
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
@@ -67,12 +74,34 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
       "DONE_%=:\n"
       "}\n" ::"r"(a), "r"(parity) : "memory");
 }
+// the same wait for the producer warp, which has nothing else to do: a suspend-time hint keeps its polling out of the issue slots
+__device__ __forceinline__ void mbar_wait_relaxed(unsigned long long* bar, unsigned parity) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(a), "r"(parity), "r"(20000u) : "memory");
+}
 // global -> shared bulk copy (the TMA engine's 1-D form), completion counted in bytes on an mbarrier
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                    (unsigned)__cvta_generic_to_shared(dst)),
                "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
+// 8-byte asynchronous copy global -> shared (the integral tables of a pair unit: their rows are only 8-byte aligned)
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// disjoint-factor tables of a pair unit in shared memory: [stack halves a] iint^a, then [stack halves b] jint^b, TBL doubles each
+__host__ __device__ inline int chxf_pair_tbl(int np2) { return (np2 + 1) & ~1; }
+__host__ __device__ inline size_t chxf_pair_table_doubles(int np2, int stack) { return (size_t)2 * stack * chxf_pair_tbl(np2); }
 // barrier of the 8 consumer warps only (the producer warp never joins it)
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
@@ -84,19 +113,19 @@ __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;
 // arrived.  The producer is only ever held back by `empty`, so it runs ahead ACROSS phases and units: while the
 // consumers multiply (phase 2) the first stages of their next angular contraction (phase 1) are already landing.
 struct ChxfPipe {
-  unsigned long long* full;   // [CHXF_STAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
-  unsigned long long* empty;  // [CHXF_STAGES]  all 8 consumer warps are done with it (8 arrivals)
+  unsigned long long* full;   // [CHXF_PSTAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
+  unsigned long long* empty;  // [CHXF_PSTAGES]  all 8 consumer warps are done with it (8 arrivals)
   int stage = 0;
   unsigned phase = 0;
   __device__ __forceinline__ void advance() {
-    if (++stage == CHXF_STAGES) { stage = 0; phase ^= 1u; }
+    if (++stage == CHXF_PSTAGES) { stage = 0; phase ^= 1u; }
   }
 };
 __device__ __forceinline__ void chxf_pipe_init(ChxfPipe& pipe, unsigned long long* bars) {
   pipe.full = bars;
-  pipe.empty = bars + CHXF_STAGES;
+  pipe.empty = bars + CHXF_PSTAGES;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < CHXF_STAGES; s++) { mbar_init(pipe.full + s, 1); mbar_init(pipe.empty + s, 8); }
+    for (int s = 0; s < CHXF_PSTAGES; s++) { mbar_init(pipe.full + s, 1); mbar_init(pipe.empty + s, 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -109,7 +138,7 @@ __device__ __forceinline__ void chxf_pipe_init(ChxfPipe& pipe, unsigned long lon
 __device__ __forceinline__ void chxf_produce(const ChanXParams& prm, ChxfPipe& pipe, const double* __restrict__ Wa, int s_begin, int s_end,
                                              int pair, int k0, double* ring) {
   const int lane = threadIdx.x & 31;
-  const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: 64-byte multiples
+  const int PB = prm.PB, PBS = chxf_pbs(PB), SD = chxf_stage_doubles(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: 64-byte multiples
   const size_t wstride = (size_t)prm.stack * prm.WB;
   const double* src0 = Wa + (size_t)pair * PB + k0;
   const unsigned bytes = (unsigned)rows * 8u;
@@ -117,12 +146,13 @@ __device__ __forceinline__ void chxf_produce(const ChanXParams& prm, ChxfPipe& p
   for (int s0 = s_begin; s0 < s_end; s0 += CHXF_SLOTS) {
     const long long wb_next = (lane < CHXF_SLOTS && s0 + CHXF_SLOTS < s_end) ? __ldg(prm.slot_wblk + s0 + CHXF_SLOTS + lane) : 0;
     if (lane == 0) {
-      mbar_wait(pipe.empty + pipe.stage, pipe.phase ^ 1u);  // passes at once on the first trip round the ring
-      mbar_expect_tx(pipe.full + pipe.stage, bytes * CHXF_SLOTS);
+      mbar_wait_relaxed(pipe.empty + pipe.stage, pipe.phase ^ 1u);  // passes at once on the first trip round the ring
+      mbar_expect_tx(pipe.full + pipe.stage, bytes * CHXF_SLOTS + CHXF_SLOTS * 128u);
     }
     __syncwarp();
-    if (lane < CHXF_SLOTS)
-      bulk_g2s(ring + (size_t)(pipe.stage * CHXF_SLOTS + lane) * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pipe.stage);
+    double* dst = ring + (size_t)pipe.stage * SD;
+    if (lane < CHXF_SLOTS) bulk_g2s(dst + (size_t)lane * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pipe.stage);
+    else if (lane == CHXF_SLOTS) bulk_g2s(dst + (size_t)CHXF_SLOTS * PBS, prm.slot_coef + (size_t)s0 * 16, CHXF_SLOTS * 128u, pipe.full + pipe.stage);
     wb = wb_next;
     pipe.advance();
   }
@@ -135,7 +165,7 @@ __device__ __forceinline__ void chxf_produce(const ChanXParams& prm, ChxfPipe& p
 template <int NB, class Emit>
 __device__ __forceinline__ void chxf_consume(const ChanXParams& prm, ChxfPipe& pipe, const int2* sU, int ntl, int k0, int b0, const double* ring, Emit emit) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
-  const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);
+  const int PB = prm.PB, PBS = chxf_pbs(PB), SD = chxf_stage_doubles(PB), rows = min(256, PB - k0);
   for (int tt = 0; tt < ntl; tt++) {
     const int2 U = sU[tt];  // (first slot, slot count) of the tile, staged in shared memory by the caller
     double acc[4][NB][2];
@@ -144,13 +174,13 @@ __device__ __forceinline__ void chxf_consume(const ChanXParams& prm, ChxfPipe& p
 #pragma unroll
       for (int b = 0; b < NB; b++) { acc[mi][b][0] = 0.0; acc[mi][b][1] = 0.0; }
     for (int s0 = 0; s0 < U.y; s0 += CHXF_SLOTS) {
-      double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments: requested before the wait
+      mbar_wait(pipe.full + pipe.stage, pipe.phase);
+      const double* S = ring + (size_t)pipe.stage * SD + gid;
+      double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments of the stage (they came with it)
 #pragma unroll
       for (int ks = 0; ks < CHXF_SLOTS / 4; ks++)
 #pragma unroll
-        for (int b = 0; b < NB; b++) bf[ks][b] = __ldg(prm.slot_coef + (size_t)(U.x + s0 + 4 * ks + t4) * 16 + (b0 + b) * 8 + gid);
-      mbar_wait(pipe.full + pipe.stage, pipe.phase);
-      const double* S = ring + (size_t)(pipe.stage * CHXF_SLOTS) * PBS + gid;
+        for (int b = 0; b < NB; b++) bf[ks][b] = S[CHXF_SLOTS * PBS + (4 * ks + t4) * 16 + (b0 + b) * 8];
 #pragma unroll
       for (int ks = 0; ks < CHXF_SLOTS / 4; ks++) {
 #pragma unroll
@@ -176,8 +206,8 @@ __device__ __forceinline__ void chxf_consume(const ChanXParams& prm, ChxfPipe& p
 struct ChxfPipeInline {
   unsigned long long* full;   // [CHXF_STAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
   unsigned long long* empty;  // [CHXF_STAGES]  all 8 warps are done with the stage   (8 arrivals)
-  int c_stage = 0, p_stage = 0;
-  unsigned c_phase = 0, p_phase = 0;
+  int c_stage = 0;
+  unsigned c_phase = 0;
 };
 __device__ __forceinline__ void chxf_pipe_inline_init(ChxfPipeInline& pipe, unsigned long long* bars) {
   pipe.full = bars;
@@ -189,65 +219,93 @@ __device__ __forceinline__ void chxf_pipe_inline_init(ChxfPipeInline& pipe, unsi
   __syncthreads();
 }
 
-// Phase 1 of the fused kernels for the tiles [t0, t0 + ntl) of a group, rows [k0, k0 + 256) of the sub-block `pair` = ie nel + je,
-// stack half a of W (Wa = W + a WB):   R[row][item] = sum_slots W^a_slot[row] coef^b[slot][item]    (b = b0 .. b0 + NB - 1)
-// as a DMMA GEMM (M = rows, N = the tile's 8 items, K = slots).  The A operand arrives through a ring of CHXF_STAGES stages
-// of CHXF_SLOTS sub-blocks: thread 0 issues one BULK COPY (cp.async.bulk, the TMA engine) per sub-block -- W is stored
-// element pair by element pair, so a sub-block is one contiguous run -- which signals the stage's `full` mbarrier by byte
-// count; every warp arrives on the stage's `empty` mbarrier when it is done with it; the producer runs CHXF_STAGES - 1
-// stages ahead ACROSS tiles and no block-wide barrier is involved.  Warp w owns the m-tiles w, w + 8, w + 16, w + 24;
-// `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt after the tile's last stage.
-template <int NB, class Emit>
-__device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfPipeInline& pipe, const double* __restrict__ Wa, int t0, int ntl, int pair,
-                                            int k0, int b0, double* ring, Emit emit) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
-  const int PB = prm.PB, PBS = chxf_pbs(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: whole m-tiles, 64-byte multiples
-  const size_t wstride = (size_t)prm.stack * prm.WB;
-  const double* src0 = Wa + (size_t)pair * PB + k0;
+// Producer of the same-element kernel.  The stages a CTA consumes form ONE flattened sequence: sweeps x stack pairs ab x row
+// chunks k0 x tiles x stages of CHXF_SLOTS slots.  Thread 0 walks that sequence with a cursor kept in SHARED memory (the kernel
+// sits at its 128-register cap) and stays CHXF_STAGES - 1 stages ahead of the consumers ACROSS the boundaries of the sequence:
+// the first stages of the next stack pair's angular contraction are requested while the last ones of the current pair are
+// consumed and land during its radial product (phase 2), so only the very first fill of a CTA is cold.
+struct ChxfSameCursor {
+  int sweep, ab, k0, tt, s, u, nu, done, p_stage;
+  unsigned p_phase;
+};
+constexpr int CHXF_SWB = 512;  // block numbers of a group's slots kept in shared memory
+__device__ __forceinline__ void chxf_same_produce(const ChanXParams& prm, ChxfPipeInline& pipe, ChxfSameCursor* cur, const int2* sU, const int* sWb,
+                                                  int slot0, int ntl, int pair, double* ring) {
+  if (threadIdx.x != 0 || cur->done) return;
+  const int PB = prm.PB, PBS = chxf_pbs(PB), st = prm.stack;
+  int pst = cur->p_stage;
+  unsigned pph = cur->p_phase;
+  const int k0 = cur->k0, rows = min(256, PB - k0);
   const unsigned bytes = (unsigned)rows * 8u;
-  // the ring may alias storage that was written through the generic proxy (the pair kernel's staging tiles): order
-  // those writes before the async-proxy writes of the bulk copies, and make sure nobody still uses that storage
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  __syncthreads();
-  // producer cursor over (tile, chunk of CHXF_SLOTS slots); only thread 0 issues
-  int p_tt = 0, p_s = 0, p_nu = 0, p_u = 0;
-  if (ntl > 0) { const int2 U = prm.tile_u[t0]; p_u = U.x; p_nu = U.y; }
-  auto produce = [&]() {
-    if (tid == 0 && p_tt < ntl) {
-      mbar_wait(pipe.empty + pipe.p_stage, pipe.p_phase ^ 1u);  // passes at once on the first trip round the ring
-      mbar_expect_tx(pipe.full + pipe.p_stage, bytes * CHXF_SLOTS);
-      double* dst = ring + (size_t)(pipe.p_stage * CHXF_SLOTS) * PBS;
+  const size_t wstride = (size_t)st * prm.WB;
+  const double* src0 = prm.W + (size_t)(cur->ab / st) * prm.WB + (size_t)pair * PB + k0;
+  mbar_wait(pipe.empty + pst, pph ^ 1u);  // passes at once on the first trip round the ring
+  mbar_expect_tx(pipe.full + pst, bytes * CHXF_SLOTS + CHXF_SLOTS * 128u);
+  double* dst = ring + (size_t)pst * chxf_stage_doubles(PB);
+  const int sl = cur->u + cur->s;
 #pragma unroll
-      for (int q = 0; q < CHXF_SLOTS; q++) {
-        const long long wb = __ldg(prm.slot_wblk + p_u + p_s + q);
-        bulk_g2s(dst + (size_t)q * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pipe.p_stage);
+  for (int q = 0; q < CHXF_SLOTS; q++) {
+    const int rel = sl + q - slot0;  // the group's block numbers are staged in shared memory (sWb) as far as they fit
+    const long long wb = rel < CHXF_SWB ? (long long)sWb[rel] : __ldg(prm.slot_wblk + sl + q);
+    bulk_g2s(dst + (size_t)q * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pst);
+  }
+  bulk_g2s(dst + (size_t)CHXF_SLOTS * PBS, prm.slot_coef + (size_t)sl * 16, CHXF_SLOTS * 128u, pipe.full + pst);
+  if (++pst == CHXF_STAGES) { pst = 0; pph ^= 1u; }
+  cur->p_stage = pst; cur->p_phase = pph;
+  // advance the cursor
+  int s = cur->s + CHXF_SLOTS;
+  if (s >= cur->nu) {
+    s = 0;
+    int tt = cur->tt + 1;
+    if (tt == ntl) {
+      tt = 0;
+      int k = k0 + 256;
+      if (k >= prm.np2) {
+        k = 0;
+        int ab = cur->ab + 1;
+        if (ab == st * st) {
+          ab = 0;
+          if (++cur->sweep == (prm.MT + 31) / 32) cur->done = 1;
+        }
+        cur->ab = ab;
       }
-      p_s += CHXF_SLOTS;
-      if (p_s >= p_nu) {
-        p_tt++;
-        p_s = 0;
-        if (p_tt < ntl) { const int2 U = prm.tile_u[t0 + p_tt]; p_u = U.x; p_nu = U.y; }
-      }
-      if (++pipe.p_stage == CHXF_STAGES) { pipe.p_stage = 0; pipe.p_phase ^= 1u; }
+      cur->k0 = k;
     }
-  };
-  for (int q = 0; q < CHXF_STAGES - 1; q++) produce();
+    cur->tt = tt;
+    const int2 U = sU[tt];
+    cur->u = U.x; cur->nu = U.y;
+  }
+  cur->s = s;
+}
+
+// Phase 1 of the same-element kernel for the tiles [t0, t0 + ntl) of a group, rows [k0, k0 + 256) of the sub-block `pair`:
+//   R[row][item] = sum_slots W^a_slot[row] coef^b[slot][item]    (b = b0 .. b0 + NB - 1)
+// as a DMMA GEMM (M = rows, N = the tile's 8 items, K = slots).  The A operand arrives through the ring of CHXF_STAGES stages of
+// CHXF_SLOTS sub-blocks filled by chxf_same_produce (bulk copies, the TMA engine's 1-D form; W is stored element pair by
+// element pair, so a sub-block is one contiguous run) which signals a stage's `full` mbarrier by byte count; every warp arrives
+// on the stage's `empty` mbarrier when it is done with it; no block-wide barrier is involved.  Warp w owns the m-tiles w, w + 8,
+// w + 16, w + 24; `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt.
+template <int NB, class Emit>
+__device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfPipeInline& pipe, ChxfSameCursor* cur, const int2* sU, const int* sWb,
+                                                   int slot0, int ntl, int pair, int k0, int b0, double* ring, Emit emit) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
+  const int PB = prm.PB, PBS = chxf_pbs(PB), SD = chxf_stage_doubles(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: whole m-tiles
   for (int tt = 0; tt < ntl; tt++) {
-    const int2 U = prm.tile_u[t0 + tt];
+    const int2 U = sU[tt];
     double acc[4][NB][2];
 #pragma unroll
     for (int mi = 0; mi < 4; mi++)
 #pragma unroll
       for (int b = 0; b < NB; b++) { acc[mi][b][0] = 0.0; acc[mi][b][1] = 0.0; }
     for (int s0 = 0; s0 < U.y; s0 += CHXF_SLOTS) {
-      produce();
-      double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments: requested before the wait
+      chxf_same_produce(prm, pipe, cur, sU, sWb, slot0, ntl, pair, ring);
+      mbar_wait(pipe.full + pipe.c_stage, pipe.c_phase);
+      const double* S = ring + (size_t)pipe.c_stage * SD + gid;
+      double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments of the stage (they came with it)
 #pragma unroll
       for (int ks = 0; ks < CHXF_SLOTS / 4; ks++)
 #pragma unroll
-        for (int b = 0; b < NB; b++) bf[ks][b] = __ldg(prm.slot_coef + (size_t)(U.x + s0 + 4 * ks + t4) * 16 + (b0 + b) * 8 + gid);
-      mbar_wait(pipe.full + pipe.c_stage, pipe.c_phase);
-      const double* S = ring + (size_t)(pipe.c_stage * CHXF_SLOTS) * PBS + gid;
+        for (int b = 0; b < NB; b++) bf[ks][b] = S[CHXF_SLOTS * PBS + (4 * ks + t4) * 16 + (b0 + b) * 8];
 #pragma unroll
       for (int ks = 0; ks < CHXF_SLOTS / 4; ks++) {
 #pragma unroll
@@ -284,7 +342,18 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
   double* ring = Bt + (size_t)NI * LDK;
   for (int q = tid; q < NI * LDK; q += 256) Bt[q] = 0.0;
   ChxfPipeInline pipe;
-  chxf_pipe_inline_init(pipe, bars);
+  __shared__ ChxfSameCursor cur;
+  __shared__ int2 sT[CHXF_TMAX], sU[CHXF_TMAX];  // the group's tiles: (first item, item count), (first slot, slot count)
+  __shared__ int sWb[CHXF_SWB];                  // W block of the group's slots (the slots of a group are consecutive)
+  const int2 U0 = prm.tile_u[t0], U1 = prm.tile_u[t0 + ntl - 1];
+  const int slot0 = U0.x, nslot = U1.x + U1.y - U0.x;
+  if (tid < ntl) { sT[tid] = tiles[t0 + tid]; sU[tid] = prm.tile_u[t0 + tid]; }
+  for (int q = tid; q < min(nslot, CHXF_SWB); q += 256) sWb[q] = (int)__ldg(prm.slot_wblk + slot0 + q);
+  if (tid == 0) {
+    cur.sweep = 0; cur.ab = 0; cur.k0 = 0; cur.tt = 0; cur.s = 0; cur.u = U0.x; cur.nu = U0.y; cur.done = 0; cur.p_stage = 0; cur.p_phase = 0;
+  }
+  chxf_pipe_inline_init(pipe, bars);  // (block-wide barrier: the cursor and the tables are visible)
+  for (int q = 0; q < CHXF_STAGES - 1; q++) chxf_same_produce(prm, pipe, &cur, sU, sWb, slot0, ntl, e * nel + e, ring);
 
   double acc[4][NTN][2];
 #pragma unroll
@@ -295,14 +364,13 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
 
   for (int mt0 = 0; mt0 < MT; mt0 += 32) {  // 32 m-tiles per sweep (4 per warp); np2 <= 256 needs one sweep
     for (int ab = 0; ab < st2; ab++) {
-      const int a = ab / st, b = ab % st;
-      const double sg = (a == b) ? fac : -fac;
+      const int b = ab % st;
+      const double sg = (ab / st == b) ? fac : -fac;
       __syncthreads();  // the previous product is done with the tile (first pass: the zero fill is complete)
       // ---- phase 1: Bt[n][k] = sg sum_slots W^a_slot[k] coef^b[slot][n] ----
-      const double* Wa = prm.W + (size_t)a * prm.WB;
       for (int k0 = 0; k0 < np2; k0 += 256) {
-        chxf_phase1_inline<1>(prm, pipe, Wa, t0, ntl, e * nel + e, k0, b, ring, [&](int tt, double (&ra)[4][1][2]) {
-          const int2 T = tiles[t0 + tt];
+        chxf_phase1_inline<1>(prm, pipe, &cur, sU, sWb, slot0, ntl, e * nel + e, k0, b, ring, [&](int tt, double (&ra)[4][1][2]) {
+          const int2 T = sT[tt];
           double* Bn = Bt + (T.x - it0 + 2 * t4) * LDK + k0 + 8 * warp + gid;  // rows outside the element are zero in W
           const bool ok0 = 2 * t4 < T.y, ok1 = 2 * t4 + 1 < T.y;
 #pragma unroll
@@ -370,13 +438,13 @@ struct ChxfPair {
   static constexpr int YS = 8 * NTL * LDY;
 };
 
-// persistent grid, CHXF_THREADS threads, dynamic smem NI * stack * RS + 8 * YS + chxf_ring_doubles(PB) doubles.
+// persistent grid, CHXF_THREADS threads, dynamic smem NI * stack * RS + 8 * YS + chxf_ring_doubles(PB) + chxf_pair_table_doubles doubles.
 // Units: (group, ordered pair of different elements).
 template <int NI, int NTL>
 __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair_kernel(ChanXParams prm, const int4* __restrict__ groups, int ngroups,
                                                                                         const int2* __restrict__ tiles) {
   extern __shared__ __align__(128) double sm[];
-  __shared__ unsigned long long bars[2 * CHXF_STAGES];
+  __shared__ unsigned long long bars[2 * CHXF_PSTAGES];
   __shared__ int2 sT[CHXF_TMAX], sU[CHXF_TMAX];
   using Geo = ChxfPair<NTL>;
   constexpr int LDR = Geo::LDR, RS = Geo::RS, LDY = Geo::LDY;
@@ -386,6 +454,8 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
   double* Rt = sm;                                                   // [NI][st][RS]
   double* Y = sm + (size_t)NI * st * RS + (warp & 7) * Geo::YS;      // per-warp staging of the first product
   double* ring = sm + (size_t)NI * st * RS + (size_t)8 * Geo::YS;    // bulk-copy stages
+  double* sI = ring + chxf_ring_doubles(prm.PB);                     // the unit's disjoint-factor tables (cp.async by the consumers)
+  const int TBL = chxf_pair_tbl(np2);
   for (int q = tid; q < NI * st * RS; q += CHXF_THREADS) Rt[q] = 0.0;  // padding rows / columns stay zero for good
   ChxfPipe pipe;
   chxf_pipe_init(pipe, bars);
@@ -437,7 +507,17 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
         for (int qt = 0; qt < NTL; qt++) { kacc[it][mt][qt][0] = 0.0; kacc[it][mt][qt][1] = 0.0; }
 
     for (int a = 0; a < st; a++) {
-      consumer_sync();  // the previous products are done with Rt
+      consumer_sync();  // the previous products are done with Rt (and with the previous unit's tables)
+      if (a == 0) {
+        // this unit's disjoint factors iint^a (element ie), jint^b (element je): requested now, they land during phase 1
+        const double* ib = (lower ? prm.big_f : prm.small_f) + ((size_t)r * nel + ie) * st * np2;
+        const double* jb = (lower ? prm.small_f : prm.big_f) + ((size_t)r * nel + je) * st * np2;
+        for (int q = tid; q < 2 * st * np2; q += 256) {
+          const int which = q / np2, i = q - which * np2;
+          cp_async8(sI + which * TBL + i, (which < st ? ib + (size_t)which * np2 : jb + (size_t)(which - st) * np2) + i);
+        }
+        cp_async_commit();
+      }
       // ---- phase 1: Rt[n][b](i, l) = (+-) fac sum_slots W^a_slot(i, l) coef^b[slot][n], both stack halves b at once ----
       for (int k0 = 0; k0 < np2; k0 += 256) {
         auto store = [&](int tt, int mi, int b, double v0, double v1) {
@@ -466,24 +546,25 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
         if (st == 2) chxf_consume<2>(prm, pipe, sU, ntl, k0, 0, ring, emit2);
         else chxf_consume<1>(prm, pipe, sU, ntl, k0, 0, ring, emit1);
       }
+      if (a == 0) cp_async_wait_all();
       consumer_sync();
     // ---- phase 2: Ksub += iint^a . Rsub^{ab} . (jint^b)^T for the warp's items ----
-    const double* iint = (lower ? prm.big_f : prm.small_f) + (((size_t)r * nel + ie) * st + a) * np2;
+    const double* iint = sI + a * TBL;
     double af[2 * NTL][NTL];
 #pragma unroll
     for (int ks = 0; ks < 2 * NTL; ks++) {
       const int kk = 4 * ks + t4;
 #pragma unroll
-      for (int mt = 0; mt < NTL; mt++) af[ks][mt] = (kk < np && 8 * mt + gid < np) ? __ldg(iint + (8 * mt + gid) + kk * np) : 0.0;
+      for (int mt = 0; mt < NTL; mt++) af[ks][mt] = (kk < np && 8 * mt + gid < np) ? iint[(8 * mt + gid) + kk * np] : 0.0;
     }
     for (int b = 0; b < st; b++) {
-      const double* jint = (lower ? prm.small_f : prm.big_f) + (((size_t)r * nel + je) * st + b) * np2;
+      const double* jint = sI + (st + b) * TBL;
       double jf[2 * NTL][NTL];
 #pragma unroll
       for (int ks = 0; ks < 2 * NTL; ks++) {
         const int kk = 4 * ks + t4;
 #pragma unroll
-        for (int mt = 0; mt < NTL; mt++) jf[ks][mt] = (kk < np && 8 * mt + gid < np) ? __ldg(jint + (8 * mt + gid) + kk * np) : 0.0;
+        for (int mt = 0; mt < NTL; mt++) jf[ks][mt] = (kk < np && 8 * mt + gid < np) ? jint[(8 * mt + gid) + kk * np] : 0.0;
       }
 #pragma unroll
       for (int it = 0; it < NIT; it++) {

@@ -1,4 +1,2 @@
-N=${1:-2}
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 tools/shard_nccl_check.py > gpurun_out/r02r_shard_check_n$N.json 2> gpurun_out/r02r_shard_check_n$N.err; tail -n 3 gpurun_out/r02r_shard_check_n$N.err; cat gpurun_out/r02r_shard_check_n$N.json
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29522 bench.py --gpus $N --steps 10 > gpurun_out/r02r_cfg4_n$N.json 2> gpurun_out/r02r_cfg4_n$N.err; tail -n 3 gpurun_out/r02r_cfg4_n$N.err
-python -c "import json; d=json.load(open('gpurun_out/r02r_cfg4_n$N.json')); print('cfg4 N=$N', d['value'], d['ms_per_step'], d['scaling'], 'e2e', d['e2e']['value']); [print(' ', e['stage'], round(e['ms'],3)) for e in d['roofline']['stages']]"
+timeout 600 python -m pytest tests/test_atomic_gpu.py tests/test_diatomic_gpu.py tests/test_hotpath_goldens.py -m gpu -x -q 2>&1 | tail -n 2
+timeout 300 python bench.py --workload n2_hf_cfg4 --steps 3 --warmup 1 --kernels-only 2>&1 | tail -n 1
