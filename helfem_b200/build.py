@@ -18,6 +18,7 @@ LIB = os.path.join(HERE, "libhelfem_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-fopenmp,-O2"]
+NVCC_FLAGS += os.environ.get("HFB200_NVCC_EXTRA", "").split()  # experiments: extra -D switches (rebuild with --force)
 
 CU_SOURCES = ["csrc/capi_common.cu", "csrc/capi_sadatom.cu", "csrc/sadatom_grid_lda.cu", "csrc/sadatom_grid_gga.cu", "csrc/sadatom_grid_mgga.cu",
               "csrc/capi_sadatom_exchange.cu", "csrc/capi_xc.cu",

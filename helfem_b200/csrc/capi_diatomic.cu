@@ -148,6 +148,8 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
   c->chan->comm = c->comm;
+  c->chan->comm_rank = c->shard_rank;
+  c->chan->comm_size = c->comm ? c->shard_n : 1;
   const int rc = c->chan->build(S, prim_ktei != nullptr);
   if (rc) return rc;
   c->nL = nlm;

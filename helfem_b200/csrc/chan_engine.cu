@@ -312,6 +312,10 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang + 8));  // + the symmetry flag of P
     owned.push_back(p);
     dNzP = p;
+    int* slots = nullptr;
+    HFB_CUDA_OK(cudaMalloc(&slots, 1024 * sizeof(int)));  // per-SM arrival counters of the fused same-element kernel
+    owned.push_back(slots);
+    dSmSlot = slots;
     if (hNzP) cudaFreeHost(hNzP);
     HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang + 8));
   }
@@ -859,8 +863,17 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
   // block mask of P and its exact-symmetry flag; the per-pattern lists are rebuilt only when either changes
   static const bool allow_sym = getenv("HFB200_X_NOSYM") == nullptr;
   tick(0, true);
-  HFB_CUDA_OK(cudaMemsetAsync(dNzP + nang2, allow_sym ? 1 : 0, 1, st));
-  chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP, allow_sym ? dNzP + nang2 : nullptr);
+  if (comm && comm_size > 1) {  // every rank scans its share of the blocks; the flags are summed over the ranks
+    if ((rc = dHdr.reserve(2 * nang2 + 2))) return rc;
+    HFB_CUDA_OK(cudaMemsetAsync(dHdr.p, 0, (nang2 + 1) * sizeof(double), st));
+    chan_x0_mask_kernel<<<(unsigned)((nang2 + comm_size - 1) / comm_size), 128, 0, st>>>(dPm, ldpm, nrad, nang, nullptr, nullptr, comm_rank, comm_size, dHdr.p);
+    HFB_CUDA_OK(cudaGetLastError());
+    if ((rc = comm_allreduce_sum(comm, dHdr.p, nang2 + 1, st))) return rc;
+    chan_x0_flags_kernel<<<(unsigned)((nang2 + 1 + 255) / 256), 256, 0, st>>>(dHdr.p, (int)nang2, dNzP, allow_sym ? 1 : 0);
+  } else {
+    HFB_CUDA_OK(cudaMemsetAsync(dNzP + nang2, allow_sym ? 1 : 0, 1, st));
+    chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP, allow_sym ? dNzP + nang2 : nullptr);
+  }
   tick(0, false);
   HFB_CUDA_OK(cudaGetLastError());
   HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2 + 1, cudaMemcpyDeviceToHost, st));
@@ -914,6 +927,10 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       }
       if (ngs == 0) continue;
       tick(2, true);
+      static const bool stagger = getenv("HFB200_X_NOSTAGGER") == nullptr;
+      q.nsm = std::min(nsm, 1024);
+      q.sm_slot = stagger ? dSmSlot : nullptr;
+      if (stagger) HFB_CUDA_OK(cudaMemsetAsync(dSmSlot, 0, 1024 * sizeof(int), st));
       const int4* gS = (const int4*)dGroupsS.p + B.gs0;
       if (ni_same == 32) rc = launch_xf_same<32>(q, gS, ngs, tiles, nsm, st);
       else if (ni_same == 16) rc = launch_xf_same<16>(q, gS, ngs, tiles, nsm, st);
@@ -1028,7 +1045,6 @@ int hfb200_chan_exchange_counts(hfb200_ctx* c, long long* out, int n) {
 int hfb200_comm_set_root(hfb200_ctx* c, int root) {
   if (!c || !c->chan || !c->comm || root >= c->shard_n) { hfb::set_error("hfb200_comm_set_root: needs a context with a communicator (hfb200_comm_init) and root < nranks"); return HFB200_EINVAL; }
   c->chan->comm_root = root < 0 ? -1 : root;
-  c->chan->comm_rank = c->shard_rank;
   return HFB200_OK;
 }
 int hfb200_chan_serve(hfb200_ctx* c, int exchange) {

@@ -47,6 +47,7 @@ struct ChanEngine {
   PinBuf hIn, hOut;
   std::vector<int> fam_c0_host;
   void* comm = nullptr;             // ncclComm_t (comm.cu) or null
+  int comm_size = 1;                // ranks of the communicator; comm_rank: this rank (set with comm)
   int comm_root = -1, comm_rank = 0; // root-driven host-matrix calls (hfb200_comm_set_root); -1: every rank passes the matrices
   DevBuf dHdr;                      // broadcast header of a root-driven call: [count, (i, l) ...]
   std::vector<double> hdr_host;
@@ -82,6 +83,7 @@ struct ChanEngine {
   int* dTiles1 = nullptr;
   std::vector<int> ang_group;                       // [nang]
   unsigned char *dNzP = nullptr, *hNzP = nullptr;
+  int* dSmSlot = nullptr;  // [1024] per-SM arrival counters (stagger of the fused same-element kernel)
   DevBuf dPdense, dKdense, dKblocks, dW;
 
   int build_items(const unsigned char* nz, bool sym);

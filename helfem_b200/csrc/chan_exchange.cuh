@@ -73,16 +73,22 @@ struct ChanXParams {
   const long long* slot_wblk;  // [slots] block of the batch's W buffer
   const double* slot_coef;     // [slots][2 stack halves][8 items of the tile]
   int sym;                     // P is exactly symmetric: only the items j <= k exist, x4 also writes the transposed block
+  int* sm_slot;                // [>= SM count] zeroed before every fused same-element launch: order of arrival of the first wave's CTAs on each SM
+  int nsm;                     // SM count of the device
 };
 
 // Frobenius-norm mask of the angular blocks of P, and whether P is EXACTLY symmetric (checked on the non-zero blocks only:
 // a zero block whose transposed partner is non-zero is caught from the partner's side).  grid (nang*nang), 128 threads.
 // sym_flag: one byte, preset to 1, cleared on the first mismatch.
+// Sharded run (nranks > 1): rank r scans the blocks b = r, r + nranks, ... and writes 0 / 1 (and a mismatch mark at [nang^2]) into the
+// zeroed double array flagsD, which the engine all-reduces and chan_x0_flags_kernel turns back into the byte mask.
 static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* P, int ldp, int nrad, int nang, unsigned char* nz,
-                                                                  unsigned char* sym_flag) {
+                                                                  unsigned char* sym_flag, int rank = 0, int nranks = 1, double* flagsD = nullptr) {
   __shared__ double red[4];
   __shared__ int s_nz;
-  const int i = blockIdx.x / nang, l = blockIdx.x % nang;
+  const int blk_id = blockIdx.x * nranks + rank;
+  if (blk_id >= nang * nang) return;
+  const int i = blk_id / nang, l = blk_id % nang;
   const double* blk = P + (size_t)i * nrad + (size_t)l * nrad * ldp;
   double s = 0.0;
   for (int k = threadIdx.x; k < nrad * nrad; k += blockDim.x) {
@@ -96,18 +102,27 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
   if (threadIdx.x == 0) {
     const double t = (red[0] + red[1]) + (red[2] + red[3]);
     const int f = (sqrt(t) >= 10.0 * 2.220446049250313e-16) ? 1 : 0;
-    nz[blockIdx.x] = (unsigned char)f;
+    if (flagsD) flagsD[blk_id] = (double)f;
+    else nz[blk_id] = (unsigned char)f;
     s_nz = f;
   }
   __syncthreads();
-  if (!s_nz || sym_flag == nullptr) return;
+  if (!s_nz || (sym_flag == nullptr && flagsD == nullptr)) return;
   const double* tb = P + (size_t)l * nrad + (size_t)i * nrad * ldp;  // block (l, i)
   bool same = true;
   for (int k = threadIdx.x; k < nrad * nrad; k += blockDim.x) {
     const int A = k % nrad, B = k / nrad;
     same = same && (blk[A + (size_t)B * ldp] == tb[B + (size_t)A * ldp]);
   }
-  if (!same) *sym_flag = 0;
+  if (!same) {
+    if (flagsD) flagsD[nang * nang] = 1.0;
+    else *sym_flag = 0;
+  }
+}
+static __global__ void __launch_bounds__(256) chan_x0_flags_kernel(const double* flagsD, int n, unsigned char* nz, int allow_sym) {
+  const int q = blockIdx.x * 256 + threadIdx.x;
+  if (q < n) nz[q] = flagsD[q] != 0.0 ? 1 : 0;
+  else if (q == n) nz[n] = (allow_sym && flagsD[n] == 0.0) ? 1 : 0;
 }
 
 // Tiling of the two angular contractions: a CTA owns up to CHX_T rows that share their coupled partners (same m),

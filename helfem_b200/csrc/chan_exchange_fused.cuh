@@ -352,6 +352,19 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
   if (tid == 0) {
     cur.sweep = 0; cur.ab = 0; cur.k0 = 0; cur.tt = 0; cur.s = 0; cur.u = U0.x; cur.nu = U0.y; cur.done = 0; cur.p_stage = 0; cur.p_phase = 0;
   }
+  // Two CTAs share an SM and alternate between a latency-bound phase 1 (no tensor work) and a phase 2 that saturates the DMMA
+  // pipe.  CTAs that start together stay in lock step (both wait for W, then both split the pipe), and so do their successors;
+  // an offset between the two is preserved just as well.  So the second CTA to arrive on each SM in the FIRST wave waits
+  // about one phase 2 (MT KS NTN DMMAs on 4 sub-partitions, 16 cycles each): from then on one CTA multiplies while the other
+  // fetches, for the rest of the launch.
+  if (tid == 0 && prm.sm_slot && (int)(blockIdx.x + gridDim.x * blockIdx.y) < 2 * prm.nsm) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (atomicAdd(prm.sm_slot + smid, 1) & 1) {
+      const long long t_begin = clock64(), wait = (long long)MT * KS * NTN * 4;
+      while (clock64() - t_begin < wait) __nanosleep(200);
+    }
+  }
   chxf_pipe_inline_init(pipe, bars);  // (block-wide barrier: the cursor and the tables are visible)
   for (int q = 0; q < CHXF_STAGES - 1; q++) chxf_same_produce(prm, pipe, &cur, sU, sWb, slot0, ntl, e * nel + e, ring);
 
@@ -392,8 +405,13 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
         const int mt = mt0 + warp + 8 * mi;
         af[mi] = (mt < MT) ? __ldg(A + (size_t)mt * KS * 32) : 0.0;
       }
+#ifdef HFB_XF_SKIP_P2
+      const int KS_run = 1;  // timing experiment only (wrong results): what the kernel costs without its radial product
+#else
+      const int KS_run = KS;
+#endif
 #pragma unroll 2
-      for (int ks = 0; ks < KS; ks++) {
+      for (int ks = 0; ks < KS_run; ks++) {
         double bf[NTN];
 #pragma unroll
         for (int mi = 0; mi < 4; mi++) {

@@ -107,7 +107,7 @@ int hfb200_comm_init(hfb200_ctx* c, const void* id, int rank, int nranks) {
   ncclComm_t comm = nullptr;
   HFB_NCCL_OK(g_nccl.CommInitRank(&comm, nranks, u, rank));
   c->comm = comm;
-  if (c->chan) c->chan->comm = comm;
+  if (c->chan) { c->chan->comm = comm; c->chan->comm_rank = rank; c->chan->comm_size = nranks; }
   return HFB200_OK;
 }
 
@@ -118,7 +118,7 @@ int hfb200_comm_destroy(hfb200_ctx* c) {
     g_nccl.CommDestroy((ncclComm_t)c->comm);
   }
   c->comm = nullptr;
-  if (c->chan) c->chan->comm = nullptr;
+  if (c->chan) { c->chan->comm = nullptr; c->chan->comm_size = 1; c->chan->comm_root = -1; }
   return HFB200_OK;
 }
 
