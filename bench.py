@@ -931,7 +931,11 @@ def run_sweep(args, w, rank, world, local_rank):
             nb = sum(units[u]["niter"] for u in ids)  # consecutive queue entries are consecutive in memory
             if host:
                 P_, J_, H_, S_ = (t.numpy().reshape(nbuilds, -1)[f0:f0 + nb] for t in (hP, hJ, hH, hS))
+                tq = time.perf_counter()
                 b.fock_host(nb, x, c, 2, nsl, thr, P_, J_, H_, S_)
+                if os.environ.get("HFB200_SWEEP_DIAG"):
+                    dt = time.perf_counter() - tq
+                    sys.stderr.write("[sweep diag] rank %d fock_host nb %d: %.2f ms, %.1f GB/s (H2D + D2H)\n" % (rank, nb, 1e3 * dt, (P_.nbytes + J_.nbytes + H_.nbytes) / dt / 1e9))
             else:
                 b.fock_batch(nb, x, c, 2, nsl, thr, dP.data_ptr() + f0 * perP * 8, dJ.data_ptr() + f0 * blk * 8, dH.data_ptr() + f0 * perH * 8,
                              dS.data_ptr() + f0 * 32, sh)

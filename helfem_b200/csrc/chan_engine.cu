@@ -312,10 +312,6 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
     HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang + 8));  // + the symmetry flag of P
     owned.push_back(p);
     dNzP = p;
-    int* slots = nullptr;
-    HFB_CUDA_OK(cudaMalloc(&slots, 1024 * sizeof(int)));  // per-SM arrival counters of the fused same-element kernel
-    owned.push_back(slots);
-    dSmSlot = slots;
     if (hNzP) cudaFreeHost(hNzP);
     HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang + 8));
   }
@@ -927,10 +923,6 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       }
       if (ngs == 0) continue;
       tick(2, true);
-      static const bool stagger = getenv("HFB200_X_NOSTAGGER") == nullptr;
-      q.nsm = std::min(nsm, 1024);
-      q.sm_slot = stagger ? dSmSlot : nullptr;
-      if (stagger) HFB_CUDA_OK(cudaMemsetAsync(dSmSlot, 0, 1024 * sizeof(int), st));
       const int4* gS = (const int4*)dGroupsS.p + B.gs0;
       if (ni_same == 32) rc = launch_xf_same<32>(q, gS, ngs, tiles, nsm, st);
       else if (ni_same == 16) rc = launch_xf_same<16>(q, gS, ngs, tiles, nsm, st);
@@ -1069,3 +1061,13 @@ int hfb200_chan_set_profile(hfb200_ctx* c, int on) {
   return HFB200_OK;
 }
 }
+
+#ifdef HFB_XF_TRACE
+// debug only: copies the phase trace of the fused same-element kernel (chan_exchange_fused.cuh) to the host
+extern "C" int hfb200_debug_trace(unsigned long long* out, int* counts) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hfb::g_trace, sizeof(unsigned long long) * 148 * 4096);
+  cudaMemcpyFromSymbol(counts, hfb::g_trace_n, sizeof(int) * 148);
+  return 0;
+}
+#endif

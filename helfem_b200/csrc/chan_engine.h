@@ -83,7 +83,6 @@ struct ChanEngine {
   int* dTiles1 = nullptr;
   std::vector<int> ang_group;                       // [nang]
   unsigned char *dNzP = nullptr, *hNzP = nullptr;
-  int* dSmSlot = nullptr;  // [1024] per-SM arrival counters (stagger of the fused same-element kernel)
   DevBuf dPdense, dKdense, dKblocks, dW;
 
   int build_items(const unsigned char* nz, bool sym);

@@ -73,8 +73,6 @@ struct ChanXParams {
   const long long* slot_wblk;  // [slots] block of the batch's W buffer
   const double* slot_coef;     // [slots][2 stack halves][8 items of the tile]
   int sym;                     // P is exactly symmetric: only the items j <= k exist, x4 also writes the transposed block
-  int* sm_slot;                // [>= SM count] zeroed before every fused same-element launch: order of arrival of the first wave's CTAs on each SM
-  int nsm;                     // SM count of the device
 };
 
 // Frobenius-norm mask of the angular blocks of P, and whether P is EXACTLY symmetric (checked on the non-zero blocks only:

@@ -25,6 +25,22 @@
 #include "chan_exchange.cuh"
 
 namespace hfb {
+// Debug only (-DHFB_XF_TRACE, tools/xf_trace.py): phase timeline of the same-element kernel's CTAs on the first SMs.
+#ifdef HFB_XF_TRACE
+__device__ unsigned long long g_trace[148 * 4096];
+__device__ int g_trace_n[148];
+__device__ __forceinline__ void xf_trace(int ev, unsigned long long payload = 0) {
+  if (threadIdx.x != 0) return;
+  unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  if (smid >= 4) return;
+  unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  if (ev == 5) t = payload;
+  const int i = atomicAdd(&g_trace_n[smid], 1);
+  if (i < 4096) g_trace[smid * 4096 + i] = (t << 20) | ((unsigned long long)(blockIdx.x + gridDim.x * blockIdx.y) & 0xffff) << 4 | (unsigned)ev;
+}
+#else
+#define xf_trace(...)
+#endif
 
 constexpr int CHXF_TMAX = 16;  // tiles per group (a group closes at NI items or CHXF_TMAX tiles)
 #ifndef HFB_XF_SLOTS
@@ -200,14 +216,21 @@ __device__ __forceinline__ void chxf_consume(const ChanXParams& prm, ChxfPipe& p
   }
 }
 
-// ---- same-element kernel: one CTA per (group, element), 256 threads, the producer is lane 0 of warp 0 inline with the
-//      consumers (the kernel needs 128 registers per thread for its 4 x 4 accumulator tiles, which a ninth warp at two
-//      CTAs per SM does not leave) ----
+// ---- same-element kernel: one CTA per (group, element), 256 threads, no producer warp (the kernel needs 128 registers per
+//      thread for its 4 x 4 accumulator tiles, which a ninth warp at two CTAs per SM does not leave) ----
+// A single thread needs ~0.3 us to issue one stage (mbarrier wait + expect_tx + five bulk copies, measured with
+// tools/micro/bulk_copy_bench.cu: ~0.2 us fixed + ~40 ns per copy), far more than the 8 warps need to consume it, so the
+// issuing is STATELESS and ROTATES over the warps: the stages a CTA consumes form one flat sequence g = 0 .. G-1 (sweeps x stack
+// pairs ab x row chunks k0 x stages; the slots of a group are consecutive, so stage j of a pass is slots 4j .. 4j+3 of the
+// group), everything about stage g follows from g alone, and lane 0 of warp (g mod 8) issues it CHXF_STAGES - 1 stages ahead
+// of its own consumption, in any order relative to the other warps.  The sequence runs across the stack pairs: the first
+// stages of the next angular contraction land during the current radial product (phase 2).
 struct ChxfPipeInline {
   unsigned long long* full;   // [CHXF_STAGES]  bytes of the stage have landed        (1 arrival + transaction bytes)
   unsigned long long* empty;  // [CHXF_STAGES]  all 8 warps are done with the stage   (8 arrivals)
-  int c_stage = 0;
-  unsigned c_phase = 0;
+  int g = 0;                  // next stage this warp consumes
+  int c_stage = 0;            // = g mod CHXF_STAGES
+  unsigned c_phase = 0;       // = (g / CHXF_STAGES) & 1
 };
 __device__ __forceinline__ void chxf_pipe_inline_init(ChxfPipeInline& pipe, unsigned long long* bars) {
   pipe.full = bars;
@@ -218,87 +241,57 @@ __device__ __forceinline__ void chxf_pipe_inline_init(ChxfPipeInline& pipe, unsi
   }
   __syncthreads();
 }
-
-// Producer of the same-element kernel.  The stages a CTA consumes form ONE flattened sequence: sweeps x stack pairs ab x row
-// chunks k0 x tiles x stages of CHXF_SLOTS slots.  Thread 0 walks that sequence with a cursor kept in SHARED memory (the kernel
-// sits at its 128-register cap) and stays CHXF_STAGES - 1 stages ahead of the consumers ACROSS the boundaries of the sequence:
-// the first stages of the next stack pair's angular contraction are requested while the last ones of the current pair are
-// consumed and land during its radial product (phase 2), so only the very first fill of a CTA is cold.
-struct ChxfSameCursor {
-  int sweep, ab, k0, tt, s, u, nu, done, p_stage;
-  unsigned p_phase;
-};
 constexpr int CHXF_SWB = 512;  // block numbers of a group's slots kept in shared memory
-__device__ __forceinline__ void chxf_same_produce(const ChanXParams& prm, ChxfPipeInline& pipe, ChxfSameCursor* cur, const int2* sU, const int* sWb,
-                                                  int slot0, int ntl, int pair, double* ring) {
-  if (threadIdx.x != 0 || cur->done) return;
-  const int PB = prm.PB, PBS = chxf_pbs(PB), st = prm.stack;
-  int pst = cur->p_stage;
-  unsigned pph = cur->p_phase;
-  const int k0 = cur->k0, rows = min(256, PB - k0);
-  const unsigned bytes = (unsigned)rows * 8u;
+// Issue stage g (one thread).  nst: stages of one pass over the group's slots; passes: (sweep, ab, k0 chunk), k0 fastest.
+__device__ __forceinline__ void chxf_same_issue(const ChanXParams& prm, const ChxfPipeInline& pipe, int g, int nst, const int* sWb, int slot0, int pair,
+                                                double* ring) {
+  const int PB = prm.PB, PBS = chxf_pbs(PB), st = prm.stack, nk0 = (prm.np2 + 255) >> 8;
+  const int j = g % nst;
+  int q = g / nst;
+  const int k0 = (q % nk0) << 8;
+  q /= nk0;
+  const int a = (q % (st * st)) / st;
+  const int rs = g % CHXF_STAGES;
+  const unsigned use = (unsigned)(g / CHXF_STAGES);
+  const unsigned bytes = (unsigned)min(256, PB - k0) * 8u;
   const size_t wstride = (size_t)st * prm.WB;
-  const double* src0 = prm.W + (size_t)(cur->ab / st) * prm.WB + (size_t)pair * PB + k0;
-  mbar_wait(pipe.empty + pst, pph ^ 1u);  // passes at once on the first trip round the ring
-  mbar_expect_tx(pipe.full + pst, bytes * CHXF_SLOTS + CHXF_SLOTS * 128u);
-  double* dst = ring + (size_t)pst * chxf_stage_doubles(PB);
-  const int sl = cur->u + cur->s;
+  const double* src0 = prm.W + (size_t)a * prm.WB + (size_t)pair * PB + k0;
+  mbar_wait(pipe.empty + rs, (use & 1u) ^ 1u);  // the consumers are done with the previous use of the ring slot (first use: passes at once)
+  mbar_expect_tx(pipe.full + rs, bytes * CHXF_SLOTS + CHXF_SLOTS * 128u);
+  double* dst = ring + (size_t)rs * chxf_stage_doubles(PB);
 #pragma unroll
-  for (int q = 0; q < CHXF_SLOTS; q++) {
-    const int rel = sl + q - slot0;  // the group's block numbers are staged in shared memory (sWb) as far as they fit
-    const long long wb = rel < CHXF_SWB ? (long long)sWb[rel] : __ldg(prm.slot_wblk + sl + q);
-    bulk_g2s(dst + (size_t)q * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + pst);
+  for (int c = 0; c < CHXF_SLOTS; c++) {
+    const int rel = CHXF_SLOTS * j + c;  // the group's block numbers are staged in shared memory (sWb) as far as they fit
+    const long long wb = rel < CHXF_SWB ? (long long)sWb[rel] : __ldg(prm.slot_wblk + slot0 + rel);
+    bulk_g2s(dst + (size_t)c * PBS, src0 + (size_t)wb * wstride, bytes, pipe.full + rs);
   }
-  bulk_g2s(dst + (size_t)CHXF_SLOTS * PBS, prm.slot_coef + (size_t)sl * 16, CHXF_SLOTS * 128u, pipe.full + pst);
-  if (++pst == CHXF_STAGES) { pst = 0; pph ^= 1u; }
-  cur->p_stage = pst; cur->p_phase = pph;
-  // advance the cursor
-  int s = cur->s + CHXF_SLOTS;
-  if (s >= cur->nu) {
-    s = 0;
-    int tt = cur->tt + 1;
-    if (tt == ntl) {
-      tt = 0;
-      int k = k0 + 256;
-      if (k >= prm.np2) {
-        k = 0;
-        int ab = cur->ab + 1;
-        if (ab == st * st) {
-          ab = 0;
-          if (++cur->sweep == (prm.MT + 31) / 32) cur->done = 1;
-        }
-        cur->ab = ab;
-      }
-      cur->k0 = k;
-    }
-    cur->tt = tt;
-    const int2 U = sU[tt];
-    cur->u = U.x; cur->nu = U.y;
-  }
-  cur->s = s;
+  bulk_g2s(dst + (size_t)CHXF_SLOTS * PBS, prm.slot_coef + (size_t)(slot0 + CHXF_SLOTS * j) * 16, CHXF_SLOTS * 128u, pipe.full + rs);
 }
 
-// Phase 1 of the same-element kernel for the tiles [t0, t0 + ntl) of a group, rows [k0, k0 + 256) of the sub-block `pair`:
-//   R[row][item] = sum_slots W^a_slot[row] coef^b[slot][item]    (b = b0 .. b0 + NB - 1)
-// as a DMMA GEMM (M = rows, N = the tile's 8 items, K = slots).  The A operand arrives through the ring of CHXF_STAGES stages of
-// CHXF_SLOTS sub-blocks filled by chxf_same_produce (bulk copies, the TMA engine's 1-D form; W is stored element pair by
-// element pair, so a sub-block is one contiguous run) which signals a stage's `full` mbarrier by byte count; every warp arrives
-// on the stage's `empty` mbarrier when it is done with it; no block-wide barrier is involved.  Warp w owns the m-tiles w, w + 8,
-// w + 16, w + 24; `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt.
+// Phase 1 of the same-element kernel for the tiles of a group (sU: their (first slot, slot count)), rows [k0, k0 + 256) of the
+// sub-block `pair`:   R[row][item] = sum_slots W^a_slot[row] coef^b[slot][item]    (b = b0 .. b0 + NB - 1)
+// as a DMMA GEMM (M = rows, N = the tile's 8 items, K = slots).  The A operand and the coefficients arrive through the ring
+// (chxf_same_issue: bulk copies, the TMA engine's 1-D form; W is stored element pair by element pair, so a sub-block is one
+// contiguous run) which signals a stage's `full` mbarrier by byte count; every warp arrives on the stage's `empty` mbarrier when
+// it is done with it; no block-wide barrier is involved.  Warp w owns the m-tiles w, w + 8, w + 16, w + 24;
+// `emit(tt, acc)` receives acc[mi][b][c] = R[row k0 + 8 (w + 8 mi) + gid][item 2 t4 + c] of tile tt.  G: stages of the CTA.
 template <int NB, class Emit>
-__device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfPipeInline& pipe, ChxfSameCursor* cur, const int2* sU, const int* sWb,
-                                                   int slot0, int ntl, int pair, int k0, int b0, double* ring, Emit emit) {
+__device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfPipeInline& pipe, const int2* sU, const int* sWb, int slot0, int nst, int G,
+                                                   int ntl, int pair, int k0, int b0, double* ring, Emit emit) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, t4 = lane & 3;
   const int PB = prm.PB, PBS = chxf_pbs(PB), SD = chxf_stage_doubles(PB), rows = min(256, PB - k0);  // PB is a multiple of 8: whole m-tiles
   for (int tt = 0; tt < ntl; tt++) {
-    const int2 U = sU[tt];
+    const int nu = sU[tt].y;
     double acc[4][NB][2];
 #pragma unroll
     for (int mi = 0; mi < 4; mi++)
 #pragma unroll
       for (int b = 0; b < NB; b++) { acc[mi][b][0] = 0.0; acc[mi][b][1] = 0.0; }
-    for (int s0 = 0; s0 < U.y; s0 += CHXF_SLOTS) {
-      chxf_same_produce(prm, pipe, cur, sU, sWb, slot0, ntl, pair, ring);
+    for (int s0 = 0; s0 < nu; s0 += CHXF_SLOTS) {
+      {
+        const int gp = pipe.g + CHXF_STAGES - 1;
+        if (lane == 0 && (gp & 7) == warp && gp < G) chxf_same_issue(prm, pipe, gp, nst, sWb, slot0, pair, ring);
+      }
       mbar_wait(pipe.full + pipe.c_stage, pipe.c_phase);
       const double* S = ring + (size_t)pipe.c_stage * SD + gid;
       double bf[CHXF_SLOTS / 4][NB];  // coefficient fragments of the stage (they came with it)
@@ -319,6 +312,7 @@ __device__ __forceinline__ void chxf_phase1_inline(const ChanXParams& prm, ChxfP
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(pipe.empty + pipe.c_stage);
+      pipe.g++;
       if (++pipe.c_stage == CHXF_STAGES) { pipe.c_stage = 0; pipe.c_phase ^= 1u; }
     }
     emit(tt, acc);
@@ -342,31 +336,17 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
   double* ring = Bt + (size_t)NI * LDK;
   for (int q = tid; q < NI * LDK; q += 256) Bt[q] = 0.0;
   ChxfPipeInline pipe;
-  __shared__ ChxfSameCursor cur;
   __shared__ int2 sT[CHXF_TMAX], sU[CHXF_TMAX];  // the group's tiles: (first item, item count), (first slot, slot count)
   __shared__ int sWb[CHXF_SWB];                  // W block of the group's slots (the slots of a group are consecutive)
   const int2 U0 = prm.tile_u[t0], U1 = prm.tile_u[t0 + ntl - 1];
   const int slot0 = U0.x, nslot = U1.x + U1.y - U0.x;
+  const int nst = nslot / CHXF_SLOTS;                                   // stages of one pass over the group's slots
+  const int GS = nst * ((np2 + 255) >> 8) * st2 * ((MT + 31) / 32);    // stages this CTA consumes
   if (tid < ntl) { sT[tid] = tiles[t0 + tid]; sU[tid] = prm.tile_u[t0 + tid]; }
   for (int q = tid; q < min(nslot, CHXF_SWB); q += 256) sWb[q] = (int)__ldg(prm.slot_wblk + slot0 + q);
-  if (tid == 0) {
-    cur.sweep = 0; cur.ab = 0; cur.k0 = 0; cur.tt = 0; cur.s = 0; cur.u = U0.x; cur.nu = U0.y; cur.done = 0; cur.p_stage = 0; cur.p_phase = 0;
-  }
-  // Two CTAs share an SM and alternate between a latency-bound phase 1 (no tensor work) and a phase 2 that saturates the DMMA
-  // pipe.  CTAs that start together stay in lock step (both wait for W, then both split the pipe), and so do their successors;
-  // an offset between the two is preserved just as well.  So the second CTA to arrive on each SM in the FIRST wave waits
-  // about one phase 2 (MT KS NTN DMMAs on 4 sub-partitions, 16 cycles each): from then on one CTA multiplies while the other
-  // fetches, for the rest of the launch.
-  if (tid == 0 && prm.sm_slot && (int)(blockIdx.x + gridDim.x * blockIdx.y) < 2 * prm.nsm) {
-    unsigned smid;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    if (atomicAdd(prm.sm_slot + smid, 1) & 1) {
-      const long long t_begin = clock64(), wait = (long long)MT * KS * NTN * 4;
-      while (clock64() - t_begin < wait) __nanosleep(200);
-    }
-  }
-  chxf_pipe_inline_init(pipe, bars);  // (block-wide barrier: the cursor and the tables are visible)
-  for (int q = 0; q < CHXF_STAGES - 1; q++) chxf_same_produce(prm, pipe, &cur, sU, sWb, slot0, ntl, e * nel + e, ring);
+  xf_trace(5, (unsigned long long)(ntl * 100000 + nslot));
+  chxf_pipe_inline_init(pipe, bars);  // (block-wide barrier: the tables are visible)
+  if (lane == 0 && warp < CHXF_STAGES - 1 && warp < GS) chxf_same_issue(prm, pipe, warp, nst, sWb, slot0, e * nel + e, ring);
 
   double acc[4][NTN][2];
 #pragma unroll
@@ -380,9 +360,10 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
       const int b = ab % st;
       const double sg = (ab / st == b) ? fac : -fac;
       __syncthreads();  // the previous product is done with the tile (first pass: the zero fill is complete)
+      xf_trace(1);
       // ---- phase 1: Bt[n][k] = sg sum_slots W^a_slot[k] coef^b[slot][n] ----
       for (int k0 = 0; k0 < np2; k0 += 256) {
-        chxf_phase1_inline<1>(prm, pipe, &cur, sU, sWb, slot0, ntl, e * nel + e, k0, b, ring, [&](int tt, double (&ra)[4][1][2]) {
+        chxf_phase1_inline<1>(prm, pipe, sU, sWb, slot0, nst, GS, ntl, e * nel + e, k0, b, ring, [&](int tt, double (&ra)[4][1][2]) {
           const int2 T = sT[tt];
           double* Bn = Bt + (T.x - it0 + 2 * t4) * LDK + k0 + 8 * warp + gid;  // rows outside the element are zero in W
           const bool ok0 = 2 * t4 < T.y, ok1 = 2 * t4 + 1 < T.y;
@@ -394,7 +375,9 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
             }
         });
       }
+      xf_trace(2);
       __syncthreads();
+      xf_trace(3);
       // ---- phase 2: C[np2 x NI] += teiK^{ab} [np2 x np2] . Bt ----
       const double* A = prm.teiK + ((((size_t)r * nel + e) * st2 + ab) * MT) * KS * 32 + lane;
       const double* bs = Bt + gid * LDK + t4;
@@ -430,6 +413,7 @@ __global__ void __launch_bounds__(256, 2) chan_xf_same_kernel(ChanXParams prm, c
 #pragma unroll
         for (int mi = 0; mi < 4; mi++) af[mi] = an[mi];
       }
+      xf_trace(4);
     }
 #pragma unroll
     for (int mi = 0; mi < 4; mi++) {
@@ -526,13 +510,14 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
 
     for (int a = 0; a < st; a++) {
       consumer_sync();  // the previous products are done with Rt (and with the previous unit's tables)
+      xf_trace(6);
       if (a == 0) {
         // this unit's disjoint factors iint^a (element ie), jint^b (element je): requested now, they land during phase 1
         const double* ib = (lower ? prm.big_f : prm.small_f) + ((size_t)r * nel + ie) * st * np2;
         const double* jb = (lower ? prm.small_f : prm.big_f) + ((size_t)r * nel + je) * st * np2;
-        for (int q = tid; q < 2 * st * np2; q += 256) {
-          const int which = q / np2, i = q - which * np2;
-          cp_async8(sI + which * TBL + i, (which < st ? ib + (size_t)which * np2 : jb + (size_t)(which - st) * np2) + i);
+        for (int q = tid; q < st * np2; q += 256) {  // both stack halves of a factor are one contiguous run
+          cp_async8(sI + q, ib + q);
+          cp_async8(sI + st * TBL + q, jb + q);
         }
         cp_async_commit();
       }
@@ -565,9 +550,11 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
         else chxf_consume<1>(prm, pipe, sU, ntl, k0, 0, ring, emit1);
       }
       if (a == 0) cp_async_wait_all();
+      xf_trace(7);
       consumer_sync();
+      xf_trace(8);
     // ---- phase 2: Ksub += iint^a . Rsub^{ab} . (jint^b)^T for the warp's items ----
-    const double* iint = sI + a * TBL;
+    const double* iint = sI + a * np2;
     double af[2 * NTL][NTL];
 #pragma unroll
     for (int ks = 0; ks < 2 * NTL; ks++) {
@@ -576,7 +563,7 @@ __global__ void __launch_bounds__(CHXF_THREADS, (NTL <= 2) ? 2 : 1) chan_xf_pair
       for (int mt = 0; mt < NTL; mt++) af[ks][mt] = (kk < np && 8 * mt + gid < np) ? iint[(8 * mt + gid) + kk * np] : 0.0;
     }
     for (int b = 0; b < st; b++) {
-      const double* jint = sI + (st + b) * TBL;
+      const double* jint = sI + st * TBL + b * np2;
       double jf[2 * NTL][NTL];
 #pragma unroll
       for (int ks = 0; ks < 2 * NTL; ks++) {
