@@ -940,7 +940,17 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
       if (rc) return rc;
       tick(3, false);
       tick(4, true);
-      chan_x4_kernel<<<(unsigned)std::min(B.nout, 148 * 8), 256, 0, st>>>(q, (const int*)dOutPtr.p + B.out0, (const int*)dOutItem.p, B.nout);
+      {
+        const size_t smem4 = (size_t)nrad * (nrad + 1) * sizeof(double);
+        static const bool x4_tiled = getenv("HFB200_X4_TILED") != nullptr;
+        if (!x4_tiled && prm.np2 <= 256 && smem4 <= 100 * 1024) {
+          HFB_CUDA_OK(cudaFuncSetAttribute(chan_x4_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem4, 48 * 1024)));
+          const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)220 * 1024 / (smem4 + 1024)));
+          chan_x4_smem_kernel<<<(unsigned)std::min(B.nout, nsm * per_sm), 256, smem4, st>>>(q, (const int*)dOutPtr.p + B.out0, (const int*)dOutItem.p, B.nout);
+        } else {
+          chan_x4_kernel<<<(unsigned)std::min(B.nout, 148 * 8), 256, 0, st>>>(q, (const int*)dOutPtr.p + B.out0, (const int*)dOutItem.p, B.nout);
+        }
+      }
       HFB_CUDA_OK(cudaGetLastError());
       tick(4, false);
     }

@@ -387,6 +387,59 @@ static __global__ void __launch_bounds__(256) chan_x4_kernel(ChanXParams prm, co
   }
 }
 
+// x4, shared-memory form (used when an (nrad x nrad) block fits): one CTA per output block at a time.  The items' sub-blocks are
+// read SUB-BLOCK BY SUB-BLOCK -- each is one contiguous run of np^2 doubles per item, so every 32-byte sector that is fetched is
+// used (the tiled form above cuts the runs at tile and element borders and fetched ~2x the algorithmic bytes, ncu r02s) -- summed
+// over the items in item order and added into the block held in shared memory (a boundary function belongs to two elements: the
+// sub-blocks overlap there, hence the barrier between sub-blocks and the fixed sub-block order); the finished block and, with
+// prm.sym, its transpose are then subtracted from K with coalesced accesses.  256 threads, dynamic smem nrad * (nrad + 1) doubles.
+static __global__ void __launch_bounds__(256) chan_x4_smem_kernel(ChanXParams prm, const int* out_ptr, const int* out_item, int nout) {
+  extern __shared__ double blk[];  // [nrad][nrad + 1]: entry (a, b) at a + b * (nrad + 1)
+  const int np = prm.np, np2 = prm.np2, nel = prm.nel, nel2 = nel * nel, nrad = prm.nrad, ldb = nrad + 1;
+  const int tid = threadIdx.x;
+  const size_t istride = (size_t)nel2 * np2;
+  const int li = tid % np, ll = tid / np;  // this thread's entry of a sub-block (np2 <= 256 is checked by the launcher)
+  for (int o = blockIdx.x; o < nout; o += gridDim.x) {
+    const int q0 = out_ptr[o], q1 = out_ptr[o + 1];
+    const int2 jk = prm.items[out_item[q0]];
+    const bool mirror = prm.sym && jk.x != jk.y;
+    for (int e = tid; e < nrad * ldb; e += 256) blk[e] = 0.0;
+    __syncthreads();
+    for (int pe = 0; pe < nel2; pe++) {
+      const int ie = pe / nel, je = pe % nel;
+      const int ni = prm.npe[ie], nj = prm.npe[je];
+      if (tid < np2 && li < ni && ll < nj) {
+        const double* B = prm.blocks + (size_t)pe * np2 + tid;
+        double s = 0.0;
+        int q = q0;
+        for (; q + 8 <= q1; q += 8) {  // eight items in flight, added in item order
+          double t[8];
+#pragma unroll
+          for (int u = 0; u < 8; u++) t[u] = __ldcs(B + (size_t)(out_item[q + u] - prm.item0) * istride);
+#pragma unroll
+          for (int u = 0; u < 8; u++) s += t[u];
+        }
+        for (; q < q1; q++) s += __ldcs(B + (size_t)(out_item[q] - prm.item0) * istride);
+        blk[(prm.first[ie] + li) + (prm.first[je] + ll) * ldb] += s;
+      }
+      __syncthreads();
+    }
+    double* Kjk = prm.K + (size_t)jk.x * nrad + (size_t)jk.y * nrad * prm.ldk;
+    for (int e = tid; e < nrad * nrad; e += 256) {
+      const int a = e % nrad, b = e / nrad;
+      Kjk[a + (size_t)b * prm.ldk] -= blk[a + b * ldb];
+    }
+    if (mirror) {
+      double* Kkj = prm.K + (size_t)jk.y * nrad + (size_t)jk.x * nrad * prm.ldk;
+      for (int e = tid; e < nrad * nrad; e += 256) {
+        const int b = e % nrad, a = e / nrad;  // K[k,j](b, a) = K[j,k](a, b): coalesced in b, conflict-free in shared memory (ldb odd or even + 1)
+        Kkj[b + (size_t)a * prm.ldk] -= blk[a + b * ldb];
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // Packed copies of a list of (nrad x nrad) angular blocks (j,k) of a dense matrix: the payload of the exchange all-reduce of a
 // sharded run.  grid (blocks), 256 threads.  mirror: also write block (k,j) = block(j,k)^T (symmetric operator, j <= k listed).
 static __global__ void __launch_bounds__(256) chan_blocks_gather_kernel(const double* M, int ld, int nrad, const int2* blk, double* packed) {
