@@ -786,14 +786,20 @@ def run_chan(args, w, rank, world, local_rank):
             e["algorithmic_bytes"] = nbytes
             e["gbs"] = nbytes / (msv * 1e-3) / 1e9 if msv > 0 else None
             e["frac_hbm"] = e["gbs"] / hbm_peak if e["gbs"] else None
-        e["traffic"] = ncu_traffic(args.workload, kernel)
+        tr = ncu_traffic(args.workload, kernel)
+        if isinstance(tr, dict):  # bytes of ONE captured launch (a build has one launch per family batch) and that launch's algorithmic bytes
+            e["traffic"] = tr["bytes"]
+            e["traffic_launch"] = tr["launch"]
+            e["traffic_over_algorithmic"] = tr["bytes"] / tr["algorithmic"]
+        else:
+            e["traffic"] = tr
         stages.append(e)
 
     add("mask", "chan_x0_mask_kernel", stage[0], "hbm", nbytes=float(n) * n * 8)
     add("x1_left_angular", "chan_x1_mma_kernel", stage[1], "hbm", nbytes=w_bytes + float(np.count_nonzero(np.asarray(b.mval)[:, None] == np.asarray(b.mval)[None, :])) * nrad * nrad * 8)
     add("xf_same_element", "chan_xf_same_kernel", stage[2], "tensor", flops=f_same, nbytes=w_bytes / nel + blocks_bytes / nel)
     add("xf_element_pairs", "chan_xf_pair_kernel", stage[3], "tensor", flops=f_pair, nbytes=w_bytes * (nel - 1) / nel + blocks_bytes * (nel - 1) / nel)
-    add("x4_assemble", "chan_x4_kernel", stage[4], "hbm", nbytes=blocks_bytes + float(cnt[6]) * nrad * nrad * 8 * (2 if cnt[8] else 1))
+    add("x4_assemble", "chan_x4_smem_kernel" if nrad * (nrad + 1) * 8 <= 100 * 1024 else "chan_x4_kernel", stage[4], "hbm", nbytes=blocks_bytes + float(cnt[6]) * nrad * nrad * 8 * (2 if cnt[8] else 1))
     add("coulomb (pack, pre, DMMA, post, unpack)", "chan_pre_kernel", ms_j, "hbm", nbytes=2.0 * n * n * 8)
     if sharded:
         stages.append({"stage": "nccl_allreduce_K (gather + all-reduce + scatter)", "ms": ms_ar, "payload_bytes": float(cnt[10]) * nrad * nrad * 8})
@@ -804,6 +810,8 @@ def run_chan(args, w, rank, world, local_rank):
                 "achieved": dom.get("tflops") if dom["bound"] == "tensor" else dom.get("gbs"),
                 "peak": FP64_TFLOPS_MEASURED if dom["bound"] == "tensor" else hbm_peak, "unit": "TFLOP/s" if dom["bound"] == "tensor" else "GB/s",
                 "frac": dom.get("frac_fp64") if dom["bound"] == "tensor" else dom.get("frac_hbm"), "traffic": dom["traffic"],
+                "traffic_note": ("ncu dram bytes of ONE launch of the kernel (%s); its algorithmic bytes are %.3g x smaller; achieved / ms_per_launch_sum "
+                                 "cover all launches of the build" % (dom.get("traffic_launch"), dom.get("traffic_over_algorithmic", float("nan")))) if dom.get("traffic_launch") else None,
                 "peak_source": "FP64: measured cuBLAS DGEMM (profiles/r01_fp64_peak.json; MEASURED_PEAKS.json has no FP64 entry; tcgen05 has no FP64 kind, "
                                "DMMA.8x8x4 is the FP64 tensor path); HBM: " + hbm_src,
                 "ms_per_launch_sum": dom["ms"], "stages": stages,
