@@ -7,7 +7,7 @@
 Default workload: BASELINE.json configs[3], the largest configuration that fits one GPU -- N2 Hartree-Fock in prolate
 spheroidal coordinates, lmax 24, mmax 6, 5 LIP-15 elements (19 552 basis functions, 585 integral families).  A *step* is ONE
 Fock build: coulomb(P) + exchange(P) (HF has no XC term) for an overlap-orthonormalised N2-like closed-shell density.
-`value` = builds/s with P, J, K resident in HBM (hfb200_chan_coulomb_device + hfb200_chan_exchange_device);
+`value` = builds/s with P, J, K resident in HBM (hfb200_chan_fock_device = coulomb + exchange of one build);
 `e2e`   = the same through the reference-facing host-matrix calls TwoDBasis::coulomb / TwoDBasis::exchange.
 N > 1:   STRONG scaling of that one build: every rank holds the integral families r % N == rank and the library all-reduces
          J (per-channel radial results) and K (packed non-zero angular blocks) over NCCL inside the timed region.
@@ -643,9 +643,11 @@ def run_chan(args, w, rank, world, local_rank):
     assert sh != 0
 
     def step(J=True, K=True):
-        if J:
+        if J and K:  # one Fock build: hfb200_chan_fock_device (the Coulomb kernels on a second stream next to the exchange pipeline)
+            b.fock_device(dP.data_ptr(), dJ.data_ptr(), dK.data_ptr(), n, sh)
+        elif J:
             b.coulomb_device(dP.data_ptr(), dJ.data_ptr(), n, sh)
-        if K:
+        elif K:
             b.exchange_device(dP.data_ptr(), dK.data_ptr(), n, sh)
 
     def barrier():

@@ -841,6 +841,27 @@ int ChanEngine::dense_apply(bool exchange, const double* P, int ldp, double* F, 
   return 0;
 }
 
+// J and K of one Fock build: the Coulomb kernels (short, bandwidth-bound, 2 % of the build at configs[3] but a fixed cost that does
+// not shrink with the number of ranks) run on a second stream of the engine next to the exchange pipeline (tensor-bound); the call
+// is ordered on `st` on both sides.  The two operators share no workspace (chan_engine.h); with a communicator their all-reduces
+// are issued in the same order on every rank (J first).
+int ChanEngine::fock_device(const double* dPm, int ldp, double* dJm, int ldj, double* dKm, int ldk, cudaStream_t st) {
+  if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
+  if (!st2) {
+    HFB_CUDA_OK(cudaStreamCreateWithFlags(&st2, cudaStreamNonBlocking));
+    HFB_CUDA_OK(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
+    HFB_CUDA_OK(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
+  }
+  int rc;
+  HFB_CUDA_OK(cudaEventRecord(evFork, st));
+  HFB_CUDA_OK(cudaStreamWaitEvent(st2, evFork, 0));
+  if ((rc = coulomb_device(dPm, ldp, dJm, ldj, st2))) return rc;
+  HFB_CUDA_OK(cudaEventRecord(evJoin, st2));
+  rc = exchange_device(dPm, ldp, dKm, ldk, st);
+  HFB_CUDA_OK(cudaStreamWaitEvent(st, evJoin, 0));
+  return rc;
+}
+
 int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ldkm, cudaStream_t st) {
   if (!have_k) { set_error("Primitive teis have not been computed!"); return HFB200_ENOTEI; }
   const int nel = prm.nel, np2 = prm.np2, nang = xprm.nang, ntot = nang * nrad, stack = prm.stack;
@@ -998,6 +1019,7 @@ void ChanEngine::release() {
   for (void* p : owned) cudaFree(p);
   owned.clear();
   for (DevBuf* b : {&dP, &dPc, &dTr, &dJc, &dJ, &dPdense, &dKdense, &dKblocks, &dW, &dRed, &dHdr}) b->release();
+  if (st2) { cudaStreamDestroy(st2); cudaEventDestroy(evFork); cudaEventDestroy(evJoin); st2 = nullptr; evFork = evJoin = nullptr; }
   for (DevList* L : {&dItems, &dItemFam, &dTiles2, &dGroupsS, &dGroupsP, &dTileU, &dSlotWblk, &dSlotCoef, &dWbase, &dWbits, &dOutPtr, &dOutItem, &dX1tab, &dRedBlocks, &dIoBlocks}) {
     if (L->p) cudaFree(L->p);
     L->p = nullptr;
@@ -1030,6 +1052,11 @@ int hfb200_chan_exchange_device(hfb200_ctx* c, const double* dP, int ldp, double
   if (!c || !c->chan || !dP || !dK) { hfb::set_error("hfb200_chan_exchange_device: invalid argument"); return HFB200_EINVAL; }
   HFB_CUDA_OK(cudaSetDevice(c->device));
   return c->chan->exchange_device(dP, ldp, dK, ldk, stream ? (cudaStream_t)stream : c->stream);
+}
+int hfb200_chan_fock_device(hfb200_ctx* c, const double* dP, int ldp, double* dJ, int ldj, double* dK, int ldk, void* stream) {
+  if (!c || !c->chan || !dP || !dJ || !dK) { hfb::set_error("hfb200_chan_fock_device: invalid argument"); return HFB200_EINVAL; }
+  HFB_CUDA_OK(cudaSetDevice(c->device));
+  return c->chan->fock_device(dP, ldp, dJ, ldj, dK, ldk, stream ? (cudaStream_t)stream : c->stream);
 }
 int hfb200_chan_exchange_stats(hfb200_ctx* c, long long* items, double* x3_flops, double* stage_ms) {
   if (!c || !c->chan) { hfb::set_error("hfb200_chan_exchange_stats: invalid argument"); return HFB200_EINVAL; }

@@ -90,6 +90,9 @@ struct ChanEngine {
   int build(const ChanSpec& spec, bool with_exchange);
   // dense HOST matrices; map (optional, length nang*nrad): operator index -> row/column of the caller's nout x nout
   // matrices, -1 = identically zero row (diatomic boundary functions, diatomic/basis.cpp:1735-1773)
+  int fock_device(const double* dP, int ldp, double* dJ, int ldj, double* dK, int ldk, cudaStream_t st);  // J and K of one build, J on a second stream
+  cudaStream_t st2 = nullptr;
+  cudaEvent_t evFork = nullptr, evJoin = nullptr;
   int dense_apply(bool exchange, const double* P, int ldp, double* F, int ldf, cudaStream_t st, const int* map = nullptr, int nout = 0);
   int coulomb_dense(const double* P, int ldp, double* J, int ldj, cudaStream_t st, const int* map = nullptr, int nout = 0) { return dense_apply(false, P, ldp, J, ldj, st, map, nout); }
   int exchange_dense(const double* P, int ldp, double* K, int ldk, cudaStream_t st, const int* map = nullptr, int nout = 0) { return dense_apply(true, P, ldp, K, ldk, st, map, nout); }

@@ -91,6 +91,11 @@ class DiatomicBasis:
         check(lib().hfb200_chan_exchange_device(self.context(), ctypes.c_void_p(dP), int(n), ctypes.c_void_p(dK), int(n),
                                                  ctypes.c_void_p(stream)))
 
+    def fock_device(self, dP, dJ, dK, n, stream=0):
+        """J and K of one Fock build from the same device-resident P (Coulomb kernels on a second stream next to the exchange pipeline)."""
+        check(lib().hfb200_chan_fock_device(self.context(), ctypes.c_void_p(dP), int(n), ctypes.c_void_p(dJ), int(n), ctypes.c_void_p(dK), int(n),
+                                             ctypes.c_void_p(stream)))
+
     def exchange_stats(self):
         items, fl, ms = ctypes.c_longlong(), ctypes.c_double(), (ctypes.c_double * 5)()
         check(lib().hfb200_chan_exchange_stats(self.context(), ctypes.byref(items), ctypes.byref(fl), ms))

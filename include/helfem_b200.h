@@ -193,6 +193,10 @@ int hfb200_diatomic_exchange(hfb200_ctx* ctx, const double* P, int ldp, double* 
 int hfb200_chan_dim(hfb200_ctx* ctx, int* ndim);
 int hfb200_chan_coulomb_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dJ, int ldj, void* stream);
 int hfb200_chan_exchange_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dK, int ldk, void* stream);
+/* J and K of ONE Fock build from the same device-resident P (no reference counterpart: the reference calls coulomb and exchange one after
+ * the other, diatomic/main.cpp SCF loop): the Coulomb kernels run on a second stream of the context next to the exchange pipeline; the
+ * call is ordered on `stream` on both sides.  Results are identical to the two separate calls. */
+int hfb200_chan_fock_device(hfb200_ctx* ctx, const double* dP, int ldp, double* dJ, int ldj, double* dK, int ldk, void* stream);
 int hfb200_chan_exchange_stats(hfb200_ctx* ctx, long long* items, double* x3_flops, double* stage_ms /* [5] or NULL */);
 /* sizes of the per-sparsity-pattern lists of the last exchange call (bench accounting): out[0] output blocks contracted (summed
  * over families), [1] tiles, [2] W sub-block slots read by the fused kernels, [3] the same padded to whole pipeline stages, [4] W blocks

@@ -164,6 +164,12 @@ def test_diatomic_midsize_properties(native):
     assert np.max(np.abs(Jd - J2)) <= 1e-12 * max(1.0, np.max(np.abs(J2)))
     items, flops, _ = b.exchange_stats()
     assert items > 0 and flops > 0
+    # J and K of one build in one call (Coulomb kernels on a second stream): bit-identical to the two separate calls, repeatedly
+    dJ2, dK2 = torch.full_like(dP, 7.0), torch.full_like(dP, -3.0)
+    for _ in range(3):
+        b.fock_device(dP.data_ptr(), dJ2.data_ptr(), dK2.data_ptr(), nd, st.cuda_stream)
+        st.synchronize()
+        assert torch.equal(dJ2, dJ) and torch.equal(dK2, dK)
 
 
 def test_diatomic_nonsymmetric_density_and_size_errors(native):
@@ -184,3 +190,17 @@ def test_diatomic_nonsymmetric_density_and_size_errors(native):
     rc = hb.lib().hfb200_diatomic_coulomb(b.context(), bad.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), n - 1,
                                            out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), n - 1)
     assert rc != 0 and b"expected size" in hb.lib().hfb200_last_error()
+
+
+@pytest.mark.parametrize("case", ["n2_l2m1", "n2_l5m2"])
+def test_diatomic_operators_are_run_to_run_deterministic(native, case):
+    """No float atomics anywhere on the path: every reduction (the mbarrier-pipelined fused kernels, the shared-memory assembly,
+    the CSR gathers) has a fixed order, so repeated calls return bit-identical matrices -- for the symmetric item list and for the
+    full one (a race in a shared-memory protocol would show up here as a run-to-run difference)."""
+    b, o, P = setup_case(case)
+    Pns = np.asfortranarray(P + 0.3 * np.triu(splitmix64(P.size, seed=77).reshape(P.shape), 1))
+    for dens in (P, Pns):
+        J0, K0 = b.coulomb(dens), b.exchange(dens)
+        for _ in range(3):
+            assert np.array_equal(b.coulomb(dens), J0)
+            assert np.array_equal(b.exchange(dens), K0)
