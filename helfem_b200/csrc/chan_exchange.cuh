@@ -248,6 +248,9 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
       const int* actl = actl_all + w * NA;
       const bool prev = done[l] != 0;
       const long long wb0 = wblk_all[w * CHX_T + 2 * t4], wb1 = wblk_all[w * CHX_T + 2 * t4 + 1];
+      const bool has0 = wb0 >= 0, has1 = wb1 >= 0;
+      double* const Wp0 = prm.W + (size_t)(has0 ? wb0 : 0) * st * WB + gid;  // this lane's rows 2 t4, 2 t4 + 1 of the tile, W index gid
+      double* const Wp1 = prm.W + (size_t)(has1 ? wb1 : 0) * st * WB + gid;
       for (int k0 = warp * 32; k0 < WB; k0 += 256) {
         const int kg = k0 + gid;
         unsigned so[4];  // element offsets inside the dense P fit 32 bits (ldp^2 < 2^32 is checked by the engine)
@@ -274,19 +277,34 @@ static __global__ void __launch_bounds__(256, 3) chan_x1_mma_kernel(ChanXParams 
             dmma(acc[mt][1][0], acc[mt][1][1], af[mt], b1);
           }
         }
+        // stores (streaming: W is far larger than L2 and is next read by the fused kernels).  wb < 0: l is not in the set of the row
+        // (its partners' blocks are all zero), nothing stored.  WB and k0 are multiples of 8, so the range test is warp-uniform.
+        if (!prev) {  // block-uniform: the common single-pass case, straight predicated stores
 #pragma unroll
-        for (int mt = 0; mt < 4; mt++) {
-          const int k = kg + 8 * mt;
-          if (k >= WB) continue;
+          for (int mt = 0; mt < 4; mt++) {
+            if (k0 + 8 * mt >= WB) break;
+            if (has0) {
+              __stcs(Wp0 + k0 + 8 * mt, acc[mt][0][0]);
+              if (st == 2) __stcs(Wp0 + k0 + 8 * mt + WB, acc[mt][1][0]);
+            }
+            if (has1) {
+              __stcs(Wp1 + k0 + 8 * mt, acc[mt][0][1]);
+              if (st == 2) __stcs(Wp1 + k0 + 8 * mt + WB, acc[mt][1][1]);
+            }
+          }
+        } else {
 #pragma unroll
-          for (int i = 0; i < 2; i++) {
-            const long long wb = i ? wb1 : wb0;
-            if (wb < 0) continue;  // l is not in the set of this row (its partners' blocks are all zero): nothing stored
-            double* W0 = prm.W + (size_t)wb * st * WB + k;
-            double v0 = acc[mt][0][i], v1 = acc[mt][1][i];
-            if (prev) { v0 += W0[0]; if (st == 2) v1 += W0[WB]; }
-            __stcs(W0, v0);  // streaming: W is far larger than L2 and is next read by the fused kernels
-            if (st == 2) __stcs(W0 + WB, v1);
+          for (int mt = 0; mt < 4; mt++) {
+            if (k0 + 8 * mt >= WB) break;
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+              if (!(i ? has1 : has0)) continue;
+              double* W0 = (i ? Wp1 : Wp0) + k0 + 8 * mt;
+              double v0 = acc[mt][0][i] + W0[0], v1 = acc[mt][1][i];
+              if (st == 2) v1 += W0[WB];
+              __stcs(W0, v0);
+              if (st == 2) __stcs(W0 + WB, v1);
+            }
           }
         }
       }
