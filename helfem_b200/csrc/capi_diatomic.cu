@@ -68,7 +68,14 @@ int hfb200_diatomic_create(hfb200_ctx** out, int device, int nang, const int* lv
   c->lval.assign(lval, lval + nang);
   c->mval.assign(mval, mval + nang);
   for (int e = 0; e < nel; e++) c->np_max = std::max(c->np_max, last[e] - first[e] + 1);
-  HFB_CUDA_OK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  {
+    const cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {  // do not leak the half-built context
+      set_error("cudaStreamCreateWithFlags failed: %s", cudaGetErrorString(e));
+      hfb200_destroy(c);
+      return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? HFB200_ENODEVICE : HFB200_ECUDA;
+    }
+  }
   *out = c;
   return HFB200_OK;
 }

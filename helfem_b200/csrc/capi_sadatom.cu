@@ -118,7 +118,14 @@ int hfb200_sadatom_create(hfb200_ctx** out, int device, int lmax, int nel, int n
     hfb200_destroy(c);
     return rc;
   }
-  HFB_CUDA_OK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  {
+    const cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {  // do not leak the half-built context
+      set_error("cudaStreamCreateWithFlags failed: %s", cudaGetErrorString(e));
+      hfb200_destroy(c);
+      return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? HFB200_ENODEVICE : HFB200_ECUDA;
+    }
+  }
   *out = c;
   return HFB200_OK;
 }

@@ -127,7 +127,10 @@ static __global__ void __launch_bounds__(256) chan_x0_flags_kernel(const double*
 // builds the UNION of the partners in shared memory (flags -> ballot scan -> slots) with a dense (slot x row)
 // coefficient table, and streams every input block ONCE for all its rows instead of once per row.
 constexpr int CHX_T = 8;      // rows j of an x1 tile / items (j, k_0..) of a tile of the fused kernels
-constexpr int CHX_UMAX = 64;  // union slots per pass
+#ifndef HFB_CHX_UMAX
+#define HFB_CHX_UMAX 64
+#endif
+constexpr int CHX_UMAX = HFB_CHX_UMAX;  // union slots per pass (a multiple of 4; -DHFB_CHX_UMAX=4 exercises the multi-pass accumulation, tools/gpu_umax_variant.sh)
 constexpr int CHX_LDC = 12;   // row stride of the DMMA coefficient tables: the 4 x 8 fragment read of a half-warp hits 32 distinct banks
 
 // slots for the flagged entries of dom[0..n): -1 = absent, 0 = present on entry; slot number on exit.  Warp 0 only.

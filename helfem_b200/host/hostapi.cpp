@@ -450,3 +450,12 @@ int hfh_diatomic_set_shard(void* h, int rank, int n) {
 }
 
 }  // extern "C"
+
+// ---- test hooks of the host-side block scan / zero fill (host/blockscan.h; CPU-only, tests/test_blockscan_cpu.py) ----
+#include "blockscan.h"
+extern "C" {
+void hfh_scan_nonzero_blocks(const double* M, int ld, int nang, const int* r0, const int* cnt, unsigned char* nz) {
+  hfb::scan_nonzero_blocks(&M, 1, ld, nang, r0, cnt, nz);
+}
+void hfh_zero_fill(double* M, int ld, int n) { hfb::zero_fill(M, ld, n); }
+}

@@ -204,3 +204,18 @@ def test_diatomic_operators_are_run_to_run_deterministic(native, case):
         for _ in range(3):
             assert np.array_equal(b.coulomb(dens), J0)
             assert np.array_equal(b.exchange(dens), K0)
+
+
+def test_diatomic_contexts_on_two_devices_in_one_process(native):
+    """Kernel attributes (dynamic shared memory opt-in) are per device: a second context on another GPU of the same process must
+    work as well as the first.  Skipped on a single-GPU box."""
+    import helfem_b200 as hb
+    if hb.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    b0, o, P = setup_case("n2_l2m1")
+    Z1, Z2, Rb, primbas, nnodes, nelem, lmax, mmax = CASES["n2_l2m1"]
+    b1 = hb.DiatomicBasis(Z1, Z2, Rb, nelem=nelem, nnodes=nnodes, primbas=primbas, lmax=lmax, mmax=mmax, device=1)
+    b1.compute_tei(True)
+    for b in (b1, b0, b1):
+        assert np.array_equal(b.exchange(P), b0.exchange(P))
+        assert np.array_equal(b.coulomb(P), b0.coulomb(P))
