@@ -59,6 +59,7 @@ struct G2DParams {
   const int2* outblk;      // [nout]
   double *Rq, *F, *VGT, *partial;
   unsigned char* nzR;      // [nspin][nel][npair]
+  int* clsnz;              // [nspin*nel][nD] some pair of the class has a non-zero radial density (product rule; zeroed per call)
   int nblk_p;  // blocks over angular points in stage B
   // product rule
   int nth, nph, nD, dmax;
@@ -92,7 +93,10 @@ __global__ void g2d_radial_density(G2DParams p) {
     }
   }
   nz = __syncthreads_or(nz);
-  if (threadIdx.x == 0) p.nzR[(size_t)(s * p.nel + e) * p.npair + ab] = nz ? 1 : 0;
+  if (threadIdx.x == 0) {
+    p.nzR[(size_t)(s * p.nel + e) * p.npair + ab] = nz ? 1 : 0;
+    if (nz && p.clsnz) atomicOr(p.clsnz + (s * p.nel + e) * p.nD + (p.mval[ab / p.nang] - p.mval[ab % p.nang] + p.dmax), 1);  // (a flag: order-independent)
+  }
   const int q = threadIdx.x;
   if (!nz) {  // block-uniform
     if (q < nq) {
@@ -133,13 +137,16 @@ __global__ void g2d_radial_density(G2DParams p) {
 // fields per (s, e): 0 Th_a Th_b R | 1 Th_a Th_b R' | 2 Th'_a Th_b R | 3 -m_a Th_a Th_b R | 4 Th_a Th_b R'' | 5 Th'_a Th'_b R
 // | 6 m_a m_b Th_a Th_b R.   grid (class, nel*nspin, theta chunks of G2D_TT), one thread per q.
 constexpr int G2D_TT = 4;
+constexpr int G2D_SEG = 4;  // the pairs of a class are dealt over (up to) this many thread rows: a serial loop over 6 400 pairs is latency-bound
 __host__ __device__ inline int g2d_nfa(int fam) { return fam >= xc::FAM_MGGA ? 7 : (fam >= xc::FAM_GGA ? 4 : 1); }
+// block (nqb, nseg <= G2D_SEG); dynamic smem (nseg - 1) * NF * G2D_TT * nqb doubles
 template <int FAM>
 __global__ void g2d_theta_density(G2DParams p) {
   constexpr int NF = FAM >= xc::FAM_MGGA ? 7 : (FAM >= xc::FAM_GGA ? 4 : 1);
-  const int d = blockIdx.x, se = blockIdx.y, t0 = blockIdx.z * G2D_TT, q = threadIdx.x;
-  const int nq = p.nq, nth = p.nth;
-  if (q >= nq) return;
+  extern __shared__ double sred[];
+  const int d = blockIdx.x, se = blockIdx.y, t0 = blockIdx.z * G2D_TT, q = threadIdx.x, seg = threadIdx.y;
+  const int nq = p.nq, nth = p.nth, nqb = blockDim.x, nseg = blockDim.y;
+  const bool live = q < nq;
   double acc[NF][G2D_TT];
 #pragma unroll
   for (int f = 0; f < NF; f++)
@@ -148,41 +155,54 @@ __global__ void g2d_theta_density(G2DParams p) {
   const unsigned char* nz = p.nzR + (size_t)se * p.npair;
   const double* Rb = p.Rq + ((size_t)se * 3) * p.npair * nq + q;
   const size_t rs = (size_t)p.npair * nq;
-  for (int i = p.cls_ptr[d]; i < p.cls_ptr[d + 1]; i++) {
-    const int2 ab = p.cls_pair[i];
-    const int pr = ab.x * p.nang + ab.y;
-    if (!nz[pr]) continue;  // block-uniform
-    const double R = Rb[(size_t)pr * nq];
-    double Rr = 0.0, Rrr = 0.0;
-    if (FAM >= xc::FAM_GGA) Rr = Rb[rs + (size_t)pr * nq];
-    if (FAM >= xc::FAM_MGGA) Rrr = Rb[2 * rs + (size_t)pr * nq];
-    const double ma = (double)p.mval[ab.x], mb = (double)p.mval[ab.y];
+  if (live && p.clsnz[se * p.nD + d])  // block-uniform: an m-diagonal density populates the Delta = 0 class only
+    for (int i = p.cls_ptr[d] + seg; i < p.cls_ptr[d + 1]; i += nseg) {
+      const int2 ab = p.cls_pair[i];
+      const int pr = ab.x * p.nang + ab.y;
+      if (!nz[pr]) continue;  // warp-uniform
+      const double R = Rb[(size_t)pr * nq];
+      double Rr = 0.0, Rrr = 0.0;
+      if (FAM >= xc::FAM_GGA) Rr = Rb[rs + (size_t)pr * nq];
+      if (FAM >= xc::FAM_MGGA) Rrr = Rb[2 * rs + (size_t)pr * nq];
+      const double ma = (double)p.mval[ab.x], mb = (double)p.mval[ab.y];
 #pragma unroll
-    for (int t = 0; t < G2D_TT; t++) {
-      if (t0 + t >= nth) break;
-      const double ta = __ldg(p.Th + (size_t)ab.x * nth + t0 + t), tb = __ldg(p.Th + (size_t)ab.y * nth + t0 + t);
-      const double tt = ta * tb;
-      acc[0][t] = fma(tt, R, acc[0][t]);
-      if (FAM >= xc::FAM_GGA) {
-        const double da = __ldg(p.DTh + (size_t)ab.x * nth + t0 + t);
-        acc[1][t] = fma(tt, Rr, acc[1][t]);
-        acc[2][t] = fma(da * tb, R, acc[2][t]);
-        acc[3][t] = fma(-ma * tt, R, acc[3][t]);
-        if (FAM >= xc::FAM_MGGA) {
-          const double db = __ldg(p.DTh + (size_t)ab.y * nth + t0 + t);
-          acc[4][t] = fma(tt, Rrr, acc[4][t]);
-          acc[5][t] = fma(da * db, R, acc[5][t]);
-          acc[6][t] = fma(ma * mb * tt, R, acc[6][t]);
+      for (int t = 0; t < G2D_TT; t++) {
+        if (t0 + t >= nth) break;
+        const double ta = __ldg(p.Th + (size_t)ab.x * nth + t0 + t), tb = __ldg(p.Th + (size_t)ab.y * nth + t0 + t);
+        const double tt = ta * tb;
+        acc[0][t] = fma(tt, R, acc[0][t]);
+        if (FAM >= xc::FAM_GGA) {
+          const double da = __ldg(p.DTh + (size_t)ab.x * nth + t0 + t);
+          acc[1][t] = fma(tt, Rr, acc[1][t]);
+          acc[2][t] = fma(da * tb, R, acc[2][t]);
+          acc[3][t] = fma(-ma * tt, R, acc[3][t]);
+          if (FAM >= xc::FAM_MGGA) {
+            const double db = __ldg(p.DTh + (size_t)ab.y * nth + t0 + t);
+            acc[4][t] = fma(tt, Rrr, acc[4][t]);
+            acc[5][t] = fma(da * db, R, acc[5][t]);
+            acc[6][t] = fma(ma * mb * tt, R, acc[6][t]);
+          }
         }
       }
     }
+  // fixed-order sum over the segments: rows 1 .. SEG-1 park their sums, row 0 adds them in order
+  if (seg > 0) {
+#pragma unroll
+    for (int f = 0; f < NF; f++)
+#pragma unroll
+      for (int t = 0; t < G2D_TT; t++) sred[(((size_t)(seg - 1) * NF + f) * G2D_TT + t) * nqb + q] = acc[f][t];
   }
+  __syncthreads();
+  if (seg != 0 || !live) return;
   // Aq[se][f][t][d][q]
 #pragma unroll
   for (int f = 0; f < NF; f++)
 #pragma unroll
-    for (int t = 0; t < G2D_TT; t++)
-      if (t0 + t < nth) p.Aq[((((size_t)se * NF + f) * nth + t0 + t) * p.nD + d) * nq + q] = acc[f][t];
+    for (int t = 0; t < G2D_TT; t++) {
+      double v = acc[f][t];
+      for (int s2 = 0; s2 < nseg - 1; s2++) v += sred[(((size_t)s2 * NF + f) * G2D_TT + t) * nqb + q];
+      if (t0 + t < nth) p.Aq[((((size_t)se * NF + f) * nth + t0 + t) * p.nD + d) * nq + q] = v;
+    }
 }
 
 // ---- B: densities at the points, XC, weighted potential fields ------------------------------------------------
@@ -324,14 +344,24 @@ __global__ void g2d_point_xc(G2DParams p) {
   }
 }
 
-__global__ void g2d_reduce_scalars(const double* partial, int n, double* out) {
-  // one thread per scalar, fixed order
-  const int i = threadIdx.x;
-  if (i < 3) {
-    double v = 0.0;
-    for (int k = 0; k < n; k++) v += partial[(size_t)k * 3 + i];
-    out[i] = v;
+__global__ void __launch_bounds__(256) g2d_reduce_scalars(const double* partial, int n, double* out) {
+  // fixed order (run-to-run deterministic): thread t sums the entries t, t + 256, ...; then a shared-memory tree
+  __shared__ double red[3][256];
+  const int t = threadIdx.x;
+  double v[3] = {0.0, 0.0, 0.0};
+  for (int k = t; k < n; k += 256)
+#pragma unroll
+    for (int i = 0; i < 3; i++) v[i] += partial[(size_t)k * 3 + i];
+#pragma unroll
+  for (int i = 0; i < 3; i++) red[i][t] = v[i];
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (t < w)
+#pragma unroll
+      for (int i = 0; i < 3; i++) red[i][t] += red[i][t + w];
+    __syncthreads();
   }
+  if (t < 3) out[t] = red[t][0];
 }
 
 // ---- C1: phi stage of the fields (product rule) -------------------------------------------------------------------
@@ -511,6 +541,8 @@ void Grid2D::release() {
   if (dOutBlk) { cudaFree(dOutBlk); dOutBlk = nullptr; }
   if (dChunks) { cudaFree(dChunks); dChunks = nullptr; }
   if (dNzR) { cudaFree(dNzR); dNzR = nullptr; }
+  if (dClsNz) { cudaFree(dClsNz); dClsNz = nullptr; }
+  clsnz_cap = 0;
   if (ev0) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); ev0 = ev1 = nullptr; }
   nzr_cap = 0;
   Pp.release(); Hp.release(); Rq.release(); F.release(); VGT.release(); partial.release(); scal.release(); Aq.release(); Fh.release();
@@ -752,6 +784,16 @@ int Grid2D::eval_fxc(int fam, int x_func, int c_func, int nspin, const double* P
   p.Rq = Rq.p; p.F = F.p; p.VGT = VGT.p; p.partial = partial.p; p.nzR = dNzR; p.nblk_p = nblk_p;
   p.nth = nth; p.nph = nph; p.nD = nD; p.dmax = dmax; p.Th = dTh; p.DTh = dDTh; p.cosT = dCosT; p.sinT = dSinT; p.mval = dM;
   p.cls_ptr = dClsPtr; p.cls_pair = dClsPair; p.chunks = dChunks; p.Aq = Aq.p; p.Fh = Fh.p;
+  if (product) {
+    if (!dClsNz || clsnz_cap < (size_t)nspin * nel * nD) {
+      if (dClsNz) cudaFree(dClsNz);
+      dClsNz = nullptr;
+      HFB_CUDA_OK(cudaMalloc(&dClsNz, (size_t)nspin * nel * nD * sizeof(int)));
+      clsnz_cap = (size_t)nspin * nel * nD;
+    }
+    HFB_CUDA_OK(cudaMemsetAsync(dClsNz, 0, (size_t)nspin * nel * nD * sizeof(int), st));
+  }
+  p.clsnz = product ? dClsNz : nullptr;
 
   const size_t smA = ((size_t)np_max * np_max + 2 * (size_t)np_max * nq) * sizeof(double);
   const size_t smD = (2 * (size_t)np_max * nq + 3 * (size_t)nq) * sizeof(double);
@@ -764,9 +806,18 @@ int Grid2D::eval_fxc(int fam, int x_func, int c_func, int nspin, const double* P
   const dim3 gB(nblk_p, nel), bB(nqb, PB);
   if (product) {
     const dim3 g1(nD, nel * nspin, (nth + G2D_TT - 1) / G2D_TT);
-    if (fam == xc::FAM_LDA) g2d_theta_density<xc::FAM_LDA><<<g1, nqb, 0, st>>>(p);
-    else if (fam == xc::FAM_GGA) g2d_theta_density<xc::FAM_GGA><<<g1, nqb, 0, st>>>(p);
-    else g2d_theta_density<xc::FAM_MGGA><<<g1, nqb, 0, st>>>(p);
+    const dim3 b1(nqb, std::max(1, std::min(G2D_SEG, 1024 / nqb)));
+    const size_t sm1 = (size_t)(b1.y - 1) * nfa * G2D_TT * nqb * sizeof(double);
+    if (fam == xc::FAM_LDA) {
+      HFB_CUDA_OK(cudaFuncSetAttribute(g2d_theta_density<xc::FAM_LDA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(sm1, 1024)));
+      g2d_theta_density<xc::FAM_LDA><<<g1, b1, sm1, st>>>(p);
+    } else if (fam == xc::FAM_GGA) {
+      HFB_CUDA_OK(cudaFuncSetAttribute(g2d_theta_density<xc::FAM_GGA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(sm1, 1024)));
+      g2d_theta_density<xc::FAM_GGA><<<g1, b1, sm1, st>>>(p);
+    } else {
+      HFB_CUDA_OK(cudaFuncSetAttribute(g2d_theta_density<xc::FAM_MGGA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(sm1, 1024)));
+      g2d_theta_density<xc::FAM_MGGA><<<g1, b1, sm1, st>>>(p);
+    }
     HFB_CUDA_OK(cudaGetLastError());
     launches++;
     if (fam == xc::FAM_LDA) launch_point<xc::FAM_LDA, true>(nspin, gB, bB, st, p);
@@ -778,7 +829,7 @@ int Grid2D::eval_fxc(int fam, int x_func, int c_func, int nspin, const double* P
     else launch_point<xc::FAM_MGGA, false>(nspin, gB, bB, st, p);
   }
   HFB_CUDA_OK(cudaGetLastError());
-  g2d_reduce_scalars<<<1, 32, 0, st>>>(partial.p, nel * nblk_p, scal.p);
+  g2d_reduce_scalars<<<1, 256, 0, st>>>(partial.p, nel * nblk_p, scal.p);
   HFB_CUDA_OK(cudaGetLastError());
   launches += 2;
   if (nout) {

@@ -38,6 +38,8 @@ struct Grid2D {
   int4* dChunks = nullptr;                   // [npair] stage C2 work: (class, first slot, count, -)
   unsigned char* dNzR = nullptr;             // [nspin][nel][npair] the radial density of the pair is non-zero
   size_t nzr_cap = 0;
+  int* dClsNz = nullptr;                     // [nspin*nel][nD] class has a non-zero pair (product rule)
+  size_t clsnz_cap = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the kernels of the last eval_fxc
   float device_ms = 0.f;
   double h2d_bytes = 0.0, d2h_bytes = 0.0;    // packed payload of the last eval_fxc
