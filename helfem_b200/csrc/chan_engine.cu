@@ -309,9 +309,10 @@ int ChanEngine::build_exchange(const ChanSpec& S) {
   }
   {
     unsigned char* p = nullptr;
-    HFB_CUDA_OK(cudaMalloc(&p, (size_t)nang * nang + 8));  // + the symmetry flag of P
+    HFB_CUDA_OK(cudaMalloc(&p, 2 * ((size_t)nang * nang + 8)));  // + the symmetry flag of P; second half: exact non-zero flags
     owned.push_back(p);
     dNzP = p;
+    dNzX = p + (size_t)nang * nang + 8;
     if (hNzP) cudaFreeHost(hNzP);
     HFB_CUDA_OK(cudaMallocHost(&hNzP, (size_t)nang * nang + 8));
   }
@@ -686,7 +687,7 @@ int ChanEngine::coulomb_kernels(int nang, cudaStream_t st) {
   return 0;
 }
 
-int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st) {
+int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st, const unsigned char* nzx) {
   const int nel = prm.nel, np2 = prm.np2, nang = (int)std::lround(std::sqrt((double)npair));
   const size_t nband = (size_t)npair * nel * np2;
   const int KP = 4 * prm.KS, MP = 8 * prm.MT;
@@ -695,7 +696,7 @@ int ChanEngine::coulomb_device(const double* dPm, int ldp, double* dJm, int ldj,
       (rc = dTr.reserve((size_t)nchan * nel * 2)) || (rc = dJc.reserve((size_t)nchan * nel * MP)))
     return rc;
   HFB_CUDA_OK(cudaMemsetAsync(dPnz, 0, (size_t)npair, st));
-  chan_band_pack_kernel<<<dim3(nel * npair), 128, 0, st>>>(prm, dFirstJ, dNpeJ, nang, nrad, dPm, ldp, dP.p, dPnz);
+  chan_band_pack_kernel<<<dim3(nel * npair), 128, 0, st>>>(prm, dFirstJ, dNpeJ, nang, nrad, dPm, ldp, dP.p, dPnz, nzx);
   HFB_CUDA_OK(cudaGetLastError());
   if ((rc = coulomb_kernels(nang, st))) return rc;
   chan_band_unpack_kernel<<<(unsigned)npair, 256, 0, st>>>(prm, dFirstJ, dElemOfJ, nang, nrad, dJ.p, dJm, ldj, dOnz);
@@ -852,13 +853,21 @@ int ChanEngine::fock_device(const double* dPm, int ldp, double* dJm, int ldj, do
     HFB_CUDA_OK(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
     HFB_CUDA_OK(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
   }
-  int rc;
-  HFB_CUDA_OK(cudaEventRecord(evFork, st));
-  HFB_CUDA_OK(cudaStreamWaitEvent(st2, evFork, 0));
-  if ((rc = coulomb_device(dPm, ldp, dJm, ldj, st2))) return rc;
-  HFB_CUDA_OK(cudaEventRecord(evJoin, st2));
-  rc = exchange_device(dPm, ldp, dKm, ldk, st);
-  HFB_CUDA_OK(cudaStreamWaitEvent(st, evJoin, 0));
+  // the exchange pipeline computes the block mask of P first; the Coulomb kernels fork off once it exists and use its exact
+  // non-zero flags to skip the zero blocks in their pack pass (1 777 of 80 089 blocks survive for an N2 density)
+  bool forked = false;
+  on_mask_ready = [&]() -> int {
+    HFB_CUDA_OK(cudaEventRecord(evFork, st));
+    HFB_CUDA_OK(cudaStreamWaitEvent(st2, evFork, 0));
+    const int rc_ = coulomb_device(dPm, ldp, dJm, ldj, st2, dNzX);
+    if (rc_) return rc_;
+    HFB_CUDA_OK(cudaEventRecord(evJoin, st2));
+    forked = true;
+    return 0;
+  };
+  const int rc = exchange_device(dPm, ldp, dKm, ldk, st);
+  on_mask_ready = nullptr;
+  if (forked) HFB_CUDA_OK(cudaStreamWaitEvent(st, evJoin, 0));
   return rc;
 }
 
@@ -882,17 +891,20 @@ int ChanEngine::exchange_device(const double* dPm, int ldpm, double* dKm, int ld
   tick(0, true);
   if (comm && comm_size > 1) {  // every rank scans its share of the blocks; the flags are summed over the ranks
     if ((rc = dHdr.reserve(2 * nang2 + 2))) return rc;
-    HFB_CUDA_OK(cudaMemsetAsync(dHdr.p, 0, (nang2 + 1) * sizeof(double), st));
+    HFB_CUDA_OK(cudaMemsetAsync(dHdr.p, 0, (2 * nang2 + 1) * sizeof(double), st));
     chan_x0_mask_kernel<<<(unsigned)((nang2 + comm_size - 1) / comm_size), 128, 0, st>>>(dPm, ldpm, nrad, nang, nullptr, nullptr, comm_rank, comm_size, dHdr.p);
     HFB_CUDA_OK(cudaGetLastError());
-    if ((rc = comm_allreduce_sum(comm, dHdr.p, nang2 + 1, st))) return rc;
-    chan_x0_flags_kernel<<<(unsigned)((nang2 + 1 + 255) / 256), 256, 0, st>>>(dHdr.p, (int)nang2, dNzP, allow_sym ? 1 : 0);
+    if ((rc = comm_allreduce_sum(comm, dHdr.p, 2 * nang2 + 1, st))) return rc;
+    chan_x0_flags_kernel<<<(unsigned)((nang2 + 1 + 255) / 256), 256, 0, st>>>(dHdr.p, (int)nang2, dNzP, allow_sym ? 1 : 0, dNzX);
   } else {
     HFB_CUDA_OK(cudaMemsetAsync(dNzP + nang2, allow_sym ? 1 : 0, 1, st));
-    chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP, allow_sym ? dNzP + nang2 : nullptr);
+    chan_x0_mask_kernel<<<(unsigned)nang2, 128, 0, st>>>(dPm, ldpm, nrad, nang, dNzP, allow_sym ? dNzP + nang2 : nullptr, 0, 1, nullptr, dNzX);
   }
   tick(0, false);
   HFB_CUDA_OK(cudaGetLastError());
+  if (on_mask_ready) {  // fock_device: the Coulomb part of the same build starts here, with the exact block mask (dNzX) in hand
+    if ((rc = on_mask_ready())) return rc;
+  }
   HFB_CUDA_OK(cudaMemcpyAsync(hNzP, dNzP, nang2 + 1, cudaMemcpyDeviceToHost, st));
   HFB_CUDA_OK(cudaStreamSynchronize(st));
   if (mask_cached.size() != nang2 + 1 || memcmp(mask_cached.data(), hNzP, nang2 + 1) != 0) {

@@ -99,7 +99,9 @@ struct ChanEngine {
   DevList dIoBlocks;                // block list of the host-matrix calls (input blocks, then output blocks)
   PinBuf hX;
   // device-resident variants: dense (nang*nrad)^2 matrices already in HBM; every kernel of the operator, no PCIe
-  int coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st);
+  int coulomb_device(const double* dPm, int ldp, double* dJm, int ldj, cudaStream_t st, const unsigned char* nzx = nullptr);  // nzx: exact block mask of P
+  std::function<int()> on_mask_ready;  // fock_device: called by exchange_device once the block mask of P is on the device
+  unsigned char* dNzX = nullptr;       // [nang^2] the block of P has an entry that is not exactly zero (filled with the mask)
   int exchange_device(const double* dPm, int ldp, double* dKm, int ldk, cudaStream_t st);
   int coulomb_kernels(int nang, cudaStream_t st);
   const int *dFirstJ = nullptr, *dNpeJ = nullptr, *dElemOfJ = nullptr;

@@ -80,8 +80,12 @@ struct ChanXParams {
 // sym_flag: one byte, preset to 1, cleared on the first mismatch.
 // Sharded run (nranks > 1): rank r scans the blocks b = r, r + nranks, ... and writes 0 / 1 (and a mismatch mark at [nang^2]) into the
 // zeroed double array flagsD, which the engine all-reduces and chan_x0_flags_kernel turns back into the byte mask.
+// nzx (optional, single rank) / flagsD[nang^2 + 1 ...] (sharded): the block has an entry that is not exactly zero -- the Coulomb pack
+// of the same Fock build skips the others (exact; the norm mask above may also drop tiny non-zero blocks, as the reference's
+// exchange does and its coulomb does not).
 static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* P, int ldp, int nrad, int nang, unsigned char* nz,
-                                                                  unsigned char* sym_flag, int rank = 0, int nranks = 1, double* flagsD = nullptr) {
+                                                                  unsigned char* sym_flag, int rank = 0, int nranks = 1, double* flagsD = nullptr,
+                                                                  unsigned char* nzx = nullptr) {
   __shared__ double red[4];
   __shared__ int s_nz;
   const int blk_id = blockIdx.x * nranks + rank;
@@ -89,9 +93,16 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
   const int i = blk_id / nang, l = blk_id % nang;
   const double* blk = P + (size_t)i * nrad + (size_t)l * nrad * ldp;
   double s = 0.0;
+  int any = 0;
   for (int k = threadIdx.x; k < nrad * nrad; k += blockDim.x) {
     const double v = blk[(k % nrad) + (size_t)(k / nrad) * ldp];
     s = fma(v, v, s);
+    any |= (v != 0.0);
+  }
+  any = __syncthreads_or(any);
+  if (threadIdx.x == 0) {
+    if (flagsD) flagsD[nang * nang + 1 + blk_id] = any ? 1.0 : 0.0;
+    else if (nzx) nzx[blk_id] = any ? 1 : 0;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -117,10 +128,12 @@ static __global__ void __launch_bounds__(128) chan_x0_mask_kernel(const double* 
     else *sym_flag = 0;
   }
 }
-static __global__ void __launch_bounds__(256) chan_x0_flags_kernel(const double* flagsD, int n, unsigned char* nz, int allow_sym) {
+static __global__ void __launch_bounds__(256) chan_x0_flags_kernel(const double* flagsD, int n, unsigned char* nz, int allow_sym, unsigned char* nzx) {
   const int q = blockIdx.x * 256 + threadIdx.x;
-  if (q < n) nz[q] = flagsD[q] != 0.0 ? 1 : 0;
-  else if (q == n) nz[n] = (allow_sym && flagsD[n] == 0.0) ? 1 : 0;
+  if (q < n) {
+    nz[q] = flagsD[q] != 0.0 ? 1 : 0;
+    nzx[q] = flagsD[n + 1 + q] != 0.0 ? 1 : 0;
+  } else if (q == n) nz[n] = (allow_sym && flagsD[n] == 0.0) ? 1 : 0;
 }
 
 // Tiling of the two angular contractions: a CTA owns up to CHX_T rows that share their coupled partners (same m),

@@ -418,8 +418,10 @@ static __global__ void __launch_bounds__(256) chan_post_kernel(ChanParams prm) {
 // Device-resident operator calls: gather the element-diagonal band of every angular pair out of a dense matrix,
 // grid (nel * npair), and the inverse (a radial index pair lies in at most two common elements), grid-stride.
 static __global__ void __launch_bounds__(128) chan_band_pack_kernel(ChanParams prm, const int* first, const int* npe, int nang, int nrad,
-                                                                    const double* D, int ld, double* band, unsigned char* pnz) {
+                                                                    const double* D, int ld, double* band, unsigned char* pnz,
+                                                                    const unsigned char* nzx = nullptr) {
   const int el = blockIdx.x % prm.nel, pr = blockIdx.x / prm.nel, k = pr / nang, l = pr % nang;
+  if (nzx && !nzx[pr]) return;  // the whole angular block of D is exactly zero (mask of the same build): pnz stays clear, the band is never read
   const int f = first[el], n = npe[el], np = prm.np;
   double* dst = band + ((size_t)pr * prm.nel + el) * prm.np2;
   int any = 0;
