@@ -10,6 +10,7 @@
 #include "../host/angular.h"
 #include "chan_engine.h"
 #include "context.h"
+#include "../host/famshard.h"
 
 using namespace hfb;
 
@@ -80,7 +81,13 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.ang_m = c->mval;
   S.fam_owned.resize(nL);
-  for (int L = 0; L < nL; L++) S.fam_owned[L] = (L % c->shard_n == c->shard_rank);  // couplings of ALL families are listed below
+  {
+    std::vector<int> famL(nL), famM(nL, -1);
+    for (int L = 0; L < nL; L++) famL[L] = L;
+    c->fam_owner = family_owner(c->lval, c->mval, famL, famM, 0, c->shard_n);
+  }
+  const std::vector<int> own = c->fam_owner;
+  for (int L = 0; L < nL; L++) S.fam_owned[L] = (own[L] == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nL);
   for (int L = 0; L < nL; L++) S.fac[L] = 4.0 * M_PI / (2 * L + 1);
   // channels (L, M), sorted by L (atomic/TwoDBasis.cpp:836-842)
@@ -104,12 +111,12 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
       }
     }
   const int nel = c->nel;
-  const int sr = c->shard_rank, sn = c->shard_n;
+  const int sr = c->shard_rank;
   typedef const double* cptr;
-  S.tei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return r % sn == sr ? prim_tei[r * nel + e] : (cptr) nullptr; };
-  if (prim_ktei) S.ktei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return r % sn == sr ? prim_ktei[r * nel + e] : (cptr) nullptr; };
-  S.small_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return r % sn == sr ? disjoint_L[r * nel + e] : (cptr) nullptr; };
-  S.big_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return r % sn == sr ? disjoint_m1L[r * nel + e] : (cptr) nullptr; };
+  S.tei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return own[r] == sr ? prim_tei[r * nel + e] : (cptr) nullptr; };
+  if (prim_ktei) S.ktei = [=](int r, int e, int, int, double* sg) { *sg = 1.0; return own[r] == sr ? prim_ktei[r * nel + e] : (cptr) nullptr; };
+  S.small_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return own[r] == sr ? disjoint_L[r * nel + e] : (cptr) nullptr; };
+  S.big_f = [=](int r, int e, int, double* sg) { *sg = 1.0; return own[r] == sr ? disjoint_m1L[r * nel + e] : (cptr) nullptr; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
   c->chan->comm = c->comm;

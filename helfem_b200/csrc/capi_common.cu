@@ -43,14 +43,20 @@ int hfb200_device_count(void) {
 }
 
 /* Multi-GPU sharding of the atomic / diatomic operators: this context only holds and contracts the
- * integral families r with r % nranks == rank (atomic: r = L; diatomic: r = index of (L,|M|)); the
- * results of the ranks add up to the full J / K (the caller all-reduces them, NCCL over NVLink).
- * Must be called before *_set_tei. */
+ * integral families the cost-balanced map of host/famshard.h gives to `rank` (atomic: r = L; diatomic:
+ * r = index of (L,|M|)); the results of the ranks add up to the full J / K (all-reduced inside the library
+ * once a communicator is attached, comm.cu).  Must be called before *_set_tei. */
 int hfb200_set_shard(hfb200_ctx* c, int rank, int nranks) {
   if (!c || nranks < 1 || rank < 0 || rank >= nranks) { hfb::set_error("hfb200_set_shard: invalid argument"); return HFB200_EINVAL; }
   if (c->chan) { hfb::set_error("hfb200_set_shard must precede set_tei"); return HFB200_EINVAL; }
   c->shard_rank = rank;
   c->shard_n = nranks;
+  return HFB200_OK;
+}
+
+int hfb200_shard_owner(hfb200_ctx* c, int* owner, int n) {
+  if (!c || !owner || n < 0 || (size_t)n > c->fam_owner.size()) { hfb::set_error("hfb200_shard_owner: invalid argument (call after *_set_tei; n <= number of families)"); return HFB200_EINVAL; }
+  for (int r = 0; r < n; r++) owner[r] = c->fam_owner[r];
   return HFB200_OK;
 }
 

@@ -14,6 +14,7 @@
 #include "../host/angular.h"
 #include "chan_engine.h"
 #include "context.h"
+#include "../host/famshard.h"
 
 using namespace hfb;
 
@@ -101,7 +102,9 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.ang_m = c->mval;
   S.fam_owned.resize(nlm);
-  for (int r = 0; r < nlm; r++) S.fam_owned[r] = (r % c->shard_n == c->shard_rank);  // couplings of ALL families are listed below
+  c->fam_owner = family_owner(c->lval, c->mval, std::vector<int>(Lmap, Lmap + nlm), std::vector<int>(Mmap, Mmap + nlm), 2, c->shard_n);
+  const std::vector<int> own = c->fam_owner;
+  for (int r = 0; r < nlm; r++) S.fam_owned[r] = (own[r] == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nlm);
   for (int r = 0; r < nlm; r++) {
     // LMfac = 4 pi Rh^5 (-1)^M (L-|M|)!/(L+|M|)!   (basis.cpp:1421)
@@ -146,12 +149,12 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
       }
     }
   // stacked integrals: fac [[T00, -T02], [-T20, T22]],  s = fac [P0; -P2],  b = [Q0; -Q2]
-  const int sr = c->shard_rank, sn = c->shard_n;
+  const int sr = c->shard_rank;
   typedef const double* cptr;
-  S.tei = [=](int r, int e, int ho, int hi, double* sg) { *sg = (ho != hi) ? -1.0 : 1.0; return r % sn == sr ? prim_tei[4 * (r * nel + e) + 2 * ho + hi] : (cptr) nullptr; };
-  if (prim_ktei) S.ktei = [=](int r, int e, int a, int b, double* sg) { *sg = 1.0; return r % sn == sr ? prim_ktei[4 * (r * nel + e) + 2 * a + b] : (cptr) nullptr; };
-  S.small_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return r % sn != sr ? (cptr) nullptr : h ? P2[r * nel + e] : P0[r * nel + e]; };
-  S.big_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return r % sn != sr ? (cptr) nullptr : h ? Q2[r * nel + e] : Q0[r * nel + e]; };
+  S.tei = [=](int r, int e, int ho, int hi, double* sg) { *sg = (ho != hi) ? -1.0 : 1.0; return own[r] == sr ? prim_tei[4 * (r * nel + e) + 2 * ho + hi] : (cptr) nullptr; };
+  if (prim_ktei) S.ktei = [=](int r, int e, int a, int b, double* sg) { *sg = 1.0; return own[r] == sr ? prim_ktei[4 * (r * nel + e) + 2 * a + b] : (cptr) nullptr; };
+  S.small_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return own[r] != sr ? (cptr) nullptr : h ? P2[r * nel + e] : P0[r * nel + e]; };
+  S.big_f = [=](int r, int e, int h, double* sg) { *sg = h ? -1.0 : 1.0; return own[r] != sr ? (cptr) nullptr : h ? Q2[r * nel + e] : Q0[r * nel + e]; };
   if (c->chan) { c->chan->release(); delete c->chan; }
   c->chan = new ChanEngine();
   c->chan->comm = c->comm;

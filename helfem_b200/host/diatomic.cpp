@@ -1,5 +1,6 @@
 // Host-side mirror of the reference's `diatomic` operator class (see diatomic.h).
 #include "diatomic.h"
+#include "famshard.h"
 
 #include <algorithm>
 #include <cmath>
@@ -211,12 +212,18 @@ void TwoDBasis::compute_tei(bool exchange) {
   for (int w = 0; w < 4; w++) disjoint[w].assign(Nel * nlm, Mat());
   prim_tei.assign(4 * Nel * nlm, Mat());
   prim_ktei.assign(exchange ? 4 * Nel * nlm : 0, Mat());
+  std::vector<int> own(nlm, 0);
+  if (owned_only) {  // the same cost-balanced map the C ABI derives (host/famshard.h)
+    std::vector<int> fL(nlm), fM(nlm);
+    for (size_t q = 0; q < nlm; q++) { fL[q] = lm_map[q].first; fM[q] = lm_map[q].second; }
+    own = family_owner(lval, mval, fL, fM, 2, shard_n);
+  }
 #ifdef _OPENMP
 #pragma omp parallel for collapse(2) schedule(dynamic)
 #endif
   for (size_t ilm = 0; ilm < nlm; ilm++)
     for (size_t iel = 0; iel < Nel; iel++) {
-      if (owned_only && (int)(ilm % (size_t)shard_n) != shard_rank) continue;  // family held by another rank
+      if (owned_only && own[ilm] != shard_rank) continue;  // family held by another rank
       const int L = lm_map[ilm].first, M = lm_map[ilm].second;
       const size_t idx = ilm * Nel + iel;
       disjoint[0][idx] = radial.Plm_integral(0, iel, L, M);

@@ -76,10 +76,15 @@ int hfb200_sadatom_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoin
                            const double* const* prim_ktei);
 void hfb200_destroy(hfb200_ctx* ctx);
 /* Multi-GPU sharding of the atomic / diatomic operators (one process per GPU): the context only holds and
- * contracts the integral families r with r % nranks == rank (atomic: r = L; diatomic: r = index of
- * (L,|M|) in lm_map); the partial J / K of the ranks add up to the full operator and are all-reduced by
- * the caller (NCCL over NVLink).  Call before *_set_tei. */
+ * contracts the integral families r (atomic: r = L; diatomic: r = index of (L,|M|) in lm_map) that the
+ * cost-balanced map of helfem_b200/host/famshard.h gives to `rank`: the families are dealt to the ranks by
+ * predicted exchange cost, longest first, identically on every rank.  *_set_tei reads the stored integrals of
+ * the owned families only (hfb200_shard_owner tells which; the other pointers may be NULL).  The partial J / K
+ * of the ranks add up to the full operator; they are all-reduced inside the library once a communicator is
+ * attached (below), else by the caller.  Call before *_set_tei. */
 int hfb200_set_shard(hfb200_ctx* ctx, int rank, int nranks);
+/* owner[r] = rank holding family r, for r < n (valid after *_set_tei) */
+int hfb200_shard_owner(hfb200_ctx* ctx, int* owner, int n);
 
 /* NCCL communicator of a sharded context (one process per GPU, like `mpirun`-style SPMD drivers; the reference's own drivers
  * are single-process, diatomic/main.cpp:810-828).  Rank 0 obtains an id with hfb200_comm_unique_id (HFB200_COMM_ID_BYTES
