@@ -9,7 +9,7 @@ spheroidal coordinates, lmax 24, mmax 6, 5 LIP-15 elements (19 552 basis functio
 Fock build: coulomb(P) + exchange(P) (HF has no XC term) for an overlap-orthonormalised N2-like closed-shell density.
 `value` = builds/s with P, J, K resident in HBM (hfb200_chan_fock_device = coulomb + exchange of one build);
 `e2e`   = the same through the reference-facing host-matrix calls TwoDBasis::coulomb / TwoDBasis::exchange.
-N > 1:   STRONG scaling of that one build: every rank holds its cost-balanced share of the integral families (host/famshard.h) and the library all-reduces
+N > 1:   STRONG scaling of that one build: every rank holds the integral families r % N == rank and the library all-reduces
          J (per-channel radial results) and K (packed non-zero angular blocks) over NCCL inside the timed region.
 `roofline` carries every stage of the build with its algorithmic flops / bytes, the dominant kernel on top.
 `cpu_baseline` / `--impl reference`: the CPU port of the reference loops on a uniform SAMPLE of output blocks, scaled to
@@ -613,7 +613,7 @@ def run_chan(args, w, rank, world, local_rank):
     kind = w["kind"]
     t0 = time.perf_counter()
     b = make_chan_basis(w, device=local_rank)
-    # N > 1: STRONG scaling of one build.  This rank holds its cost-balanced share of the integral families (hfb200_set_shard); the library all-reduces
+    # N > 1: STRONG scaling of one build.  The integral families r % world == rank live on this rank; the library all-reduces
     # J (per-channel radial results) and K (packed non-zero angular blocks) over NCCL inside the timed region.
     sharded = world > 1 and not args.replicas
     if sharded:
@@ -829,7 +829,7 @@ def run_chan(args, w, rank, world, local_rank):
             "config": {"workload": args.workload, "desc": w["desc"], "operators": "coulomb + exchange (HF)", "ndim": n, "nbf": nb,
                        "nang": int(b.nang), "nrad": int(b.nrad),
                        "l2": "dense P/J/K = %.0f MB per build, W = %.1f GB%s" % (3 * n * n * 8 / 1e6, w_bytes / 1e9, "" if 3 * n * n * 8 > 126e6 else " (fits L2: launch-bound regime)"),
-                       "partition": ("one build by all %d ranks: integral families dealt by predicted cost (host/famshard.h), NCCL all-reduce of J (channel results) and K (packed blocks) "
+                       "partition": ("one build by all ranks: integral families r %% %d == rank, NCCL all-reduce of J (channel results) and K (packed blocks) "
                                      "inside the library and inside the timed region" % world if sharded
                                      else "independent builds per rank, no data-path collective" if world > 1 else "one GPU"),
                        "setup_s": {"compute_tei_host": t_tei, "upload": t_upload, "first_build": t_first}},

@@ -108,7 +108,7 @@ class AtomicBasis:
         check(lib().hfb200_chan_set_profile(self.context(), int(bool(on))))
 
     def set_shard(self, rank, nranks):
-        """Multi-GPU: contract only the integral families that the cost-balanced map (shard.family_owners) gives to `rank` (before the first operator call)."""
+        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call)."""
         check_host(lib().hfh_atomic_set_shard(self._h, int(rank), int(nranks)))
 
     def exchange_counts(self):

@@ -81,11 +81,7 @@ int hfb200_atomic_set_tei(hfb200_ctx* c, int nL, const double* const* disjoint_L
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.ang_m = c->mval;
   S.fam_owned.resize(nL);
-  {
-    std::vector<int> famL(nL), famM(nL, -1);
-    for (int L = 0; L < nL; L++) famL[L] = L;
-    c->fam_owner = family_owner(c->lval, c->mval, famL, famM, 0, c->shard_n);
-  }
+  c->fam_owner = family_owner(nL, c->shard_n);
   const std::vector<int> own = c->fam_owner;
   for (int L = 0; L < nL; L++) S.fam_owned[L] = (own[L] == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nL);

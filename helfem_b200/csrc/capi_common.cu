@@ -43,8 +43,8 @@ int hfb200_device_count(void) {
 }
 
 /* Multi-GPU sharding of the atomic / diatomic operators: this context only holds and contracts the
- * integral families the cost-balanced map of host/famshard.h gives to `rank` (atomic: r = L; diatomic:
- * r = index of (L,|M|)); the results of the ranks add up to the full J / K (all-reduced inside the library
+ * integral families r with r % nranks == rank (host/famshard.h; atomic: r = L; diatomic: r = index of
+ * (L,|M|)); the results of the ranks add up to the full J / K (all-reduced inside the library
  * once a communicator is attached, comm.cu).  Must be called before *_set_tei. */
 int hfb200_set_shard(hfb200_ctx* c, int rank, int nranks) {
   if (!c || nranks < 1 || rank < 0 || rank >= nranks) { hfb::set_error("hfb200_set_shard: invalid argument"); return HFB200_EINVAL; }

@@ -102,7 +102,7 @@ int hfb200_diatomic_set_tei(hfb200_ctx* c, int nlm, const int* Lmap, const int* 
   for (int a = 0; a < nang; a++) S.ang_group[a] = 2 * c->mval[a] + (c->lval[a] & 1);
   S.ang_m = c->mval;
   S.fam_owned.resize(nlm);
-  c->fam_owner = family_owner(c->lval, c->mval, std::vector<int>(Lmap, Lmap + nlm), std::vector<int>(Mmap, Mmap + nlm), 2, c->shard_n);
+  c->fam_owner = family_owner(nlm, c->shard_n);
   const std::vector<int> own = c->fam_owner;
   for (int r = 0; r < nlm; r++) S.fam_owned[r] = (own[r] == c->shard_rank);  // couplings of ALL families are listed below
   S.fac.resize(nlm);

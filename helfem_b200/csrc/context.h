@@ -84,7 +84,7 @@ struct hfb200_ctx {
   std::vector<int> lval, mval;
   double Rhalf = 0.0;
   int shard_rank = 0, shard_n = 1;  // this context holds the integral families r with fam_owner[r] == shard_rank
-  std::vector<int> fam_owner;       // [families] owning rank (host/famshard.h: dealt by predicted cost), filled by set_tei
+  std::vector<int> fam_owner;       // [families] owning rank (host/famshard.h), filled by set_tei
   void* comm = nullptr;             // ncclComm_t of the sharded operators (comm.cu), or null: the caller sums the partial operators
   hfb::ChanEngine* chan = nullptr;
   hfb::Grid2D* g2d = nullptr;  // product-grid XC engine (grid2d.h)

@@ -110,7 +110,7 @@ class DiatomicBasis:
         check(lib().hfb200_chan_set_profile(self.context(), int(bool(on))))
 
     def set_shard(self, rank, nranks, owned_only=False):
-        """Multi-GPU: contract only the integral families that the cost-balanced map (shard.family_owners) gives to `rank` (before the first operator call).
+        """Multi-GPU: contract only the integral families r % nranks == rank (before the first operator call).
         owned_only: compute_tei builds the stored integrals of the owned families only."""
         check_host(lib().hfh_diatomic_set_shard(self._h, int(rank), int(nranks)))
         check_host(lib().hfh_diatomic_set_owned_only(self._h, int(bool(owned_only))))

@@ -212,12 +212,7 @@ void TwoDBasis::compute_tei(bool exchange) {
   for (int w = 0; w < 4; w++) disjoint[w].assign(Nel * nlm, Mat());
   prim_tei.assign(4 * Nel * nlm, Mat());
   prim_ktei.assign(exchange ? 4 * Nel * nlm : 0, Mat());
-  std::vector<int> own(nlm, 0);
-  if (owned_only) {  // the same cost-balanced map the C ABI derives (host/famshard.h)
-    std::vector<int> fL(nlm), fM(nlm);
-    for (size_t q = 0; q < nlm; q++) { fL[q] = lm_map[q].first; fM[q] = lm_map[q].second; }
-    own = family_owner(lval, mval, fL, fM, 2, shard_n);
-  }
+  const std::vector<int> own = family_owner((int)nlm, owned_only ? shard_n : 1);  // the map the C ABI applies (host/famshard.h)
 #ifdef _OPENMP
 #pragma omp parallel for collapse(2) schedule(dynamic)
 #endif

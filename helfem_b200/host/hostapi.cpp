@@ -460,10 +460,9 @@ void hfh_scan_nonzero_blocks(const double* M, int ld, int nang, const int* r0, c
 void hfh_zero_fill(double* M, int ld, int n) { hfb::zero_fill(M, ld, n); }
 }
 
-// ---- the cost-balanced family -> rank map of the sharded operators (host/famshard.h), for tests and harnesses ----
+// ---- the family -> rank map of the sharded operators (host/famshard.h), for tests and harnesses ----
 #include "famshard.h"
-extern "C" void hfh_family_owner(int nang, const int* lval, const int* mval, int nfam, const int* famL, const int* famM, int reach, int nranks, int* owner) {
-  const std::vector<int> own = hfb::family_owner(std::vector<int>(lval, lval + nang), std::vector<int>(mval, mval + nang), std::vector<int>(famL, famL + nfam),
-                                                 std::vector<int>(famM, famM + nfam), reach, nranks);
+extern "C" void hfh_family_owner(int nfam, int nranks, int* owner) {
+  const std::vector<int> own = hfb::family_owner(nfam, nranks);
   for (int r = 0; r < nfam; r++) owner[r] = own[r];
 }

@@ -7,11 +7,9 @@ Two partitions exist, matching how the reference's work decomposes:
 * atomic / diatomic J and K (configs[0]/[3]): the operator is a SUM over integral families
   (atomic: L of the Legendre expansion, /root/reference/src/atomic/TwoDBasis.cpp:973-1073;
   diatomic: (L,|M|) of the Neumann expansion, /root/reference/src/diatomic/TwoDBasis.cpp:1029-1143).
-  The families are dealt to the ranks by predicted cost (`family_owners`: the library's rule, helfem_b200/host/famshard.h,
-  used by `hfb200_set_shard`), so every rank holds ~1/nranks of the two-electron integrals and does ~1/nranks of the
-  contractions; the partial operators are summed by ONE all-reduce (NCCL over NVLink inside the library on GPUs; gloo in the CPU
-  tests) -- `allreduce_operator`.  ANY partition of the families gives the same sum: the oracle-side CPU tests use the plain
-  round-robin `family_owner`.
+  Family r lives on rank r % nranks (`hfb200_set_shard`, helfem_b200/host/famshard.h), so every rank holds 1/nranks of the
+  two-electron integrals and does 1/nranks of the contractions; the partial operators are summed by ONE all-reduce (NCCL over
+  NVLink inside the library on GPUs; gloo in the CPU tests) -- `allreduce_operator`.
 
 Harness-side helper (torch.distributed is plumbing); the per-rank compute is the C-ABI library.
 """
@@ -19,24 +17,18 @@ import numpy as np
 
 
 def family_owner(r, nranks):
-    """Round-robin rank of family r: the partition the oracle-side tests use (any partition of the families sums to the same
-    operator); the library itself balances by cost, see family_owners."""
+    """Rank that holds integral family r (the rule hfb200_set_shard applies, helfem_b200/host/famshard.h)."""
     return r % nranks
 
 
-def family_owners(lval, mval, famL, famM, reach, nranks):
-    """The library's family -> rank map (helfem_b200/host/famshard.h; what hfb200_set_shard applies): families dealt by predicted
-    exchange cost, longest first.  famM[r] = |M| of the family, or -1 for a family that holds every M (atomic); reach = 0 (atomic)
-    or 2 (diatomic)."""
+def family_owners(nfam, nranks):
+    """The library's own family -> rank map (helfem_b200/host/famshard.h), through the host library."""
     import ctypes
     from . import lib
-    ci = lambda a: np.ascontiguousarray(a, dtype=np.int32)
-    lval, mval, famL, famM = ci(lval), ci(mval), ci(famL), ci(famM)
-    out = np.zeros(len(famL), dtype=np.int32)
-    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    out = np.zeros(nfam, dtype=np.int32)
     L = lib()
     L.hfh_family_owner.restype = None
-    L.hfh_family_owner(len(lval), p(lval), p(mval), len(famL), p(famL), p(famM), int(reach), int(nranks), p(out))
+    L.hfh_family_owner(int(nfam), int(nranks), out.ctypes.data_as(ctypes.c_void_p))
     return out
 
 

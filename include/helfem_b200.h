@@ -76,10 +76,9 @@ int hfb200_sadatom_set_tei(hfb200_ctx* ctx, int nL, const double* const* disjoin
                            const double* const* prim_ktei);
 void hfb200_destroy(hfb200_ctx* ctx);
 /* Multi-GPU sharding of the atomic / diatomic operators (one process per GPU): the context only holds and
- * contracts the integral families r (atomic: r = L; diatomic: r = index of (L,|M|) in lm_map) that the
- * cost-balanced map of helfem_b200/host/famshard.h gives to `rank`: the families are dealt to the ranks by
- * predicted exchange cost, longest first, identically on every rank.  *_set_tei reads the stored integrals of
- * the owned families only (hfb200_shard_owner tells which; the other pointers may be NULL).  The partial J / K
+ * contracts the integral families r (atomic: r = L; diatomic: r = index of (L,|M|) in lm_map) with
+ * r % nranks == rank (helfem_b200/host/famshard.h).  *_set_tei reads the stored integrals of the owned
+ * families only (hfb200_shard_owner returns the map; the other pointers may be NULL).  The partial J / K
  * of the ranks add up to the full operator; they are all-reduced inside the library once a communicator is
  * attached (below), else by the caller.  Call before *_set_tei. */
 int hfb200_set_shard(hfb200_ctx* ctx, int rank, int nranks);

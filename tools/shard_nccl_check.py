@@ -3,7 +3,7 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 \
         tools/shard_nccl_check.py [--lmax 4 --mmax 2 --nelem 4 --nnodes 8]
 
-Every rank builds the same basis, owns its cost-balanced share of the integral families (hfb200_set_shard), attaches the communicator
+Every rank builds the same basis, owns the integral families r % N == rank (hfb200_set_shard), attaches the communicator
 and calls the host-matrix operators TwoDBasis::coulomb / exchange, which return the COMPLETE J / K on every rank.  Every
 rank compares with the CPU oracle (full family loop, unsharded second host object) for a symmetric AND a non-symmetric
 density (the two item lists of the exchange engine); rank 0 prints one JSON line."""
