@@ -1,4 +1,8 @@
-"""debug: timeline of the same-element kernel's phases on SMs 0..3 (library built with -DHFB_XF_TRACE)"""
+"""Debug: phase timeline of the fused exchange kernels on the first SMs (%globaltimer stamps written by thread 0 of every CTA).
+Needs a library built with the trace points:  HFB200_NVCC_EXTRA="-DHFB_XF_TRACE" python -m helfem_b200.build --force
+    python tools/xf_trace.py        # same-element kernel: phase 1 / phase 2 of every stack pair
+    python tools/xf_trace.py pair   # element-pair kernel
+Outputs of round 2: profiles/r02_xf_trace_*.txt (the pair trace there also had stamps inside the stage loop)."""
 import ctypes, sys, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -20,9 +24,9 @@ for sm in range(2):
     n = min(int(cnt[sm]), 4096)
     raw = [(int(v) >> 20, (int(v) >> 4) & 0xffff, int(v) & 15) for v in out[sm * 4096: sm * 4096 + n]]
     info = {blk: (t // 100000, t % 100000) for t, blk, e in raw if e == 5}
-    ev = sorted(x for x in raw if x[2] in ((6, 7, 8, 9, 10, 11, 12) if "pair" in sys.argv else (1, 2, 3, 4)))
+    ev = sorted(x for x in raw if x[2] in ((6, 7, 8) if "pair" in sys.argv else (1, 2, 3, 4)))
     t0 = ev[0][0]
     print("  cta: (tiles, slots)", {k: info[k] for k in list(info)[:12]})
     print("SM", sm, "events", n)
     for t, blk, e in [x for x in ev if x[1] == ev[0][1]][:70]:
-        print("  %9.2f us  cta %5d  %s" % ((t - t0) / 1e3, blk, {1: "P1 begin", 2: "P1 end", 3: "P2 begin", 4: "P2 end", 6: "pair P1 begin (= previous P2 end)", 7: "pair P1 end", 8: "pair P2 begin", 9: "  stage: before full wait", 10: "  stage: data there", 11: "  stage: consumed", 12: "  tile emitted"}[e]))
+        print("  %9.2f us  cta %5d  %s" % ((t - t0) / 1e3, blk, {1: "P1 begin", 2: "P1 end", 3: "P2 begin", 4: "P2 end", 6: "pair P1 begin (= previous P2 end)", 7: "pair P1 end", 8: "pair P2 begin"}[e]))
