@@ -85,5 +85,13 @@ def test_set_shard_after_tei_is_refused(native):
     b.compute_tei(False)
     n = b.nbf
     b.coulomb(np.asfortranarray(np.eye(n)))  # creates the context and uploads the integrals
-    rc = native.hfb200_set_shard(None, 0, 1)
-    assert rc == hb.EINVAL
+    import ctypes
+    native.hfb200_set_shard.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+    assert native.hfb200_set_shard(None, 0, 1) == hb.EINVAL           # null context
+    assert native.hfb200_set_shard(b.context(), 0, 2) == hb.EINVAL    # the context already holds the full set of integrals
+    assert b"precede" in hb.lib().hfb200_last_error()
+    with pytest.raises(Exception):                                    # the host class refuses as well (std::logic_error)
+        b.set_shard(0, 2)
+    own = np.zeros(1, dtype=np.int32)
+    native.hfb200_shard_owner.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    assert native.hfb200_shard_owner(b.context(), own.ctypes.data_as(ctypes.c_void_p), 1) == 0 and own[0] == 0
