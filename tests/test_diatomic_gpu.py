@@ -219,3 +219,19 @@ def test_diatomic_contexts_on_two_devices_in_one_process(native):
     for b in (b1, b0, b1):
         assert np.array_equal(b.exchange(P), b0.exchange(P))
         assert np.array_equal(b.coulomb(P), b0.coulomb(P))
+
+
+@pytest.mark.parametrize("case", ["n2_l2m1", "co_l3m2", "n2_hip_l1m1", "n2_l5m2"])
+def test_diatomic_bare_gate_on_a_normalised_density(native, case):
+    """The north star's gate is 1e-9 ABSOLUTE.  The seeded densities above populate every angular block with O(1) noise and reach
+    |J| ~ 1e5, where only the relative branch of tol() can hold; here the density is what an SCF produces -- m-pure orbitals,
+    Loewdin-orthonormalised in the overlap metric (tr(P S) = 14) -- and J, K must agree with the oracle to 1e-9 absolute, no escape.
+    (BASELINE configs[3] at full size is held to the same bare gate by test_cfg4_fullsize_gpu.py.)"""
+    from util import diatomic_orbitals
+    b, o, _ = setup_case(case)
+    C = diatomic_orbitals(b)
+    pure = b.pure_indices()
+    P = np.asfortranarray(2.0 * C[pure] @ C[pure].T)
+    J, K = b.coulomb(P), b.exchange(P)
+    dJ, dK = float(np.max(np.abs(J - o.coulomb(P)))), float(np.max(np.abs(K - o.exchange(P))))
+    assert dJ <= 1e-9 and dK <= 1e-9, (dJ, dK, float(np.max(np.abs(J))), float(np.max(np.abs(K))))
