@@ -1,6 +1,7 @@
 """Generates tests/golden/xc_mpmath.npz: seeded spin-resolved test points (above every threshold, sigma > 0) and the libxc-style
 outputs of the six functionals (+ lda_c_pw_mod) from the 50-digit mpmath restatement tests/xc_mpmath.py, polarised and
-unpolarised.  Usage (authoring container, CPU, a few minutes):  python tests/golden/make_xc_mpmath_goldens.py [npoints]"""
+unpolarised.  Usage (authoring container, CPU, all cores; the committed fixture has 1024 points, 8192 take ~3 minutes on 8 cores):
+    python tests/golden/make_xc_mpmath_goldens.py 1024"""
 import os
 import sys
 
@@ -38,20 +39,26 @@ def points(n, seed=20261104):
     return rho, sigma, tau
 
 
+def _one(args):
+    fid, r, sg, t = args
+    e, vr, vs, vt = xm.evaluate_polarised(fid, r[0], r[1], sg[0], sg[1], sg[2], t[0], t[1])
+    u = xm.evaluate_unpolarised(fid, 2 * r[0], 4 * sg[0], 2 * t[0])
+    return (float(e), [float(v) for v in vr], [float(v) for v in vs], [float(v) for v in vt]) + tuple(float(v) for v in u)
+
+
 def main():
+    import multiprocessing as mp
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 512
     rho, sigma, tau = points(n)
     out = {"rho": rho, "sigma": sigma, "tau": tau}
-    for fid in FIDS:
-        pe, pvr, pvs, pvt = np.zeros(n), np.zeros((n, 2)), np.zeros((n, 3)), np.zeros((n, 2))
-        ue, uvr, uvs, uvt = np.zeros(n), np.zeros(n), np.zeros(n), np.zeros(n)
-        for i in range(n):
-            e, vr, vs, vt = xm.evaluate_polarised(fid, rho[i, 0], rho[i, 1], sigma[i, 0], sigma[i, 1], sigma[i, 2], tau[i, 0], tau[i, 1])
-            pe[i], pvr[i], pvs[i], pvt[i] = e, vr, vs, vt
-            ue[i], uvr[i], uvs[i], uvt[i] = xm.evaluate_unpolarised(fid, 2 * rho[i, 0], 4 * sigma[i, 0], 2 * tau[i, 0])
-        out.update({"p%d_exc" % fid: pe, "p%d_vrho" % fid: pvr, "p%d_vsigma" % fid: pvs, "p%d_vtau" % fid: pvt,
-                    "u%d_exc" % fid: ue, "u%d_vrho" % fid: uvr, "u%d_vsigma" % fid: uvs, "u%d_vtau" % fid: uvt})
-        print("functional", fid, "done", flush=True)
+    with mp.Pool() as pool:
+        for fid in FIDS:
+            res = pool.map(_one, [(fid, rho[i], sigma[i], tau[i]) for i in range(n)], chunksize=16)
+            out.update({"p%d_exc" % fid: np.array([r[0] for r in res]), "p%d_vrho" % fid: np.array([r[1] for r in res]),
+                        "p%d_vsigma" % fid: np.array([r[2] for r in res]), "p%d_vtau" % fid: np.array([r[3] for r in res]),
+                        "u%d_exc" % fid: np.array([r[4] for r in res]), "u%d_vrho" % fid: np.array([r[5] for r in res]),
+                        "u%d_vsigma" % fid: np.array([r[6] for r in res]), "u%d_vtau" % fid: np.array([r[7] for r in res])})
+            print("functional", fid, "done", flush=True)
     np.savez_compressed(os.path.join(HERE, "xc_mpmath.npz"), **out)
 
 
