@@ -822,7 +822,9 @@ def run_chan(args, w, rank, world, local_rank):
                 "whole_build_frac_fp64": (f_same + f_pair) / (ms / args.steps * 1e-3) / 1e12 / FP64_TFLOPS_MEASURED,
                 "radial_flops_per_build": x3_flops, "ms_coulomb": ms_j, "ms_exchange": ms_k, "output_blocks": items,
                 "symmetric_item_list": bool(cnt[8]), "family_batches": b.exchange_batches(), "w_bytes": w_bytes}
-    nlaunch = 5 + 1 + 4 * b.exchange_batches() + (2 if sharded else 0)
+    # our kernels per build (ncu launch list, profiles/r02w_launches_n2_hf_cfg4.csv): Coulomb pack, pre, jmma, flag, post, unpack; the mask; x1, fused
+    # same-element, fused pairs, x4 per family batch; sharded: + mask-flag conversion, block gather, block scatter (NCCL's own kernels not counted)
+    nlaunch = 6 + 1 + 4 * b.exchange_batches() + (3 if sharded else 0)
     line = {"metric": "fock_builds_per_sec", "value": value, "unit": "builds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
